@@ -1,0 +1,378 @@
+// C++ host implementations of the "native" aggregation rules (float and double).
+//
+// Capability parity with the reference's CPU natives
+//   krum    /root/reference/pytorch_impl/libs/native/py_krum/krum.cpp:50-118
+//   bulyan  /root/reference/pytorch_impl/libs/native/py_bulyan/bulyan.cpp:53-193
+//   median  /root/reference/pytorch_impl/libs/native/py_median/median.cpp:42-77
+//   brute   /root/reference/pytorch_impl/libs/native/py_brute/brute.cpp:47-113
+// and their helpers (operations.hpp:41-79). Exposed through a plain C ABI (no torch headers);
+// garfield_b200/native binds them with ctypes.
+//
+// Design: all pairwise squared distances come from ONE blocked sweep over the n×d data (each
+// cache-resident coordinate block updates all n(n-1)/2 accumulators) instead of n(n-1)/2
+// separate passes; selection logic works on the n×n matrix; the output pass is blocked the
+// same way. Partial sums are kept per block in double and combined in block order, so results
+// do not depend on the thread count.
+
+#include <algorithm>
+#include <cmath>
+#include <cstdint>
+#include <cstring>
+#include <limits>
+#include <numeric>
+#include <string>
+#include <vector>
+
+#include "combinations.hpp"
+#include "garfield_b200.h"
+#include "threadpool.hpp"
+
+namespace {
+
+thread_local std::string tl_error;
+
+int fail(char const* what) {
+    tl_error = what;
+    return 1;
+}
+
+constexpr std::size_t kBlock = 4096;  // coordinates per work item (n rows × 16 KiB fp32 stays in L1/L2)
+
+template <class T>
+bool finite(T v) { return std::isfinite(v); }
+
+// Strict weak order: finite ascending, every non-finite value after all finite ones.
+template <class T>
+bool finite_less(T x, T y) {
+    if (!finite(x)) return false;
+    if (!finite(y)) return true;
+    return x < y;
+}
+
+// dist[i*n+j] = Σ_x (g_i[x] − g_j[x])², symmetric, diagonal untouched (caller fills).
+template <class T>
+void pairwise_sqdist(T const* const* in, int n, std::int64_t d, std::vector<double>& dist) {
+    std::size_t const pairs = static_cast<std::size_t>(n) * (n - 1) / 2;
+    std::size_t const blocks = (static_cast<std::size_t>(d) + kBlock - 1) / kBlock;
+    std::vector<double> partial(blocks * pairs, 0.0);
+    gb::parallel_for(0, blocks, [&](std::size_t lo, std::size_t hi) {
+        for (std::size_t b = lo; b < hi; ++b) {
+            std::size_t const x0 = b * kBlock;
+            std::size_t const x1 = std::min<std::size_t>(static_cast<std::size_t>(d), x0 + kBlock);
+            double* acc = partial.data() + b * pairs;
+            std::size_t p = 0;
+            for (int i = 0; i < n - 1; ++i) {
+                T const* gi = in[i];
+                for (int j = i + 1; j < n; ++j, ++p) {
+                    T const* gj = in[j];
+                    T s0 = 0, s1 = 0, s2 = 0, s3 = 0;  // 4 lanes of input-precision partial sums
+                    std::size_t x = x0;
+                    for (; x + 4 <= x1; x += 4) {
+                        T const a = gi[x] - gj[x], c = gi[x + 1] - gj[x + 1];
+                        T const e = gi[x + 2] - gj[x + 2], g = gi[x + 3] - gj[x + 3];
+                        s0 += a * a; s1 += c * c; s2 += e * e; s3 += g * g;
+                    }
+                    for (; x < x1; ++x) {
+                        T const a = gi[x] - gj[x];
+                        s0 += a * a;
+                    }
+                    acc[p] = static_cast<double>(s0) + static_cast<double>(s1) + static_cast<double>(s2) + static_cast<double>(s3);
+                }
+            }
+        }
+    });
+    dist.assign(static_cast<std::size_t>(n) * n, 0.0);
+    std::size_t p = 0;
+    for (int i = 0; i < n - 1; ++i)
+        for (int j = i + 1; j < n; ++j, ++p) {
+            double total = 0.0;
+            for (std::size_t b = 0; b < blocks; ++b) total += partial[b * pairs + p];
+            dist[static_cast<std::size_t>(i) * n + j] = dist[static_cast<std::size_t>(j) * n + i] = total;
+        }
+}
+
+// out[x] = Σ_k w[k] · in[sel[k]][x]
+template <class T>
+void weighted_sum(T const* const* in, std::int64_t d, int const* sel, T const* w, int count, T* out) {
+    std::size_t const blocks = (static_cast<std::size_t>(d) + kBlock - 1) / kBlock;
+    gb::parallel_for(0, blocks, [&](std::size_t lo, std::size_t hi) {
+        for (std::size_t b = lo; b < hi; ++b) {
+            std::size_t const x0 = b * kBlock;
+            std::size_t const x1 = std::min<std::size_t>(static_cast<std::size_t>(d), x0 + kBlock);
+            T const* first = in[sel[0]];
+            for (std::size_t x = x0; x < x1; ++x) out[x] = first[x] * w[0];
+            for (int k = 1; k < count; ++k) {
+                T const* g = in[sel[k]];
+                T const wk = w[k];
+                for (std::size_t x = x0; x < x1; ++x) out[x] += g[x] * wk;
+            }
+        }
+    });
+}
+
+template <class T>
+void selection_average(T const* const* in, std::int64_t d, int const* sel, int count, T* out) {
+    // sum then divide (matches the reference's accumulate-then-divide rounding)
+    std::size_t const blocks = (static_cast<std::size_t>(d) + kBlock - 1) / kBlock;
+    T const denom = static_cast<T>(count);
+    gb::parallel_for(0, blocks, [&](std::size_t lo, std::size_t hi) {
+        for (std::size_t b = lo; b < hi; ++b) {
+            std::size_t const x0 = b * kBlock;
+            std::size_t const x1 = std::min<std::size_t>(static_cast<std::size_t>(d), x0 + kBlock);
+            T const* first = in[sel[0]];
+            for (std::size_t x = x0; x < x1; ++x) out[x] = first[x];
+            for (int k = 1; k < count; ++k) {
+                T const* g = in[sel[k]];
+                for (std::size_t x = x0; x < x1; ++x) out[x] += g[x];
+            }
+            for (std::size_t x = x0; x < x1; ++x) out[x] /= denom;
+        }
+    });
+}
+
+// score_i = Σ of the `keep` smallest finite-ordered distances touching i; order[i] lists the
+// other gradients by increasing distance (ties by index).
+void neighbour_scores(std::vector<double> const& dist, int n, int keep, std::vector<double>& scores,
+                      std::vector<std::vector<int>>& order) {
+    scores.assign(n, 0.0);
+    order.assign(n, {});
+    for (int i = 0; i < n; ++i) {
+        auto& row = order[i];
+        for (int j = 0; j < n; ++j)
+            if (j != i) row.push_back(j);
+        double const* di = dist.data() + static_cast<std::size_t>(i) * n;
+        std::stable_sort(row.begin(), row.end(), [&](int a, int b) { return finite_less(di[a], di[b]); });
+        double s = 0.0;
+        for (int k = 0; k < keep; ++k) s += di[row[k]];
+        scores[i] = s;
+    }
+}
+
+std::vector<int> by_score(std::vector<double> const& scores) {
+    std::vector<int> idx(scores.size());
+    std::iota(idx.begin(), idx.end(), 0);
+    std::stable_sort(idx.begin(), idx.end(), [&](int a, int b) { return finite_less(scores[a], scores[b]); });
+    return idx;
+}
+
+template <class T>
+int krum(T const* const* in, int n, std::int64_t d, int f, int m, T* out) {
+    if (n < 1 || d < 1) return fail("krum: expected at least one non-empty gradient");
+    if (f < 1 || n < 2 * f + 3) return fail("krum: need f >= 1 and n >= 2f+3");
+    if (m < 1 || m > n - f - 2) return fail("krum: need 1 <= m <= n-f-2");
+    std::vector<double> dist;
+    pairwise_sqdist(in, n, d, dist);
+    std::vector<double> scores;
+    std::vector<std::vector<int>> order;
+    neighbour_scores(dist, n, n - f - 2, scores, order);
+    std::vector<int> best = by_score(scores);
+    selection_average(in, d, best.data(), m, out);
+    return 0;
+}
+
+template <class T>
+int bulyan(T const* const* in, int n, std::int64_t d, int f, int m, T* out) {
+    if (n < 1 || d < 1) return fail("bulyan: expected at least one non-empty gradient");
+    if (f < 1 || n < 4 * f + 3) return fail("bulyan: need f >= 1 and n >= 4f+3");
+    if (m < 1 || m > n - f - 2) return fail("bulyan: need 1 <= m <= n-f-2");
+    int const keep = n - f - 2;
+    int const theta = n - 2 * f - 2;
+    int const beta = theta - 2 * f;
+    std::vector<double> dist;
+    pairwise_sqdist(in, n, d, dist);
+    std::vector<double> scores;
+    std::vector<std::vector<int>> order;
+    neighbour_scores(dist, n, keep, scores, order);
+    // kept[i][j] = dist(i,j) when j is one of i's `keep` nearest, else 0 ("pruned")
+    std::vector<double> kept(static_cast<std::size_t>(n) * n, 0.0);
+    for (int i = 0; i < n; ++i)
+        for (int k = 0; k < keep; ++k) {
+            int const j = order[i][k];
+            kept[static_cast<std::size_t>(i) * n + j] = dist[static_cast<std::size_t>(i) * n + j];
+        }
+    // θ selection rounds → θ×n weights
+    std::vector<T> weights(static_cast<std::size_t>(theta) * n, T(0));
+    for (int k = 0; k < theta; ++k) {
+        std::vector<int> rank = by_score(scores);
+        int const take = m - k;
+        for (int r = 0; r < take; ++r) weights[static_cast<std::size_t>(k) * n + rank[r]] = T(1) / static_cast<T>(take);
+        if (k + 1 >= theta) break;
+        int const gone = rank[0];
+        scores[gone] = std::numeric_limits<double>::infinity();
+        for (int i = 0; i < n; ++i)
+            if (i != gone && std::isfinite(scores[i])) scores[i] -= kept[static_cast<std::size_t>(i) * n + gone];
+    }
+    // phase 2, fused per coordinate block: θ round-averages in a small local tile, then the
+    // mean of the β values closest to their (upper) median
+    std::size_t const blocks = (static_cast<std::size_t>(d) + kBlock - 1) / kBlock;
+    gb::parallel_for(0, blocks, [&](std::size_t lo, std::size_t hi) {
+        std::vector<T> tile(static_cast<std::size_t>(theta) * kBlock);
+        std::vector<T> column(theta);
+        for (std::size_t b = lo; b < hi; ++b) {
+            std::size_t const x0 = b * kBlock;
+            std::size_t const len = std::min<std::size_t>(static_cast<std::size_t>(d), x0 + kBlock) - x0;
+            std::fill(tile.begin(), tile.end(), T(0));
+            for (int k = 0; k < theta; ++k) {
+                T* row = tile.data() + static_cast<std::size_t>(k) * kBlock;
+                for (int i = 0; i < n; ++i) {
+                    T const w = weights[static_cast<std::size_t>(k) * n + i];
+                    if (w == T(0)) continue;
+                    T const* g = in[i] + x0;
+                    for (std::size_t x = 0; x < len; ++x) row[x] += g[x] * w;
+                }
+            }
+            for (std::size_t x = 0; x < len; ++x) {
+                for (int k = 0; k < theta; ++k) column[k] = tile[static_cast<std::size_t>(k) * kBlock + x];
+                std::nth_element(column.begin(), column.begin() + theta / 2, column.end());
+                T const med = column[theta / 2];
+                std::nth_element(column.begin(), column.begin() + (beta - 1), column.end(), [&](T a, T c) {
+                    return std::fabs(a - med) < std::fabs(c - med);
+                });
+                T sum = 0;
+                for (int k = 0; k < beta; ++k) sum += column[k];
+                out[x0 + x] = sum / static_cast<T>(beta);
+            }
+        }
+    });
+    return 0;
+}
+
+template <class T>
+int median(T const* const* in, int n, std::int64_t d, T* out) {
+    if (n < 1 || d < 1) return fail("median: expected at least one non-empty gradient");
+    gb::parallel_for(0, static_cast<std::size_t>(d), [&](std::size_t lo, std::size_t hi) {
+        std::vector<T> column(n);
+        for (std::size_t x = lo; x < hi; ++x) {
+            int len = 0;
+            for (int i = 0; i < n; ++i) {
+                T const v = in[i][x];
+                if (finite(v)) column[len++] = v;
+            }
+            if (len == 0) {
+                out[x] = 0;
+                continue;
+            }
+            std::nth_element(column.begin(), column.begin() + len / 2, column.begin() + len);
+            out[x] = column[len / 2];
+        }
+    }, 8192);
+    return 0;
+}
+
+template <class T>
+int brute(T const* const* in, int n, std::int64_t d, int f, T* out) {
+    if (n < 1 || d < 1) return fail("brute: expected at least one non-empty gradient");
+    if (f < 1 || n < 2 * f + 1) return fail("brute: need f >= 1 and n >= 2f+1");
+    int const k = n - f;
+    bool overflow = false;
+    std::uint64_t const total = gb::binomial(static_cast<unsigned>(n), static_cast<unsigned>(k), &overflow);
+    if (overflow || total == 0) return fail("brute: too many combinations");
+    std::vector<double> dist;
+    pairwise_sqdist(in, n, d, dist);
+    for (auto& v : dist)
+        if (!std::isfinite(v)) v = std::numeric_limits<double>::max();
+    // every chunk keeps its first strict minimum; chunks are merged in rank order so the
+    // lexicographically first minimal subset wins regardless of the thread count
+    std::size_t const chunks = std::min<std::uint64_t>(total, 4ull * gb::ThreadPool::global().size());
+    std::vector<double> best_diam(chunks, std::numeric_limits<double>::infinity());
+    std::vector<std::uint64_t> best_pos(chunks, 0);
+    gb::parallel_for(0, chunks, [&](std::size_t lo, std::size_t hi) {
+        std::vector<int> idx(k);
+        for (std::size_t c = lo; c < hi; ++c) {
+            std::uint64_t const start = total * c / chunks, stop = total * (c + 1) / chunks;
+            if (start >= stop) continue;
+            gb::combination_unrank(static_cast<unsigned>(n), static_cast<unsigned>(k), start, idx.data());
+            for (std::uint64_t pos = start; pos < stop; ++pos) {
+                double diam = 0.0;
+                for (int a = 0; a < k - 1; ++a) {
+                    double const* row = dist.data() + static_cast<std::size_t>(idx[a]) * n;
+                    for (int b = a + 1; b < k; ++b) diam = std::max(diam, row[idx[b]]);
+                }
+                if (diam < best_diam[c]) {
+                    best_diam[c] = diam;
+                    best_pos[c] = pos;
+                }
+                gb::combination_next(static_cast<unsigned>(n), static_cast<unsigned>(k), idx.data());
+            }
+        }
+    }, 1);
+    std::size_t win = 0;
+    for (std::size_t c = 1; c < chunks; ++c)
+        if (best_diam[c] < best_diam[win]) win = c;
+    std::vector<int> idx(k);
+    gb::combination_unrank(static_cast<unsigned>(n), static_cast<unsigned>(k), best_pos[win], idx.data());
+    selection_average(in, d, idx.data(), k, out);
+    return 0;
+}
+
+template <class T>
+int sqdist_matrix(T const* const* in, int n, std::int64_t d, double* out) {
+    if (n < 1 || d < 1) return fail("pairwise_sqdist: expected at least one non-empty gradient");
+    std::vector<double> dist;
+    if (n > 1) pairwise_sqdist(in, n, d, dist); else dist.assign(1, 0.0);
+    for (int i = 0; i < n; ++i) dist[static_cast<std::size_t>(i) * n + i] = std::numeric_limits<double>::infinity();
+    std::memcpy(out, dist.data(), sizeof(double) * static_cast<std::size_t>(n) * n);
+    return 0;
+}
+
+template <class F>
+int guarded(F&& body) {
+    try {
+        return body();
+    } catch (std::exception const& err) {
+        tl_error = err.what();
+        return 2;
+    } catch (...) {
+        tl_error = "unknown C++ exception";
+        return 2;
+    }
+}
+
+}  // namespace
+
+extern "C" {
+
+GB_API char const* gb_cpu_last_error(void) { return tl_error.c_str(); }
+GB_API int gb_cpu_num_threads(void) { return static_cast<int>(gb::ThreadPool::global().size()); }
+
+GB_API int gb_cpu_krum_f32(float const* const* in, int n, int64_t d, int f, int m, float* out) { return guarded([&] { return krum(in, n, d, f, m, out); }); }
+GB_API int gb_cpu_krum_f64(double const* const* in, int n, int64_t d, int f, int m, double* out) { return guarded([&] { return krum(in, n, d, f, m, out); }); }
+GB_API int gb_cpu_bulyan_f32(float const* const* in, int n, int64_t d, int f, int m, float* out) { return guarded([&] { return bulyan(in, n, d, f, m, out); }); }
+GB_API int gb_cpu_bulyan_f64(double const* const* in, int n, int64_t d, int f, int m, double* out) { return guarded([&] { return bulyan(in, n, d, f, m, out); }); }
+GB_API int gb_cpu_median_f32(float const* const* in, int n, int64_t d, float* out) { return guarded([&] { return median(in, n, d, out); }); }
+GB_API int gb_cpu_median_f64(double const* const* in, int n, int64_t d, double* out) { return guarded([&] { return median(in, n, d, out); }); }
+GB_API int gb_cpu_brute_f32(float const* const* in, int n, int64_t d, int f, float* out) { return guarded([&] { return brute(in, n, d, f, out); }); }
+GB_API int gb_cpu_brute_f64(double const* const* in, int n, int64_t d, int f, double* out) { return guarded([&] { return brute(in, n, d, f, out); }); }
+GB_API int gb_cpu_pairwise_sqdist_f32(float const* const* in, int n, int64_t d, double* out) { return guarded([&] { return sqdist_matrix(in, n, d, out); }); }
+GB_API int gb_cpu_pairwise_sqdist_f64(double const* const* in, int n, int64_t d, double* out) { return guarded([&] { return sqdist_matrix(in, n, d, out); }); }
+
+GB_API int gb_cpu_selection_average_f32(float const* const* in, int64_t d, int const* sel, int count, float* out) {
+    return guarded([&] { if (count < 1) return fail("selection_average: empty selection"); selection_average(in, d, sel, count, out); return 0; });
+}
+GB_API int gb_cpu_selection_average_f64(double const* const* in, int64_t d, int const* sel, int count, double* out) {
+    return guarded([&] { if (count < 1) return fail("selection_average: empty selection"); selection_average(in, d, sel, count, out); return 0; });
+}
+GB_API int gb_cpu_weighted_sum_f32(float const* const* in, int64_t d, int const* sel, float const* w, int count, float* out) {
+    return guarded([&] { if (count < 1) return fail("weighted_sum: empty selection"); weighted_sum(in, d, sel, w, count, out); return 0; });
+}
+
+GB_API uint64_t gb_combinations_count(unsigned n, unsigned k, int* overflow) {
+    bool over = false;
+    uint64_t const v = gb::binomial(n, k, &over);
+    if (overflow) *overflow = over ? 1 : 0;
+    return v;
+}
+GB_API void gb_combinations_seek(unsigned n, unsigned k, uint64_t pos, int* idx) { gb::combination_unrank(n, k, pos, idx); }
+GB_API int gb_combinations_next(unsigned n, unsigned k, int* idx) { return gb::combination_next(n, k, idx) ? 1 : 0; }
+
+// Test hook: marks every index of [0, total) once per covering chunk; returns the number of chunks.
+GB_API int gb_cpu_parallel_for_probe(int64_t total, int64_t grain, int32_t* hits) {
+    std::atomic<int> chunks{0};
+    gb::parallel_for(0, static_cast<std::size_t>(total), [&](std::size_t lo, std::size_t hi) {
+        chunks.fetch_add(1);
+        for (std::size_t i = lo; i < hi; ++i) __atomic_fetch_add(&hits[i], 1, __ATOMIC_RELAXED);
+    }, static_cast<std::size_t>(grain));
+    return chunks.load();
+}
+
+}  // extern "C"
