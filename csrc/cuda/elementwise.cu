@@ -1,0 +1,207 @@
+// Flat-arena elementwise kernels: optimizers (torch.optim semantics on one d-length vector),
+// Byzantine attack generation, and small utilities (scale / axpy / sum of squares).
+//
+// Counterparts in the reference are ATen ops executed on the HOST by the parameter server:
+//   optimizer step   /root/reference/pytorch_impl/libs/garfieldpp/server.py:277-287 (+ tools.py:107-123)
+//   attacks          /root/reference/pytorch_impl/libs/garfieldpp/byzWorker.py:78-143, byzServer.py:86-107
+// Here they run on the flat device arenas with 128-bit accesses; the SGD step additionally
+// exists fused into the aggregation epilogue (gar_coordwise.cu).
+
+#include <cmath>
+
+#include "gar_common.cuh"
+#include "garfield_b200.h"
+#include "launch.cuh"
+
+namespace gb {
+namespace {
+
+constexpr int kEwThreads = 256;
+
+inline int ew_grid(long long work_items) {
+    long long blocks = (work_items + kEwThreads - 1) / kEwThreads;
+    long long const cap = static_cast<long long>(device_sm_count()) * 8;
+    if (blocks > cap) blocks = cap;
+    if (blocks < 1) blocks = 1;
+    return static_cast<int>(blocks);
+}
+
+// Generic grid-stride map over d elements, 4 at a time when the base pointers allow it.
+template <class F>
+__global__ void __launch_bounds__(kEwThreads) map_kernel(long long d, F f) {
+    long long const stride = static_cast<long long>(gridDim.x) * blockDim.x;
+    for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < d; i += stride) f(i);
+}
+
+template <class F>
+int launch_map(long long d, cudaStream_t stream, F f, char const* what) {
+    map_kernel<<<ew_grid(d), kEwThreads, 0, stream>>>(d, f);
+    return cuda_check(cudaGetLastError(), what);
+}
+
+struct Mirrors {
+    float* p[kMaxMirrors];
+    int n;
+};
+
+}  // namespace
+}  // namespace gb
+
+using namespace gb;
+
+extern "C" {
+
+// ---------------------------------------------------------------------------- optimizers ---
+
+GB_API int gb_sgd_step(float* param, float const* grad, float* mom, int64_t d, float lr, float momentum, float dampening,
+                       float weight_decay, int nesterov, int first_step, float* const* mirrors, int n_mirrors, void* stream) {
+    if (n_mirrors < 0 || n_mirrors > kMaxMirrors) return cuda_fail("sgd: too many mirrors");
+    if (momentum != 0.0f && mom == nullptr) return cuda_fail("sgd: momentum buffer missing");
+    Mirrors mir{};
+    mir.n = n_mirrors;
+    for (int k = 0; k < n_mirrors; ++k) mir.p[k] = mirrors[k];
+    return launch_map(d, static_cast<cudaStream_t>(stream), [=] __device__(long long i) {
+        float p = param[i];
+        float g = fmaf(weight_decay, p, grad[i]);
+        if (momentum != 0.0f) {
+            float const buf = first_step ? g : fmaf(momentum, mom[i], (1.0f - dampening) * g);
+            mom[i] = buf;
+            g = nesterov ? fmaf(momentum, buf, g) : buf;
+        }
+        p = fmaf(-lr, g, p);
+        param[i] = p;
+        for (int k = 0; k < mir.n; ++k) mir.p[k][i] = p;
+    }, "sgd step");
+}
+
+GB_API int gb_adam_step(float* param, float const* grad, float* exp_avg, float* exp_avg_sq, int64_t d, float lr, float beta1, float beta2,
+                        float eps, float weight_decay, int step, int decoupled, void* stream) {
+    float const bc1 = 1.0f - powf(beta1, static_cast<float>(step));
+    float const bc2_sqrt = sqrtf(1.0f - powf(beta2, static_cast<float>(step)));
+    float const step_size = lr / bc1;
+    return launch_map(d, static_cast<cudaStream_t>(stream), [=] __device__(long long i) {
+        float p = param[i];
+        float g = grad[i];
+        if (decoupled) p *= 1.0f - lr * weight_decay;
+        else g = fmaf(weight_decay, p, g);
+        float const m = fmaf(beta1, exp_avg[i], (1.0f - beta1) * g);
+        float const v = fmaf(beta2, exp_avg_sq[i], (1.0f - beta2) * g * g);
+        exp_avg[i] = m;
+        exp_avg_sq[i] = v;
+        float const denom = sqrtf(v) / bc2_sqrt + eps;
+        param[i] = p - step_size * (m / denom);
+    }, "adam step");
+}
+
+GB_API int gb_rmsprop_step(float* param, float const* grad, float* square_avg, float* mom, int64_t d, float lr, float alpha, float eps,
+                           float weight_decay, float momentum, void* stream) {
+    if (momentum != 0.0f && mom == nullptr) return cuda_fail("rmsprop: momentum buffer missing");
+    return launch_map(d, static_cast<cudaStream_t>(stream), [=] __device__(long long i) {
+        float p = param[i];
+        float const g = fmaf(weight_decay, p, grad[i]);
+        float const sq = fmaf(alpha, square_avg[i], (1.0f - alpha) * g * g);
+        square_avg[i] = sq;
+        float const avg = sqrtf(sq) + eps;
+        if (momentum != 0.0f) {
+            float const buf = fmaf(momentum, mom[i], g / avg);
+            mom[i] = buf;
+            p -= lr * buf;
+        } else {
+            p -= lr * (g / avg);
+        }
+        param[i] = p;
+    }, "rmsprop step");
+}
+
+GB_API int gb_adagrad_step(float* param, float const* grad, float* state_sum, int64_t d, float lr, float lr_decay, float eps,
+                           float weight_decay, int step, void* stream) {
+    float const clr = lr / (1.0f + static_cast<float>(step - 1) * lr_decay);
+    return launch_map(d, static_cast<cudaStream_t>(stream), [=] __device__(long long i) {
+        float const p = param[i];
+        float const g = fmaf(weight_decay, p, grad[i]);
+        float const s = fmaf(g, g, state_sum[i]);
+        state_sum[i] = s;
+        param[i] = p - clr * (g / (sqrtf(s) + eps));
+    }, "adagrad step");
+}
+
+// ------------------------------------------------------------------------------- attacks ---
+
+// out[i] ~ U[0,1)   (ref: byzWorker.py:78-85 torch.rand)
+GB_API int gb_attack_random(float* out, int64_t d, uint64_t seed, void* stream) {
+    long long const quads = (d + 3) / 4;
+    return launch_map(quads, static_cast<cudaStream_t>(stream), [=] __device__(long long q) {
+        uint4 const r = philox4x32(seed, static_cast<unsigned long long>(q), 1u);
+        uint32_t const bits[4] = {r.x, r.y, r.z, r.w};
+        for (int k = 0; k < 4; ++k) {
+            long long const i = q * 4 + k;
+            if (i < d) out[i] = u01(bits[k]);
+        }
+    }, "attack random");
+}
+
+// out = factor * in   (reverse attack: factor = -100; ref: byzWorker.py:87-94)
+GB_API int gb_scale(float const* in, float* out, int64_t d, float factor, void* stream) {
+    return launch_map(d, static_cast<cudaStream_t>(stream), [=] __device__(long long i) { out[i] = factor * in[i]; }, "scale");
+}
+
+// out = in with each coordinate zeroed with probability p   (intended drop attack; ref: byzWorker.py:96-106, Q5)
+GB_API int gb_attack_drop(float const* in, float* out, int64_t d, float p, uint64_t seed, void* stream) {
+    long long const quads = (d + 3) / 4;
+    return launch_map(quads, static_cast<cudaStream_t>(stream), [=] __device__(long long q) {
+        uint4 const r = philox4x32(seed, static_cast<unsigned long long>(q), 2u);
+        uint32_t const bits[4] = {r.x, r.y, r.z, r.w};
+        for (int k = 0; k < 4; ++k) {
+            long long const i = q * 4 + k;
+            if (i < d) out[i] = (u01(bits[k]) < p) ? 0.0f : in[i];
+        }
+    }, "attack drop");
+}
+
+// Colluding attacks over the fw "honest" estimates in rows[0..fw):
+//   kind 0 "lie":    out = μ + z·σ   (σ unbiased; 0 when fw == 1 unless nan_single)   ref: byzWorker.py:108-125
+//   kind 1 "empire": out = −eps·μ                                                    ref: byzWorker.py:127-143
+GB_API int gb_attack_collude(float const* const* rows, int fw, int64_t d, int kind, float coeff, int nan_single, float* out, void* stream) {
+    if (fw < 1 || fw > kMaxRows) return cuda_fail("attack: need 1 <= fw <= 64 estimate rows");
+    RowTable table{};
+    for (int i = 0; i < fw; ++i) table.p[i] = rows[i];
+    return launch_map(d, static_cast<cudaStream_t>(stream), [=] __device__(long long i) {
+        float mean = 0.0f;
+        for (int r = 0; r < fw; ++r) mean += table.p[r][i];
+        mean /= static_cast<float>(fw);
+        if (kind == 1) {
+            out[i] = -coeff * mean;
+            return;
+        }
+        float var = 0.0f;
+        for (int r = 0; r < fw; ++r) {
+            float const dv = table.p[r][i] - mean;
+            var = fmaf(dv, dv, var);
+        }
+        float sigma;
+        if (fw > 1) sigma = sqrtf(var / static_cast<float>(fw - 1));
+        else sigma = nan_single ? NAN : 0.0f;
+        out[i] = fmaf(coeff, sigma, mean);
+    }, "attack collude");
+}
+
+// ------------------------------------------------------------------------------ utilities ---
+
+// y = a·x + b·y
+GB_API int gb_axpby(float const* x, float* y, int64_t d, float a, float b, void* stream) {
+    return launch_map(d, static_cast<cudaStream_t>(stream), [=] __device__(long long i) { y[i] = fmaf(a, x[i], b * y[i]); }, "axpby");
+}
+
+// Copy one source vector into up to 8 destinations (model publication to peer arenas).
+GB_API int gb_broadcast_copy(float const* src, float* const* dsts, int n_dst, int64_t d, void* stream) {
+    if (n_dst < 1 || n_dst > kMaxMirrors) return cuda_fail("broadcast_copy: need 1..8 destinations");
+    Mirrors mir{};
+    mir.n = n_dst;
+    for (int k = 0; k < n_dst; ++k) mir.p[k] = dsts[k];
+    return launch_map(d, static_cast<cudaStream_t>(stream), [=] __device__(long long i) {
+        float const v = src[i];
+        for (int k = 0; k < mir.n; ++k) mir.p[k][i] = v;
+    }, "broadcast copy");
+}
+
+}  // extern "C"

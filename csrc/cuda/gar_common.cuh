@@ -1,0 +1,202 @@
+// Shared declarations of the aggregation kernels: row tables, rule ids, the TMA-bulk tile
+// ring used by every streaming kernel, register sorting networks and a counter-based RNG.
+#pragma once
+
+#include <cstdint>
+#include <cuda_runtime.h>
+
+#include "ptx.cuh"
+
+namespace gb {
+
+constexpr int kMaxRows = 64;          // max number of gradients per aggregation call
+constexpr int kMaxMirrors = 8;        // max peer copies written by the fused update epilogue
+constexpr int kConsumerWarps = 8;
+constexpr int kThreads = 32 * (1 + kConsumerWarps);  // warp 0 = TMA producer
+constexpr int kStages = 3;
+
+// n row pointers, passed by value in the kernel parameter space. Rows may live in the memory
+// of another GPU (peer-mapped): the kernels only ever read them.
+struct RowTable {
+    const float* p[kMaxRows];
+};
+
+// Per-coordinate rules (the reference's K8/K9/K10 kernels plus the TF-only and new ones).
+enum CoordRule : int {
+    kRuleLinear = 0,             // out = Σ_i W[0][i]·x_i                (selection_average, K3)
+    kRuleMedianLower = 1,        // torch.median semantics, NaN-propagating
+    kRuleMedianFiniteUpper = 2,  // ⌊c/2⌋-th of the c finite values, 0 if none  (K10)
+    kRuleTrimmedMean = 3,        // mean of sorted ranks [f, n-f)
+    kRuleAveragedMedian = 4,     // mean of the β values closest to the (lower|upper) median (K8)
+    kRuleCondense = 5,           // Bernoulli(p) ? lower median : x_0
+};
+
+// Optional optimizer step fused into the aggregation epilogue (torch.optim.SGD semantics),
+// followed by stores of the updated parameter into up to kMaxMirrors peer arenas.
+struct FusedUpdate {
+    int mode;  // 0 = none, 1 = SGD(momentum, dampening, weight_decay, nesterov)
+    int nesterov;
+    int first_step;  // momentum buffer is initialised with the gradient on the first step
+    int n_mirrors;
+    float lr, momentum, dampening, weight_decay;
+    float* param;
+    float* mom;
+    float* mirror[kMaxMirrors];
+};
+
+struct CoordArgs {
+    RowTable rows;
+    int n;            // number of input rows
+    int rule;         // CoordRule
+    int rank;         // f (trimmed mean) | β (averaged median)
+    int upper;        // averaged median: use the upper median
+    int theta;        // > 0: values fed to the rule are y = W·x  (W is theta × n, row-major)
+    int tile;         // coordinates per ring stage
+    int use_tma;      // 0: rows are not 16-byte aligned → direct global loads only
+    float p;          // condense probability
+    unsigned long long seed;
+    long long d;
+    const float* W;
+    float* out;       // may be null when a fused update consumes the result
+    FusedUpdate upd;
+};
+
+enum SelectMode : int {
+    kSelectNone = 0,          // distances only
+    kSelectKrum = 1,          // m best scores; score = Σ `neighbors` smallest (sqrt if !squared)
+    kSelectBulyanPython = 2,  // static-score rounds (reference python semantics)
+    kSelectBulyanNative = 3,  // pruned-distance score updates (reference native semantics)
+    kSelectMda = 4,           // minimum-diameter subset of size n-f
+    kSelectClosest = 5,       // the m rows (of the first n-1) closest to the LAST row (aksel)
+};
+
+struct SelectArgs {
+    int mode, f, m, neighbors, squared;
+};
+
+struct PairwiseArgs {
+    RowTable rows;
+    int n;
+    int tile;
+    int use_tma;
+    long long d;
+    float* partials;        // scratch: gridDim.x × n × n floats
+    unsigned int* counter;  // scratch: 1 word, must be 0 at launch (reset by the kernel)
+    float* dist;            // out: n × n squared distances (+inf diagonal / non-finite)
+    float* W;               // out: theta × n averaging weights (theta = 1 unless Bulyan)
+    int* info;              // out: [0] = number of selection rounds, [1..] selected ids of round 0
+    SelectArgs sel;
+};
+
+// ------------------------------------------------------------------- sorting networks ---
+
+// Bitonic network on a register array (fully unrolled; NP a power of two). NaNs must have
+// been replaced beforehand (fminf/fmaxf drop them).
+template <int NP>
+__device__ __forceinline__ void sort_regs(float (&v)[NP]) {
+#pragma unroll
+    for (int k = 2; k <= NP; k <<= 1) {
+#pragma unroll
+        for (int j = k >> 1; j > 0; j >>= 1) {
+#pragma unroll
+            for (int i = 0; i < NP; ++i) {
+                int const l = i ^ j;
+                if (l > i) {
+                    bool const up = (i & k) == 0;
+                    float const lo = fminf(v[i], v[l]), hi = fmaxf(v[i], v[l]);
+                    v[i] = up ? lo : hi;
+                    v[l] = up ? hi : lo;
+                }
+            }
+        }
+    }
+}
+
+// Same network ordering (key, value) pairs by key.
+template <int NP>
+__device__ __forceinline__ void sort_pairs(float (&key)[NP], float (&val)[NP]) {
+#pragma unroll
+    for (int k = 2; k <= NP; k <<= 1) {
+#pragma unroll
+        for (int j = k >> 1; j > 0; j >>= 1) {
+#pragma unroll
+            for (int i = 0; i < NP; ++i) {
+                int const l = i ^ j;
+                if (l > i) {
+                    bool const up = (i & k) == 0;
+                    bool const swap = up ? (key[i] > key[l]) : (key[i] < key[l]);
+                    float const ki = key[i], kl = key[l], vi = val[i], vl = val[l];
+                    key[i] = swap ? kl : ki;
+                    key[l] = swap ? ki : kl;
+                    val[i] = swap ? vl : vi;
+                    val[l] = swap ? vi : vl;
+                }
+            }
+        }
+    }
+}
+
+// ------------------------------------------------------------------------ Philox RNG ---
+
+// Philox4x32-10 keyed by `seed`, counter = (index, stream). Returns 4 uniform uint32.
+__device__ __forceinline__ uint4 philox4x32(unsigned long long seed, unsigned long long index, unsigned int stream) {
+    uint32_t k0 = static_cast<uint32_t>(seed), k1 = static_cast<uint32_t>(seed >> 32);
+    uint32_t c0 = static_cast<uint32_t>(index), c1 = static_cast<uint32_t>(index >> 32), c2 = stream, c3 = 0x9E3779B9u;
+#pragma unroll
+    for (int round = 0; round < 10; ++round) {
+        uint32_t const hi0 = __umulhi(0xD2511F53u, c0), lo0 = 0xD2511F53u * c0;
+        uint32_t const hi1 = __umulhi(0xCD9E8D57u, c2), lo1 = 0xCD9E8D57u * c2;
+        uint32_t const n0 = hi1 ^ c1 ^ k0, n1 = lo1, n2 = hi0 ^ c3 ^ k1, n3 = lo0;
+        c0 = n0; c1 = n1; c2 = n2; c3 = n3;
+        k0 += 0x9E3779B9u;
+        k1 += 0xBB67AE85u;
+    }
+    return make_uint4(c0, c1, c2, c3);
+}
+
+__device__ __forceinline__ float u01(uint32_t bits) {  // [0, 1)
+    return static_cast<float>(bits >> 8) * (1.0f / 16777216.0f);
+}
+
+// ---------------------------------------------------------------------- tile ring ---
+
+// Shared-memory ring of `kStages` tiles, each n rows × `tile` floats, filled by one elected
+// producer lane with cp.async.bulk (TMA 1-D) and drained by kConsumerWarps warps.
+struct TileRing {
+    uint64_t full[kStages];
+    uint64_t empty[kStages];
+};
+
+__device__ __forceinline__ void ring_init(TileRing& ring) {
+    if (threadIdx.x == 0) {
+#pragma unroll
+        for (int s = 0; s < kStages; ++s) {
+            ptx::mbar_init(&ring.full[s], 1);
+            ptx::mbar_init(&ring.empty[s], kConsumerWarps);
+        }
+        ptx::fence_mbar_init();
+    }
+    __syncthreads();
+}
+
+// Producer side: one lane streams this CTA's full tiles. `want(i)` tells whether row i is needed.
+template <class Want>
+__device__ __forceinline__ void ring_produce(TileRing& ring, float* stage_base, RowTable const& rows, int n, int tile, long long full_tiles,
+                                             Want want) {
+    size_t const stage_floats = static_cast<size_t>(n) * tile;
+    uint32_t const row_bytes = static_cast<uint32_t>(tile) * 4u;
+    int needed = 0;
+    for (int i = 0; i < n; ++i) needed += want(i) ? 1 : 0;
+    long long it = 0;
+    for (long long t = blockIdx.x; t < full_tiles; t += gridDim.x, ++it) {
+        int const s = static_cast<int>(it % kStages);
+        uint32_t const phase = static_cast<uint32_t>((it / kStages) & 1);
+        ptx::mbar_wait(&ring.empty[s], phase ^ 1u);
+        ptx::mbar_arrive_expect_tx(&ring.full[s], row_bytes * static_cast<uint32_t>(needed));
+        float* dst = stage_base + s * stage_floats;
+        for (int i = 0; i < n; ++i)
+            if (want(i)) ptx::bulk_g2s(dst + static_cast<size_t>(i) * tile, rows.p[i] + t * tile, row_bytes, &ring.full[s]);
+    }
+}
+
+}  // namespace gb

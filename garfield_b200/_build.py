@@ -65,8 +65,9 @@ def _headers():
 def _stamp(paths, flags):
     h = hashlib.sha1()
     for p in sorted(map(str, paths)):
-        h.update(p.encode())
-        h.update(str(os.stat(p).st_mtime_ns).encode())
+        h.update(os.path.basename(p).encode())
+        with open(p, "rb") as fh:  # content hash: survives copies that reset mtimes (gpurun snapshots)
+            h.update(fh.read())
     h.update(" ".join(flags).encode())
     return h.hexdigest()
 
@@ -129,7 +130,7 @@ def build_cuda(force=False):
         raise RuntimeError("nvcc not found; cannot build the sm_100a library")
     sources = sorted((CSRC / "cuda").glob("*.cu"))
     opt = ["-O0", "-g", "-G"] if _debug() else ["-O3", "-DNDEBUG"]
-    cflags = ARCH_FLAGS + ["-std=c++17", "-lineinfo", "--expt-relaxed-constexpr", "-Xcompiler", "-fPIC,-fvisibility=hidden",
+    cflags = ARCH_FLAGS + ["-std=c++17", "-lineinfo", "--expt-relaxed-constexpr", "--extended-lambda", "-Xcompiler", "-fPIC,-fvisibility=hidden",
                            "-Xptxas", "-v" if os.environ.get("GARFIELD_PTXAS_V") else "-O3"] + opt
     ldflags = ARCH_FLAGS + ["-shared", "-Xcompiler", "-fPIC", "-cudart", "shared"]
     if force:

@@ -1,0 +1,103 @@
+"""ctypes binding of libgarfield_b200_cuda.so (declared in include/garfield_b200.h).
+
+The library is loaded once per process. On a machine with a CUDA device a missing/unloadable
+library is a hard error (`require()`), never a silent PyTorch fallback.
+"""
+
+from __future__ import annotations
+
+import ctypes
+
+import torch
+
+from .. import _build
+
+_handle = None
+_error = None
+
+vp, i32, i64, u64, f32 = ctypes.c_void_p, ctypes.c_int, ctypes.c_int64, ctypes.c_uint64, ctypes.c_float
+pp = ctypes.POINTER(ctypes.c_void_p)
+
+
+class FusedUpdate(ctypes.Structure):
+    """Mirror of `gb_fused_update`."""
+    _fields_ = [("mode", i32), ("nesterov", i32), ("first_step", i32), ("n_mirrors", i32),
+                ("lr", f32), ("momentum", f32), ("dampening", f32), ("weight_decay", f32),
+                ("param", vp), ("mom", vp), ("mirror", vp * 8)]
+
+
+def _declare(h):
+    h.gb_cuda_last_error.restype = ctypes.c_char_p
+    h.gb_coordwise.argtypes = [pp, i32, i64, i32, i32, i32, f32, u64, vp, i32, vp, ctypes.POINTER(FusedUpdate), vp]
+    h.gb_pairwise_scratch_bytes.restype = i64
+    h.gb_pairwise_scratch_bytes.argtypes = [i32]
+    h.gb_pairwise_select.argtypes = [pp, i32, i64, i32, i32, i32, i32, i32, vp, i64, vp, vp, vp, vp]
+    h.gb_sgd_step.argtypes = [vp, vp, vp, i64, f32, f32, f32, f32, i32, i32, pp, i32, vp]
+    h.gb_adam_step.argtypes = [vp, vp, vp, vp, i64, f32, f32, f32, f32, f32, i32, i32, vp]
+    h.gb_rmsprop_step.argtypes = [vp, vp, vp, vp, i64, f32, f32, f32, f32, f32, vp]
+    h.gb_adagrad_step.argtypes = [vp, vp, vp, i64, f32, f32, f32, f32, i32, vp]
+    h.gb_attack_random.argtypes = [vp, i64, u64, vp]
+    h.gb_scale.argtypes = [vp, vp, i64, f32, vp]
+    h.gb_attack_drop.argtypes = [vp, vp, i64, f32, u64, vp]
+    h.gb_attack_collude.argtypes = [pp, i32, i64, i32, f32, i32, vp, vp]
+    h.gb_axpby.argtypes = [vp, vp, i64, f32, f32, vp]
+    h.gb_broadcast_copy.argtypes = [vp, pp, i32, i64, vp]
+    h.gb_ipc_handle_size.restype = i32
+    h.gb_arena_alloc.argtypes = [i64, pp]
+    h.gb_arena_free.argtypes = [vp]
+    h.gb_ipc_export.argtypes = [vp, vp]
+    h.gb_ipc_open.argtypes = [vp, pp]
+    h.gb_ipc_close.argtypes = [vp]
+    h.gb_enable_peer.argtypes = [i32]
+    for name in ("gb_gemm_bf16", "gb_gemm_workspace_bytes"):
+        if hasattr(h, name):
+            pass
+
+
+def load():
+    """Return the ctypes handle, or None when the library cannot be loaded (error kept)."""
+    global _handle, _error
+    if _handle is None and _error is None:
+        try:
+            h = _build.load_cuda()
+            _declare(h)
+            _handle = h
+        except Exception as err:
+            _error = err
+    return _handle
+
+
+def available():
+    """True when a CUDA device is present AND the sm_100a library is loaded."""
+    if not torch.cuda.is_available():
+        return False
+    if load() is None:
+        raise RuntimeError("CUDA device present but libgarfield_b200_cuda.so failed to load: %r" % (_error,))
+    return True
+
+
+def require():
+    h = load()
+    if h is None:
+        raise RuntimeError("libgarfield_b200_cuda.so unavailable: %r" % (_error,))
+    return h
+
+
+def check(rc):
+    if rc != 0:
+        raise RuntimeError(require().gb_cuda_last_error().decode())
+
+
+def stream_ptr(device=None):
+    return ctypes.c_void_p(torch.cuda.current_stream(device).cuda_stream)
+
+
+def row_table(tensors):
+    return (ctypes.c_void_p * len(tensors))(*[t.data_ptr() for t in tensors])
+
+
+launches = [0]  # number of kernels of this library launched by this process (bench accounting)
+
+
+def count(n=1):
+    launches[0] += n

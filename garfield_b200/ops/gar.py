@@ -1,0 +1,174 @@
+"""Device aggregation rules: thin Python drivers around the sm_100a kernels.
+
+Every rule is at most two launches and never synchronises with the host:
+
+    pairwise_select  one TMA-streamed pass → n×n distances → in-kernel selection → W (θ×n)
+    coordwise        one TMA-streamed pass → per-coordinate rule on x or on W·x
+                     (+ optional fused SGD update and publication to peer arenas)
+
+Inputs are lists of n 1-D float32 CUDA tensors (any mix of local and peer-mapped memory).
+Reference counterparts: /root/reference/pytorch_impl/libs/native/py_*/ *.cu (see the kernel
+files for line-level citations).
+"""
+
+from __future__ import annotations
+
+import ctypes
+
+import torch
+
+from . import _lib
+from ._lib import FusedUpdate
+
+__all__ = ["available", "pairwise_sqdist", "select", "coordwise", "krum", "bulyan", "mda", "aksel",
+           "average", "weighted", "SgdFusion", "MAX_ROWS"]
+
+MAX_ROWS = 64
+
+RULES = {"linear": 0, "median_lower": 1, "median_finite_upper": 2, "trimmed_mean": 3,
+         "averaged_median": 4, "condense": 5}
+MODES = {"none": 0, "krum": 1, "bulyan_python": 2, "bulyan_native": 3, "mda": 4, "closest": 5}
+
+
+def available():
+    return _lib.available()
+
+
+class _Workspace:
+    """Per-device cached scratch (partials + counter), distance / weight / info buffers."""
+    _cache = {}
+
+    @classmethod
+    def get(cls, device, n):
+        key = (device.index if device.index is not None else torch.cuda.current_device(), n)
+        ws = cls._cache.get(key)
+        if ws is None:
+            lib = _lib.require()
+            with torch.cuda.device(device):
+                nbytes = int(lib.gb_pairwise_scratch_bytes(n))
+            ws = dict(
+                scratch=torch.zeros(nbytes, dtype=torch.uint8, device=device),
+                dist=torch.empty(n, n, dtype=torch.float32, device=device),
+                W=torch.zeros(n, n, dtype=torch.float32, device=device),
+                info=torch.zeros(1 + n, dtype=torch.int32, device=device),
+            )
+            cls._cache[key] = ws
+        return ws
+
+
+def _prep(gradients):
+    n = len(gradients)
+    if n < 1 or n > MAX_ROWS:
+        raise ValueError("device rules support 1..%d gradients, got %d" % (MAX_ROWS, n))
+    g0 = gradients[0]
+    rows = []
+    for g in gradients:
+        if g.dtype != torch.float32 or not g.is_cuda or g.dim() != 1 or g.shape != g0.shape:
+            raise ValueError("expected 1-D float32 CUDA tensors of equal length")
+        rows.append(g if g.is_contiguous() else g.contiguous())
+    return rows, n, g0.numel(), g0.device
+
+
+class SgdFusion:
+    """Description of an SGD step (torch.optim.SGD semantics) to fuse into the aggregation
+    epilogue: `param`/`mom` are flat fp32 arenas of length d, `mirrors` are further arenas
+    (typically peer-mapped) that receive the updated parameters."""
+
+    def __init__(self, param, mom, lr, momentum=0.0, dampening=0.0, weight_decay=0.0, nesterov=False,
+                 first_step=False, mirrors=()):
+        self.param, self.mom, self.lr, self.momentum = param, mom, lr, momentum
+        self.dampening, self.weight_decay, self.nesterov = dampening, weight_decay, nesterov
+        self.first_step, self.mirrors = first_step, tuple(mirrors)
+
+    def struct(self):
+        u = FusedUpdate()
+        u.mode, u.nesterov, u.first_step, u.n_mirrors = 1, int(self.nesterov), int(self.first_step), len(self.mirrors)
+        u.lr, u.momentum, u.dampening, u.weight_decay = self.lr, self.momentum, self.dampening, self.weight_decay
+        u.param = self.param.data_ptr()
+        u.mom = self.mom.data_ptr() if self.mom is not None else None
+        for k, t in enumerate(self.mirrors):
+            u.mirror[k] = t.data_ptr() if isinstance(t, torch.Tensor) else int(t)
+        return u
+
+
+def coordwise(gradients, rule, f=0, beta=0, upper=False, p=0.9, seed=0, W=None, theta=0, out=None, update=None,
+              want_out=True):
+    """Run one per-coordinate rule. Returns the aggregated vector (None if only updating)."""
+    rows, n, d, device = _prep(gradients)
+    lib = _lib.require()
+    code = RULES[rule]
+    rank = f if rule == "trimmed_mean" else beta
+    if out is None and want_out:
+        out = torch.empty(d, dtype=torch.float32, device=device)
+    upd = update.struct() if update is not None else None
+    with torch.cuda.device(device):
+        _lib.check(lib.gb_coordwise(
+            _lib.row_table(rows), n, d, code, int(rank), int(bool(upper)), float(p), int(seed) & 0xFFFFFFFFFFFFFFFF,
+            W.data_ptr() if W is not None else None, int(theta),
+            out.data_ptr() if out is not None else None,
+            ctypes.byref(upd) if upd is not None else None, _lib.stream_ptr(device)))
+    _lib.count()
+    return out
+
+
+def select(gradients, mode, f=0, m=0, neighbors=0, squared=True):
+    """Distances + selection in one launch. Returns the device workspace dict with
+    `dist` (n×n), `W` (n×n buffer, first θ rows valid) and `info`."""
+    rows, n, d, device = _prep(gradients)
+    lib = _lib.require()
+    ws = _Workspace.get(device, n)
+    with torch.cuda.device(device):
+        _lib.check(lib.gb_pairwise_select(
+            _lib.row_table(rows), n, d, MODES[mode], int(f), int(m), int(neighbors), int(bool(squared)),
+            ws["scratch"].data_ptr(), ws["scratch"].numel(), ws["dist"].data_ptr(), ws["W"].data_ptr(),
+            ws["info"].data_ptr(), _lib.stream_ptr(device)))
+    _lib.count()
+    return ws
+
+
+def pairwise_sqdist(gradients):
+    """n×n matrix of squared L2 distances (device tensor; +inf diagonal and non-finite)."""
+    return select(gradients, "none")["dist"].clone()
+
+
+def weighted(gradients, W, theta=1, **kw):
+    """out = W[0]·rows (θ = 1) — the selection-average pass."""
+    return coordwise(gradients, "linear", W=W, theta=theta, **kw)
+
+
+def krum(gradients, f, m, neighbors, squared, update=None, want_out=True):
+    ws = select(gradients, "krum", f=f, m=m, neighbors=neighbors, squared=squared)
+    return coordwise(gradients, "linear", W=ws["W"], theta=1, update=update, want_out=want_out)
+
+
+def bulyan(gradients, f, m=None, native=False, update=None, want_out=True):
+    n = len(gradients)
+    m = n - f - 2 if m is None else m
+    theta = n - 2 * f - 2
+    ws = select(gradients, "bulyan_native" if native else "bulyan_python", f=f, m=m, squared=native)
+    return coordwise(gradients, "averaged_median", beta=theta - 2 * f, upper=native, W=ws["W"], theta=theta,
+                     update=update, want_out=want_out)
+
+
+def mda(gradients, f, squared=False, update=None, want_out=True):
+    ws = select(gradients, "mda", f=f, squared=squared)
+    return coordwise(gradients, "linear", W=ws["W"], theta=1, update=update, want_out=want_out)
+
+
+def aksel(gradients, c, update=None, want_out=True):
+    med = coordwise(gradients, "median_lower")
+    ws = select(list(gradients) + [med], "closest", m=c, squared=True)
+    # W has n+1 columns (last = the median row, weight 0): reuse it on the extended row list
+    return coordwise(list(gradients) + [med], "linear", W=ws["W"], theta=1, update=update, want_out=want_out)
+
+
+_uniform = {}
+
+
+def average(gradients, update=None, want_out=True):
+    n = len(gradients)
+    device = gradients[0].device
+    key = (device, n)
+    if key not in _uniform:
+        _uniform[key] = torch.full((1, n), 1.0 / n, dtype=torch.float32, device=device)
+    return coordwise(gradients, "linear", W=_uniform[key], theta=1, update=update, want_out=want_out)

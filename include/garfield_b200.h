@@ -66,6 +66,80 @@ GB_API void gb_mreg_destroy(void* handle);
 GB_API int gb_mreg_write(void* handle, void const* src, int64_t timeout_ns);
 GB_API int gb_mreg_read(void* handle, void* dst, uint64_t* seq, int64_t timeout_ns);
 
+
+/* ---------------------------------------------------------------- sm_100a library --- */
+/* All device entry points take raw device pointers and a cudaStream_t (as void*); they launch
+ * asynchronously on that stream and never synchronise or allocate unless stated. */
+
+GB_API char const* gb_cuda_last_error(void);
+GB_API int gb_cuda_device_count(void);
+GB_API int gb_cuda_sm_count(void);
+
+/* Peer-memory arena over CUDA IPC (replaces the reference's RPC transport of CPU tensors,
+ * ref: /root/reference/pytorch_impl/libs/garfieldpp/server.py:112-184; allocation replaces
+ * include/cudarray.cu.hpp:43-190 per-call cudaMalloc). */
+GB_API int gb_ipc_handle_size(void);
+GB_API int gb_arena_alloc(int64_t bytes, void** ptr);
+GB_API int gb_arena_free(void* ptr);
+GB_API int gb_ipc_export(void* ptr, void* handle_out);
+GB_API int gb_ipc_open(void const* handle, void** ptr);
+GB_API int gb_ipc_close(void* ptr);
+GB_API int gb_enable_peer(int peer);
+
+/* Optional optimizer step fused into an aggregation epilogue (torch.optim.SGD semantics,
+ * ref: garfieldpp/server.py:277-287 update_model + optimizer.step) and publication of the
+ * updated parameters into up to 8 peer arenas (ref: server.py:127 model shipping). */
+typedef struct gb_fused_update {
+    int mode;        /* 0 none, 1 SGD */
+    int nesterov;
+    int first_step;  /* 1: momentum buffer := gradient */
+    int n_mirrors;
+    float lr, momentum, dampening, weight_decay;
+    float* param;
+    float* mom;
+    float* mirror[8];
+} gb_fused_update;
+
+/* Per-coordinate rules. rule: 0 linear (needs W 1×n), 1 lower median (NaN-propagating),
+ * 2 upper median of the finite values, 3 f-trimmed mean (rank = f), 4 mean of the `rank`
+ * values closest to the lower/upper median, 5 condense (Bernoulli(p) ? median : row 0).
+ * theta > 0: the rule is applied to the theta mixes y = W·x (W theta×n row-major, device).
+ * ref: include/operations.cu.hpp:57-139, py_median/median.cu:60-83, py_bulyan/bulyan.cu:215-243 */
+GB_API int gb_coordwise(float const* const* rows, int n, int64_t d, int rule, int rank, int upper, float p, uint64_t seed,
+                        float const* W, int theta, float* out, gb_fused_update const* upd, void* stream);
+
+/* One pass over the rows → n×n squared distances (+inf diagonal, non-finite → +inf) and, in the
+ * same kernel, the selection logic. mode: 0 none, 1 Krum(f, m, neighbors, squared), 2 Bulyan
+ * python semantics, 3 Bulyan native semantics, 4 MDA (squared=1: native non-finite policy),
+ * 5 the m rows closest to the LAST row (Aksel). Outputs (device): dist[n*n], W[theta*n]
+ * (theta = n-2f-2 for Bulyan else 1), info[1+n] (info[0] = theta, then round-0 selected ids).
+ * `scratch` is caller-provided device memory of at least gb_pairwise_scratch_bytes(n) bytes
+ * whose first word must be zero before the first use (the kernel leaves it zero).
+ * ref: py_krum/krum.cu:68-158, py_bulyan/bulyan.cu:67-207,256-322, py_brute/brute.cu:64-154 */
+GB_API int64_t gb_pairwise_scratch_bytes(int n);
+GB_API int gb_pairwise_select(float const* const* rows, int n, int64_t d, int mode, int f, int m, int neighbors, int squared,
+                              void* scratch, int64_t scratch_bytes, float* dist, float* W, int* info, void* stream);
+
+/* Flat-arena optimizer steps (torch.optim semantics). ref: garfieldpp/server.py:277-287,
+ * garfieldpp/tools.py:107-123 (sgd, adam, adamw, rmsprop, adagrad — run on the HOST there). */
+GB_API int gb_sgd_step(float* param, float const* grad, float* mom, int64_t d, float lr, float momentum, float dampening,
+                       float weight_decay, int nesterov, int first_step, float* const* mirrors, int n_mirrors, void* stream);
+GB_API int gb_adam_step(float* param, float const* grad, float* exp_avg, float* exp_avg_sq, int64_t d, float lr, float beta1, float beta2,
+                        float eps, float weight_decay, int step, int decoupled, void* stream);
+GB_API int gb_rmsprop_step(float* param, float const* grad, float* square_avg, float* mom, int64_t d, float lr, float alpha, float eps,
+                           float weight_decay, float momentum, void* stream);
+GB_API int gb_adagrad_step(float* param, float const* grad, float* state_sum, int64_t d, float lr, float lr_decay, float eps,
+                           float weight_decay, int step, void* stream);
+
+/* Byzantine attack generation on device. ref: garfieldpp/byzWorker.py:78-143, byzServer.py:86-107 */
+GB_API int gb_attack_random(float* out, int64_t d, uint64_t seed, void* stream);
+GB_API int gb_scale(float const* in, float* out, int64_t d, float factor, void* stream);
+GB_API int gb_attack_drop(float const* in, float* out, int64_t d, float p, uint64_t seed, void* stream);
+GB_API int gb_attack_collude(float const* const* rows, int fw, int64_t d, int kind, float coeff, int nan_single, float* out, void* stream);
+
+GB_API int gb_axpby(float const* x, float* y, int64_t d, float a, float b, void* stream);
+GB_API int gb_broadcast_copy(float const* src, float* const* dsts, int n_dst, int64_t d, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -1,0 +1,179 @@
+"""sm_100a kernels vs plain PyTorch fp32/fp64 references of the same ops (run with -m gpu)."""
+
+import itertools
+import math
+
+import pytest
+import torch
+
+import aggregators
+from garfield_b200.aggregators import _host
+
+pytestmark = pytest.mark.gpu
+
+
+def cuda_lib():
+    from garfield_b200.ops import gar
+    assert gar.available(), "sm_100a library must be loaded on a GPU box"
+    return gar
+
+
+def make(n, d, seed=0, spread=1.0, device="cuda"):
+    gen = torch.Generator().manual_seed(seed)
+    base = torch.randn(d, generator=gen)
+    return [(base + spread * torch.randn(d, generator=gen)).to(device) for _ in range(n)]
+
+
+SHAPES = [(3, 1), (5, 7), (8, 1000), (8, 3 * 1024 + 5), (11, 50001), (16, 4096), (23, 9999), (33, 2049), (64, 700)]
+
+
+def test_native_library_is_loaded():
+    import garfield_b200._build as b
+    cuda_lib()
+    with open("/proc/self/maps") as maps:
+        assert "libgarfield_b200_cuda.so" in maps.read()
+
+
+@pytest.mark.parametrize("n,d", SHAPES)
+def test_coordwise_rules(n, d):
+    gar = cuda_lib()
+    g = make(n, d, seed=n * 7 + d)
+    mat = torch.stack(g).cpu()
+    torch.testing.assert_close(gar.coordwise(g, "median_lower").cpu(), _host.median_lower(mat), rtol=0, atol=0)
+    torch.testing.assert_close(gar.coordwise(g, "median_finite_upper").cpu(), _host.median_finite_upper(mat), rtol=0, atol=0)
+    f = (n - 1) // 4
+    torch.testing.assert_close(gar.coordwise(g, "trimmed_mean", f=f).cpu(), _host.trimmed_mean(mat, f), rtol=1e-5, atol=1e-6)
+    beta = max(1, n - f)
+    torch.testing.assert_close(gar.coordwise(g, "averaged_median", beta=beta).cpu(), _host.averaged_median(mat, beta), rtol=1e-5, atol=1e-6)
+    torch.testing.assert_close(gar.coordwise(g, "averaged_median", beta=beta, upper=True).cpu(),
+                               _host.averaged_median(mat, beta, upper=True), rtol=1e-5, atol=1e-6)
+    torch.testing.assert_close(gar.average(g).cpu(), mat.mean(0), rtol=1e-5, atol=1e-6)
+
+
+def test_coordwise_unaligned_rows_and_nonfinite():
+    gar = cuda_lib()
+    n, d = 9, 5000
+    backing = [torch.randn(d + 3, device="cuda") for _ in range(n)]
+    g = [b[1:d + 1] for b in backing]  # 4-byte aligned only → direct-load path
+    mat = torch.stack(g).cpu()
+    torch.testing.assert_close(gar.coordwise(g, "median_lower").cpu(), _host.median_lower(mat), rtol=0, atol=0)
+    bad = [x.clone() for x in make(n, d, seed=5)]
+    bad[0][10] = float("nan"); bad[1][10] = float("inf"); bad[2][11] = -float("inf")
+    for b in bad:
+        b[12] = float("nan")
+    cpu = torch.stack(bad).cpu()
+    got = gar.coordwise(bad, "median_finite_upper").cpu()
+    torch.testing.assert_close(got, _host.median_finite_upper(cpu), rtol=0, atol=0)
+    assert got[12].item() == 0.0
+    low = gar.coordwise(bad, "median_lower").cpu()
+    assert math.isnan(low[10].item()) and math.isnan(low[12].item())
+    ok = torch.ones(d, dtype=torch.bool); ok[10] = ok[12] = False
+    torch.testing.assert_close(low[ok], _host.median_lower(cpu)[ok], rtol=0, atol=0)
+
+
+@pytest.mark.parametrize("n,d", SHAPES[2:])
+def test_pairwise_distances(n, d):
+    gar = cuda_lib()
+    g = make(n, d, seed=d)
+    got = gar.pairwise_sqdist(g).cpu().double()
+    mat = torch.stack(g).cpu().double()
+    want = torch.cdist(mat, mat).pow(2)
+    want.fill_diagonal_(float("inf"))
+    torch.testing.assert_close(got, want, rtol=2e-5, atol=1e-5)
+    again = gar.pairwise_sqdist(g).cpu().double()
+    assert torch.equal(got, again), "distances must be run-to-run deterministic"
+
+
+RULE_CASES = [(7, 1, 3000), (8, 1, 40000), (11, 2, 12345), (15, 3, 5000), (23, 5, 2048), (33, 7, 1500)]
+
+
+@pytest.mark.parametrize("n,f,d", RULE_CASES)
+@pytest.mark.parametrize("name", ["krum", "native-krum", "bulyan", "native-bulyan", "brute", "native-brute", "aksel",
+                                  "average", "median", "native-median", "trimmed_mean", "averaged_median"])
+def test_registry_rules_on_cuda_match_cpu(name, n, f, d):
+    cuda_lib()
+    if name in ("brute", "native-brute") and math.comb(n, f) > 40000:
+        pytest.skip("host oracle too slow")
+    g = make(n, d, seed=n + f + d)
+    cpu = [x.cpu() for x in g]
+    rule = aggregators.gars[name]
+    if rule.check(gradients=cpu, f=f) is not None:
+        pytest.skip("invalid (n, f) for this rule")
+    got = rule(gradients=g, f=f)
+    assert got.is_cuda and got.dtype == torch.float32
+    want = rule(gradients=cpu, f=f)
+    torch.testing.assert_close(got.cpu(), want, rtol=3e-5, atol=3e-6)
+
+
+def test_rules_ignore_byzantine_nonfinite_rows():
+    cuda_lib()
+    honest = make(9, 4000, seed=3, spread=0.05)
+    attack = [torch.full((4000,), float("nan"), device="cuda"), torch.full((4000,), float("inf"), device="cuda")]
+    g = honest + attack
+    cpu = [x.cpu() for x in g]
+    for name in ("krum", "native-krum", "bulyan", "native-bulyan", "brute", "native-median"):
+        got = aggregators.gars[name](gradients=g, f=2)
+        assert torch.isfinite(got).all(), name
+        torch.testing.assert_close(got.cpu(), aggregators.gars[name](gradients=cpu, f=2), rtol=3e-5, atol=3e-6)
+
+
+def test_krum_m_and_condense():
+    gar = cuda_lib()
+    g = make(11, 3000, seed=1)
+    cpu = [x.cpu() for x in g]
+    for m in (1, 3, 7):
+        torch.testing.assert_close(aggregators.krum(gradients=g, f=2, m=m).cpu(), aggregators.krum(gradients=cpu, f=2, m=m), rtol=3e-5, atol=3e-6)
+    out = aggregators.condense(gradients=g, f=2, p=0.9, seed=11).cpu()
+    med = torch.stack(cpu).median(0).values
+    from_med, from_first = out == med, out == cpu[0]
+    assert bool((from_med | from_first).all()) and 0.85 < from_med.float().mean().item() < 0.95
+    assert torch.equal(out, aggregators.condense(gradients=g, f=2, p=0.9, seed=11).cpu())
+
+
+@pytest.mark.parametrize("momentum,nesterov,wd", [(0.0, False, 0.0), (0.9, False, 5e-4), (0.9, True, 1e-3)])
+def test_fused_sgd_epilogue_matches_torch(momentum, nesterov, wd):
+    gar = cuda_lib()
+    from garfield_b200.ops.optim import FlatOptimizer
+    n, f, d = 8, 1, 20000 + 3
+    p0 = torch.randn(d)
+    ref_p = torch.nn.Parameter(p0.clone())
+    ref = torch.optim.SGD([ref_p], lr=0.1, momentum=momentum, nesterov=nesterov, weight_decay=wd)
+    flat = p0.clone().cuda()
+    mirror = torch.zeros(d, device="cuda")
+    opt = FlatOptimizer(flat, "sgd", lr=0.1, momentum=momentum, nesterov=nesterov, weight_decay=wd)
+    for step in range(3):
+        g = make(n, d, seed=100 + step)
+        agg_cpu = aggregators.gars["native-krum"](gradients=[x.cpu() for x in g], f=f)
+        ref_p.grad = agg_cpu.clone()
+        ref.step()
+        out = gar.krum(g, f=f, m=n - f - 2, neighbors=n - f - 2, squared=True, update=opt.sgd_fusion(mirrors=[mirror]))
+        opt.note_fused_step()
+        torch.testing.assert_close(out.cpu(), agg_cpu, rtol=3e-5, atol=3e-6)
+        torch.testing.assert_close(flat.cpu(), ref_p.detach(), rtol=3e-5, atol=3e-6)
+        assert torch.equal(mirror, flat)
+
+
+def test_flat_optimizers_cuda_match_torch():
+    from test_optim_attacks import CONFIGS, run_pair
+    cuda_lib()
+    for name, kwargs in CONFIGS:
+        got, want = run_pair(name, kwargs, "cuda")
+        torch.testing.assert_close(got, want, rtol=3e-5, atol=3e-6, msg=lambda m: "%s %s: %s" % (name, kwargs, m))
+
+
+def test_attacks_cuda():
+    from garfield_b200.ops import attacks
+    cuda_lib()
+    g = torch.randn(100003, device="cuda")
+    r = attacks.random_like(g, seed=1)
+    assert r.min() >= 0 and r.max() < 1 and abs(r.mean().item() - 0.5) < 0.01
+    assert torch.equal(r, attacks.random_like(g, seed=1)) and not torch.equal(r, attacks.random_like(g, seed=2))
+    torch.testing.assert_close(attacks.reverse(g), g * -100)
+    dropped = attacks.drop(g, p=0.3, seed=3)
+    zeroed = dropped == 0
+    assert 0.29 < zeroed.float().mean().item() < 0.31 and torch.equal(dropped[~zeroed], g[~zeroed])
+    est = [torch.randn(100003, device="cuda") for _ in range(4)]
+    stack = torch.stack(est)
+    torch.testing.assert_close(attacks.lie(est), stack.mean(0) + 1.035 * stack.std(0), rtol=1e-5, atol=1e-6)
+    torch.testing.assert_close(attacks.empire(est), -10 * stack.mean(0), rtol=1e-5, atol=1e-6)
+    torch.testing.assert_close(attacks.lie(est[:1]), est[0])
