@@ -70,7 +70,9 @@ GB_API int gb_sgd_step(float* param, float const* grad, float* mom, int64_t d, f
         }
         p = fmaf(-lr, g, p);
         param[i] = p;
-        for (int k = 0; k < mir.n; ++k) mir.p[k][i] = p;
+#pragma unroll
+        for (int k = 0; k < kMaxMirrors; ++k)
+            if (k < mir.n) mir.p[k][i] = p;
     }, "sgd step");
 }
 
@@ -200,7 +202,9 @@ GB_API int gb_broadcast_copy(float const* src, float* const* dsts, int n_dst, in
     for (int k = 0; k < n_dst; ++k) mir.p[k] = dsts[k];
     return launch_map(d, static_cast<cudaStream_t>(stream), [=] __device__(long long i) {
         float const v = src[i];
-        for (int k = 0; k < mir.n; ++k) mir.p[k][i] = v;
+#pragma unroll
+        for (int k = 0; k < kMaxMirrors; ++k)
+            if (k < mir.n) mir.p[k][i] = v;
     }, "broadcast copy");
 }
 

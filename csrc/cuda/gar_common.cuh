@@ -3,6 +3,7 @@
 #pragma once
 
 #include <cstdint>
+#include <utility>
 #include <cuda_runtime.h>
 
 #include "ptx.cuh"
@@ -90,50 +91,83 @@ struct PairwiseArgs {
 
 // ------------------------------------------------------------------- sorting networks ---
 
-// Bitonic network on a register array (fully unrolled; NP a power of two). NaNs must have
-// been replaced beforehand (fminf/fmaxf drop them).
+// Batcher odd-even merge sort on a register array (NP a power of two): 19 / 63 / 191 / 543
+// compare-exchanges for NP = 8 / 16 / 32 / 64. The comparator list is a constexpr table and
+// the network is expanded with a fold expression, so every register index is a constant
+// expression (a partially unrolled loop nest would push the array to local memory).
+// NaNs must have been replaced beforehand (fminf/fmaxf drop them).
+template <int NP>
+struct OddEvenNetwork {
+    static constexpr int kMax = NP <= 2 ? 1 : NP * 9;  // >= comparator count for NP <= 64
+    struct Table {
+        int a[kMax];
+        int b[kMax];
+        int count;
+    };
+    static constexpr Table build() {
+        Table t{};
+        t.count = 0;
+        for (int p = 1; p < NP; p <<= 1)
+            for (int k = p; k >= 1; k >>= 1)
+                for (int j = k % p; j + k < NP; j += 2 * k)
+                    for (int i = 0; i < k; ++i)
+                        if ((i + j) / (2 * p) == (i + j + k) / (2 * p)) {
+                            t.a[t.count] = i + j;
+                            t.b[t.count] = i + j + k;
+                            ++t.count;
+                        }
+        return t;
+    }
+    static constexpr Table table = build();
+};
+
+template <int NP, int C>
+__device__ __forceinline__ void compare_exchange(float (&v)[NP]) {
+    constexpr int a = OddEvenNetwork<NP>::table.a[C], b = OddEvenNetwork<NP>::table.b[C];
+    float const lo = fminf(v[a], v[b]), hi = fmaxf(v[a], v[b]);
+    v[a] = lo;
+    v[b] = hi;
+}
+
+template <int NP, int C>
+__device__ __forceinline__ void compare_exchange_pair(float (&key)[NP], float (&val)[NP]) {
+    constexpr int a = OddEvenNetwork<NP>::table.a[C], b = OddEvenNetwork<NP>::table.b[C];
+    bool const swap = key[a] > key[b];
+    float const ka = key[a], kb = key[b], va = val[a], vb = val[b];
+    key[a] = swap ? kb : ka;
+    key[b] = swap ? ka : kb;
+    val[a] = swap ? vb : va;
+    val[b] = swap ? va : vb;
+}
+
+template <int NP, int... Cs>
+__device__ __forceinline__ void sort_regs_seq(float (&v)[NP], std::integer_sequence<int, Cs...>) {
+    (compare_exchange<NP, Cs>(v), ...);
+}
+template <int NP, int... Cs>
+__device__ __forceinline__ void sort_pairs_seq(float (&key)[NP], float (&val)[NP], std::integer_sequence<int, Cs...>) {
+    (compare_exchange_pair<NP, Cs>(key, val), ...);
+}
+
 template <int NP>
 __device__ __forceinline__ void sort_regs(float (&v)[NP]) {
-#pragma unroll
-    for (int k = 2; k <= NP; k <<= 1) {
-#pragma unroll
-        for (int j = k >> 1; j > 0; j >>= 1) {
-#pragma unroll
-            for (int i = 0; i < NP; ++i) {
-                int const l = i ^ j;
-                if (l > i) {
-                    bool const up = (i & k) == 0;
-                    float const lo = fminf(v[i], v[l]), hi = fmaxf(v[i], v[l]);
-                    v[i] = up ? lo : hi;
-                    v[l] = up ? hi : lo;
-                }
-            }
-        }
-    }
+    sort_regs_seq<NP>(v, std::make_integer_sequence<int, OddEvenNetwork<NP>::table.count>{});
 }
 
 // Same network ordering (key, value) pairs by key.
 template <int NP>
 __device__ __forceinline__ void sort_pairs(float (&key)[NP], float (&val)[NP]) {
+    sort_pairs_seq<NP>(key, val, std::make_integer_sequence<int, OddEvenNetwork<NP>::table.count>{});
+}
+
+// v[k] for a runtime (warp-uniform) k without dynamic register indexing.
+template <int NP>
+__device__ __forceinline__ float pick_reg(float const (&v)[NP], int k) {
+    float r = v[0];
 #pragma unroll
-    for (int k = 2; k <= NP; k <<= 1) {
-#pragma unroll
-        for (int j = k >> 1; j > 0; j >>= 1) {
-#pragma unroll
-            for (int i = 0; i < NP; ++i) {
-                int const l = i ^ j;
-                if (l > i) {
-                    bool const up = (i & k) == 0;
-                    bool const swap = up ? (key[i] > key[l]) : (key[i] < key[l]);
-                    float const ki = key[i], kl = key[l], vi = val[i], vl = val[l];
-                    key[i] = swap ? kl : ki;
-                    key[l] = swap ? ki : kl;
-                    val[i] = swap ? vl : vi;
-                    val[l] = swap ? vi : vl;
-                }
-            }
-        }
-    }
+    for (int i = 1; i < NP; ++i)
+        if (i == k) r = v[i];
+    return r;
 }
 
 // ------------------------------------------------------------------------ Philox RNG ---

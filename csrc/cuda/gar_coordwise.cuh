@@ -1,0 +1,282 @@
+// coordwise_select kernel template (see gar_coordwise.cu for the description and citations).
+// Instantiated per padded column size NP in gar_coordwise_np*.cu so the translation units build
+// in parallel.
+#pragma once
+
+#include <cfloat>
+#include <cmath>
+
+#include "gar_common.cuh"
+
+namespace gb {
+
+template <int V>
+struct Vec;
+template <>
+struct Vec<4> {
+    using type = float4;
+};
+template <>
+struct Vec<2> {
+    using type = float2;
+};
+template <>
+struct Vec<1> {
+    using type = float;
+};
+
+template <int V>
+__device__ __forceinline__ void vec_load(float (&dst)[V], const float* p) {
+    typename Vec<V>::type const v = *reinterpret_cast<typename Vec<V>::type const*>(p);
+    if constexpr (V == 4) {
+        dst[0] = v.x; dst[1] = v.y; dst[2] = v.z; dst[3] = v.w;
+    } else if constexpr (V == 2) {
+        dst[0] = v.x; dst[1] = v.y;
+    } else {
+        dst[0] = v;
+    }
+}
+
+template <int V>
+__device__ __forceinline__ void vec_store(float* p, float const (&src)[V]) {
+    if constexpr (V == 4) *reinterpret_cast<float4*>(p) = make_float4(src[0], src[1], src[2], src[3]);
+    else if constexpr (V == 2) *reinterpret_cast<float2*>(p) = make_float2(src[0], src[1]);
+    else *p = src[0];
+}
+
+// SGD step (torch.optim.SGD semantics) + publication, on V consecutive coordinates.
+template <int V>
+__device__ __forceinline__ void apply_update(FusedUpdate const& u, long long x, float (&g)[V], float* out) {
+    if (out != nullptr) vec_store<V>(out + x, g);
+    if (u.mode == 0) return;
+    float p[V];
+    vec_load<V>(p, u.param + x);
+#pragma unroll
+    for (int e = 0; e < V; ++e) g[e] = fmaf(u.weight_decay, p[e], g[e]);
+    if (u.momentum != 0.0f) {
+        float buf[V];
+        if (u.first_step) {
+#pragma unroll
+            for (int e = 0; e < V; ++e) buf[e] = g[e];
+        } else {
+            vec_load<V>(buf, u.mom + x);
+#pragma unroll
+            for (int e = 0; e < V; ++e) buf[e] = fmaf(u.momentum, buf[e], (1.0f - u.dampening) * g[e]);
+        }
+        vec_store<V>(u.mom + x, buf);
+#pragma unroll
+        for (int e = 0; e < V; ++e) g[e] = u.nesterov ? fmaf(u.momentum, buf[e], g[e]) : buf[e];
+    }
+#pragma unroll
+    for (int e = 0; e < V; ++e) p[e] = fmaf(-u.lr, g[e], p[e]);
+    vec_store<V>(u.param + x, p);
+#pragma unroll
+    for (int k = 0; k < kMaxMirrors; ++k)
+        if (k < u.n_mirrors) vec_store<V>(u.mirror[k] + x, p);
+}
+
+// Reduce the `cnt` values of one coordinate held in v[0..NP). Entries at index >= cnt must hold
+// FLT_MAX (finite padding that sorts last). A cheap all-finite test (Σ 0·v on the FMA pipe)
+// selects the common path, which is the bare sorting network; columns containing NaN/±inf take
+// the careful path (NaN propagation or non-finite filtering, depending on the rule).
+template <int NP, int RULE>
+__device__ __forceinline__ float reduce_column(float (&v)[NP], int cnt, int rank, int upper, float p, unsigned long long seed,
+                                               long long x, float first_row_value) {
+    if constexpr (RULE == kRuleLinear) {
+        return v[0];
+    } else {
+        float probe = 0.0f;
+#pragma unroll
+        for (int i = 0; i < NP; ++i) probe = fmaf(v[i], 0.0f, probe);
+        bool has_nan = false;
+        int finite = cnt;
+        if (probe != 0.0f) {  // NaN: at least one non-finite value in this column
+            finite = 0;
+#pragma unroll
+            for (int i = 0; i < NP; ++i) {
+                float const val = v[i];
+                bool const live = i < cnt;
+                bool const isnan_ = val != val;
+                bool const fin = fabsf(val) <= FLT_MAX;
+                has_nan |= live && isnan_;
+                finite += (live && fin) ? 1 : 0;
+                if constexpr (RULE == kRuleMedianFiniteUpper) v[i] = (live && fin) ? val : INFINITY;
+                else v[i] = (live && !isnan_) ? val : INFINITY;
+            }
+        }
+        sort_regs<NP>(v);
+
+        float result = 0.0f;
+        if constexpr (RULE == kRuleMedianLower || RULE == kRuleCondense) {
+            result = pick_reg<NP>(v, (cnt - 1) >> 1);
+            if (has_nan) result = NAN;
+            if constexpr (RULE == kRuleCondense) {
+                uint4 const r = philox4x32(seed, static_cast<unsigned long long>(x), 0u);
+                result = (u01(r.x) < p) ? result : first_row_value;
+            }
+        } else if constexpr (RULE == kRuleMedianFiniteUpper) {
+            result = pick_reg<NP>(v, finite >> 1);
+            if (finite == 0) result = 0.0f;
+        } else if constexpr (RULE == kRuleTrimmedMean) {
+            int const lo = rank, hi = cnt - rank;
+            float sum = 0.0f;
+#pragma unroll
+            for (int i = 0; i < NP; ++i) sum += (i >= lo && i < hi) ? v[i] : 0.0f;
+            result = has_nan ? NAN : sum / static_cast<float>(hi - lo);
+        } else if constexpr (RULE == kRuleAveragedMedian) {
+            float const med = pick_reg<NP>(v, upper ? (cnt >> 1) : ((cnt - 1) >> 1));
+            float key[NP];
+#pragma unroll
+            for (int i = 0; i < NP; ++i) key[i] = (i < cnt) ? fabsf(v[i] - med) : INFINITY;
+            sort_pairs<NP>(key, v);
+            float sum = 0.0f;
+#pragma unroll
+            for (int i = 0; i < NP; ++i) sum += (i < rank) ? v[i] : 0.0f;
+            result = has_nan ? NAN : sum / static_cast<float>(rank);
+        }
+        return result;
+    }
+}
+
+// V consecutive coordinates starting at x: gather the columns through `loadv(i, dst[V])`, reduce.
+template <int NP, int RULE, bool MIX, int V, class LoadV>
+__device__ __forceinline__ void columns(CoordArgs const& a, float const* Ws, unsigned long long used_mask, long long x, LoadV loadv,
+                                        float (&result)[V]) {
+    float v[NP][V];
+    float first[V];
+    int cnt;
+    if constexpr (MIX) {  // y_k = Σ_i W[k][i]·x_i; Ws is NP × n, zero rows beyond theta; unused rows skipped (may hold NaN)
+        cnt = a.theta;
+#pragma unroll
+        for (int k = 0; k < NP; ++k)
+#pragma unroll
+            for (int e = 0; e < V; ++e) v[k][e] = 0.0f;
+        for (int i = 0; i < a.n; ++i) {
+            if (!((used_mask >> i) & 1ull)) continue;  // warp-uniform
+            float xi[V];
+            loadv(i, xi);
+#pragma unroll
+            for (int k = 0; k < NP; ++k) {
+                float const w = Ws[k * a.n + i];
+#pragma unroll
+                for (int e = 0; e < V; ++e) v[k][e] = fmaf(w, xi[e], v[k][e]);
+            }
+        }
+#pragma unroll
+        for (int k = 0; k < NP; ++k)
+            if (k >= cnt) {
+#pragma unroll
+                for (int e = 0; e < V; ++e) v[k][e] = FLT_MAX;
+            }
+#pragma unroll
+        for (int e = 0; e < V; ++e) first[e] = 0.0f;
+    } else {
+        cnt = a.n;
+#pragma unroll
+        for (int i = 0; i < NP; ++i) {
+            if (i < a.n) {
+                loadv(i, v[i]);
+            } else {
+#pragma unroll
+                for (int e = 0; e < V; ++e) v[i][e] = FLT_MAX;
+            }
+        }
+#pragma unroll
+        for (int e = 0; e < V; ++e) first[e] = v[0][e];
+    }
+#pragma unroll
+    for (int e = 0; e < V; ++e) {
+        float col[NP];
+#pragma unroll
+        for (int i = 0; i < NP; ++i) col[i] = v[i][e];
+        result[e] = reduce_column<NP, RULE>(col, cnt, a.rank, a.upper, a.p, a.seed, x + e, first[e]);
+    }
+}
+
+template <int NP, int RULE, bool MIX, int V>
+__global__ void __launch_bounds__(kThreads) coordwise_kernel(const __grid_constant__ CoordArgs a) {
+    extern __shared__ __align__(128) unsigned char smem_raw[];
+    __shared__ TileRing ring;
+    float* Ws = reinterpret_cast<float*>(smem_raw);  // NP × n weights (MIX only), zero padded
+    int const w_floats = MIX ? ((NP * a.n + 31) / 32) * 32 : 0;
+    float* stages = Ws + w_floats;  // kStages × n × tile
+    int const warp = threadIdx.x >> 5;
+    int const tile = a.tile;
+    long long const full_tiles = a.use_tma ? a.d / tile : 0;
+
+    if constexpr (MIX)
+        for (int i = threadIdx.x; i < NP * a.n; i += blockDim.x) Ws[i] = (i < a.theta * a.n) ? a.W[i] : 0.0f;
+    ring_init(ring);  // contains the __syncthreads that also publishes Ws
+    unsigned long long used_mask = ~0ull;  // rows with at least one non-zero weight
+    if constexpr (MIX) {
+        used_mask = 0ull;
+        for (int i = 0; i < a.n; ++i) {
+            bool used = false;
+            for (int k = 0; k < a.theta; ++k) used |= (Ws[k * a.n + i] != 0.0f);
+            used_mask |= used ? (1ull << i) : 0ull;
+        }
+    }
+
+    if (warp == 0) {
+        if (full_tiles > 0 && ptx::elect_one())
+            ring_produce(ring, stages, a.rows, a.n, tile, full_tiles, [&](int i) { return ((used_mask >> i) & 1ull) != 0ull; });
+    } else {
+        int const ctid = threadIdx.x - 32;
+        constexpr int kConsumers = 32 * kConsumerWarps;
+        size_t const stage_floats = static_cast<size_t>(a.n) * tile;
+        long long it = 0;
+        for (long long t = blockIdx.x; t < full_tiles; t += gridDim.x, ++it) {
+            int const s = static_cast<int>(it % kStages);
+            uint32_t const phase = static_cast<uint32_t>((it / kStages) & 1);
+            ptx::mbar_wait(&ring.full[s], phase);
+            float const* src = stages + s * stage_floats;
+            for (int c = ctid * V; c < tile; c += kConsumers * V) {
+                long long const x = t * tile + c;
+                float r[V];
+                columns<NP, RULE, MIX, V>(a, Ws, used_mask, x, [&](int i, float (&dst)[V]) { vec_load<V>(dst, src + i * tile + c); }, r);
+                apply_update<V>(a.upd, x, r, a.out);
+            }
+            __syncwarp();
+            if ((threadIdx.x & 31) == 0) ptx::mbar_arrive(&ring.empty[s]);
+        }
+        // remainder (and everything when buffers are not 16-byte aligned): direct global loads
+        long long const done = full_tiles * tile;
+        for (long long x = done + static_cast<long long>(blockIdx.x) * kConsumers + ctid; x < a.d;
+             x += static_cast<long long>(gridDim.x) * kConsumers) {
+            float r[1];
+            columns<NP, RULE, MIX, 1>(a, Ws, used_mask, x, [&](int i, float (&dst)[1]) { dst[0] = a.rows.p[i][x]; }, r);
+            apply_update<1>(a.upd, x, r, a.out);
+        }
+    }
+}
+
+template <int NP, int RULE, bool MIX, int V>
+cudaError_t launch_coordwise(CoordArgs const& a, int grid, size_t smem, cudaStream_t stream) {
+    auto kern = coordwise_kernel<NP, RULE, MIX, V>;
+    cudaError_t err = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem));
+    if (err != cudaSuccess) return err;
+    kern<<<grid, kThreads, smem, stream>>>(a);
+    return cudaGetLastError();
+}
+
+// Per-NP dispatch over the rules (defined once per NP in gar_coordwise_np*.cu).
+template <int NP>
+cudaError_t dispatch_coordwise(CoordArgs const& a, int grid, size_t smem, cudaStream_t stream);
+
+#define GB_DEFINE_COORDWISE_DISPATCH(NP, V)                                                                            \
+    template <>                                                                                                        \
+    cudaError_t dispatch_coordwise<NP>(CoordArgs const& a, int grid, size_t smem, cudaStream_t stream) {               \
+        bool const mix = a.theta > 0;                                                                                  \
+        switch (a.rule) {                                                                                              \
+            case kRuleMedianLower: return launch_coordwise<NP, kRuleMedianLower, false, V>(a, grid, smem, stream);     \
+            case kRuleMedianFiniteUpper: return launch_coordwise<NP, kRuleMedianFiniteUpper, false, V>(a, grid, smem, stream); \
+            case kRuleTrimmedMean: return launch_coordwise<NP, kRuleTrimmedMean, false, V>(a, grid, smem, stream);     \
+            case kRuleCondense: return launch_coordwise<NP, kRuleCondense, false, V>(a, grid, smem, stream);           \
+            case kRuleAveragedMedian:                                                                                  \
+                return mix ? launch_coordwise<NP, kRuleAveragedMedian, true, V>(a, grid, smem, stream)                 \
+                           : launch_coordwise<NP, kRuleAveragedMedian, false, V>(a, grid, smem, stream);               \
+            default: return cudaErrorInvalidValue;                                                                     \
+        }                                                                                                              \
+    }
+
+}  // namespace gb

@@ -42,26 +42,53 @@ __device__ __forceinline__ void block_pair_of(int item, int B, int& bi, int& bj)
     bj = bi + item;
 }
 
-__device__ __forceinline__ float sq4(float4 a, float4 b) {
+// acc += Σ over the 4 coordinates of (a − b)²   (4 FADD + 4 FFMA)
+__device__ __forceinline__ float sq4_acc(float acc, float4 a, float4 b) {
     float const dx = a.x - b.x, dy = a.y - b.y, dz = a.z - b.z, dw = a.w - b.w;
-    return fmaf(dx, dx, fmaf(dy, dy, fmaf(dz, dz, dw * dw)));
+    return fmaf(dw, dw, fmaf(dz, dz, fmaf(dy, dy, fmaf(dx, dx, acc))));
 }
 
-// Accumulate one 128-coordinate chunk (lane = 4 coordinates) of block pair (bi, bj).
-template <class Load4>
-__device__ __forceinline__ void accumulate_chunk(float (&acc)[kG][kG], int bi, int bj, int n, Load4 load4) {
-    float4 a[kG], b[kG];
+// Accumulate the 128-coordinate chunks first, first+stride, ... (lane = 4 coordinates) of the
+// row-block pair whose rows start at `pa` / `pb` in shared memory (row pitch `tile` floats).
+// FULL: all 4 rows of both blocks exist (no predicates). DIAG: bi == bj (upper triangle only).
+template <bool FULL, bool DIAG>
+__device__ __forceinline__ void accumulate_block(float (&acc)[kG][kG], float const* pa, float const* pb, int tile, int rows_a, int rows_b,
+                                                 int first, int stride, int chunks) {
+    for (int ch = first; ch < chunks; ch += stride) {
+        float4 a[kG], b[kG];
 #pragma unroll
-    for (int r = 0; r < kG; ++r) {
-        int const ra = bi * kG + r, rb = bj * kG + r;
-        a[r] = ra < n ? load4(ra) : make_float4(0.f, 0.f, 0.f, 0.f);
-        b[r] = (bi == bj) ? a[r] : (rb < n ? load4(rb) : make_float4(0.f, 0.f, 0.f, 0.f));
+        for (int r = 0; r < kG; ++r) {
+            if (FULL || r < rows_a) a[r] = *reinterpret_cast<float4 const*>(pa + r * tile + ch * 128);
+            else a[r] = make_float4(0.f, 0.f, 0.f, 0.f);
+            if constexpr (DIAG) {
+                b[r] = a[r];
+            } else {
+                if (FULL || r < rows_b) b[r] = *reinterpret_cast<float4 const*>(pb + r * tile + ch * 128);
+                else b[r] = make_float4(0.f, 0.f, 0.f, 0.f);
+            }
+        }
+#pragma unroll
+        for (int r = 0; r < kG; ++r)
+#pragma unroll
+            for (int c = 0; c < kG; ++c)
+                if (!DIAG || c > r) acc[r][c] = sq4_acc(acc[r][c], a[r], b[c]);
     }
-#pragma unroll
-    for (int r = 0; r < kG; ++r)
-#pragma unroll
-        for (int c = 0; c < kG; ++c)
-            if (bi != bj || c > r) acc[r][c] += sq4(a[r], b[c]);
+}
+
+// Dispatch on (all rows present, diagonal block). `src` = stage base with the lane offset added.
+__device__ __forceinline__ void accumulate_pair(float (&acc)[kG][kG], float const* src, int tile, int n, int bi, int bj, int first,
+                                                int stride, int chunks) {
+    float const* pa = src + bi * kG * tile;
+    float const* pb = src + bj * kG * tile;
+    int const rows_a = min(kG, n - bi * kG), rows_b = min(kG, n - bj * kG);
+    bool const full = rows_a == kG && rows_b == kG;
+    if (bi == bj) {
+        if (full) accumulate_block<true, true>(acc, pa, pb, tile, rows_a, rows_b, first, stride, chunks);
+        else accumulate_block<false, true>(acc, pa, pb, tile, rows_a, rows_b, first, stride, chunks);
+    } else {
+        if (full) accumulate_block<true, false>(acc, pa, pb, tile, rows_a, rows_b, first, stride, chunks);
+        else accumulate_block<false, false>(acc, pa, pb, tile, rows_a, rows_b, first, stride, chunks);
+    }
 }
 
 __device__ __forceinline__ float warp_sum(float v) {
@@ -339,20 +366,14 @@ __global__ void __launch_bounds__(kThreads) pairwise_kernel(const __grid_constan
             int const s = static_cast<int>(it % kStages);
             uint32_t const phase = static_cast<uint32_t>((it / kStages) & 1);
             ptx::mbar_wait(&ring.full[s], phase);
-            float const* src = stages + s * stage_floats;
+            float const* src = stages + s * stage_floats + lane * 4;
             if (fixed) {
-                for (int ch = my_first; ch < chunks; ch += my_stride)
-                    accumulate_chunk(acc, my_bi, my_bj, n, [&](int row) {
-                        return *reinterpret_cast<float4 const*>(src + static_cast<size_t>(row) * tile + ch * 128 + lane * 4);
-                    });
+                accumulate_pair(acc, src, tile, n, my_bi, my_bj, my_first, my_stride, chunks);
             } else {
                 for (int p = cw; p < BP; p += kConsumerWarps) {
                     int bi, bj;
                     block_pair_of(p, B, bi, bj);
-                    for (int ch = 0; ch < chunks; ++ch)
-                        accumulate_chunk(acc, bi, bj, n, [&](int row) {
-                            return *reinterpret_cast<float4 const*>(src + static_cast<size_t>(row) * tile + ch * 128 + lane * 4);
-                        });
+                    accumulate_pair(acc, src, tile, n, bi, bj, 0, 1, chunks);
                     flush(acc, bi, bj, n, slot);
                 }
             }
@@ -487,13 +508,7 @@ extern "C" GB_API int gb_pairwise_select(float const* const* rows, int n, int64_
     a.partials = reinterpret_cast<float*>(static_cast<unsigned char*>(scratch) + 256);
 
     auto kern = pairwise_kernel;
-    static bool configured[64] = {false};
-    int dev = 0;
-    cudaGetDevice(&dev);
-    if (dev >= 0 && dev < 64 && !configured[dev]) {
-        if (cuda_check(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024), "pairwise smem attribute")) return 1;
-        configured[dev] = true;
-    }
+    if (cuda_check(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)), "pairwise smem attribute")) return 1;
     kern<<<static_cast<int>(grid), kThreads, smem, static_cast<cudaStream_t>(stream)>>>(a);
     return cuda_check(cudaGetLastError(), "pairwise launch");
 }

@@ -22,6 +22,7 @@ int cuda_fail(char const* message) {
 
 int cuda_check(cudaError_t err, char const* what) {
     if (err == cudaSuccess) return 0;
+    cudaGetLastError();  // clear the (non-sticky) error so it is not misattributed to a later call
     tl_error = std::string(what) + ": " + cudaGetErrorName(err) + " (" + cudaGetErrorString(err) + ")";
     return 1;
 }
