@@ -172,3 +172,41 @@ def average(gradients, update=None, want_out=True):
     if key not in _uniform:
         _uniform[key] = torch.full((1, n), 1.0 / n, dtype=torch.float32, device=device)
     return coordwise(gradients, "linear", W=_uniform[key], theta=1, update=update, want_out=want_out)
+
+
+def aggregate(name, gradients, f, m=None, update=None, want_out=True, **kw):
+    """Run the registry rule `name` on device rows with an optional fused SGD epilogue.
+
+    Same semantics as `aggregators.gars[name](gradients=..., f=...)` on CUDA tensors; the fused
+    form additionally applies the optimizer step and publishes the parameters in the same pass.
+    """
+    n = len(gradients)
+    common = dict(update=update, want_out=want_out)
+    if name == "average":
+        return average(gradients, **common)
+    if name == "median":
+        return coordwise(gradients, "median_lower", **common)
+    if name == "native-median":
+        return coordwise(gradients, "median_finite_upper", **common)
+    if name == "trimmed_mean":
+        return coordwise(gradients, "trimmed_mean", f=f, **common)
+    if name == "averaged_median":
+        return coordwise(gradients, "averaged_median", beta=kw.get("beta") or n - f, **common)
+    if name == "condense":
+        return coordwise(gradients, "condense", p=kw.get("p", 0.9), seed=kw.get("seed", 0), **common)
+    if name == "krum":
+        return krum(gradients, f, n - f - 2 if m is None else m, n - f - 1, False, **common)
+    if name == "native-krum":
+        return krum(gradients, f, n - f - 2 if m is None else m, n - f - 2, True, **common)
+    if name == "bulyan":
+        return bulyan(gradients, f, m, native=False, **common)
+    if name == "native-bulyan":
+        return bulyan(gradients, f, m, native=True, **common)
+    if name in ("brute", "mda"):
+        return mda(gradients, f, squared=False, **common)
+    if name == "native-brute":
+        return mda(gradients, f, squared=True, **common)
+    if name == "aksel":
+        mode = kw.get("mode", "mid")
+        return aksel(gradients, (n + 1) // 2 if mode == "mid" else n - f, **common)
+    raise KeyError("unknown aggregation rule %r" % (name,))

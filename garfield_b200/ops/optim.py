@@ -28,14 +28,16 @@ _DEFAULTS = {
 }
 
 
-class FlatOptimizer:
-    """Optimizer over one flat parameter tensor. `step(flat_grad)` applies one update in place."""
+class FlatOptimizer(torch.optim.Optimizer):
+    """Optimizer over one flat parameter tensor. `step(flat_grad)` applies one update in place.
+
+    Subclasses `torch.optim.Optimizer` so LR schedulers, `adjust_learning_rate` and
+    `param_groups` edits behave as with the reference's torch optimizers.
+    """
 
     def __init__(self, flat_param, name, *args, **kwargs):
         if name not in _DEFAULTS:
             raise KeyError(name)
-        self.name = name
-        self.param = flat_param
         hyper = dict(_DEFAULTS[name])
         if args:  # positional lr, like torch.optim constructors
             hyper["lr"] = args[0]
@@ -43,16 +45,17 @@ class FlatOptimizer:
             if key not in hyper:
                 raise TypeError("unexpected optimizer argument %r for %s" % (key, name))
             hyper[key] = value
-        hyper["params"] = [flat_param]
-        self.param_groups = [hyper]
-        self.state = {}
+        self.name = name
+        self.param = flat_param
         self.steps = 0
+        super().__init__([flat_param], hyper)
 
     # -- state helpers ---------------------------------------------------------------------
     def _buf(self, key, fill=0.0):
-        if key not in self.state:
-            self.state[key] = torch.full_like(self.param, fill)
-        return self.state[key]
+        slot = self.state[self.param]
+        if key not in slot:
+            slot[key] = torch.full_like(self.param, fill)
+        return slot[key]
 
     @property
     def hyper(self):
@@ -64,14 +67,17 @@ class FlatOptimizer:
     def state_dict(self):
         hyper = {k: v for k, v in self.hyper.items() if k != "params"}
         return {"name": self.name, "hyper": hyper, "steps": self.steps,
-                "state": {k: v.detach().clone() for k, v in self.state.items()}}
+                "state": {k: v.detach().clone() for k, v in self.state[self.param].items()}}
 
     def load_state_dict(self, sd):
         if sd["name"] != self.name:
             raise ValueError("optimizer kind mismatch: %s vs %s" % (sd["name"], self.name))
         self.hyper.update(sd["hyper"])
         self.steps = int(sd["steps"])
-        self.state = {k: v.to(self.param.device).clone() for k, v in sd["state"].items()}
+        slot = self.state[self.param]
+        slot.clear()
+        for k, v in sd["state"].items():
+            slot[k] = v.to(self.param.device).clone()
 
     def sgd_fusion(self, mirrors=()):
         """`ops.gar.SgdFusion` describing this optimizer's next step (SGD only)."""
@@ -88,8 +94,12 @@ class FlatOptimizer:
 
     # -- the update ------------------------------------------------------------------------
     @torch.no_grad()
-    def step(self, grad, mirrors=()):
+    def step(self, grad=None, mirrors=()):
         p, h = self.param, self.hyper
+        if grad is None or callable(grad):  # torch-style call: use the gradient attached to the flat parameter
+            grad = p.grad
+            if grad is None:
+                return None
         grad = grad.to(device=p.device, dtype=p.dtype).reshape(-1)
         self.steps += 1
         use_kernel = p.is_cuda and p.dtype == torch.float32 and _lib.available()

@@ -1,0 +1,214 @@
+"""Device-resident SSMW (AggregaThor) step engine: one process per GPU, n workers + 1 server.
+
+What one `step()` does (reference loop: applications/Aggregathor/trainer.py:231-237 +
+garfieldpp/server.py:112-159,277-287 + worker.py:77-96):
+
+    S1/S2  every local worker runs forward+backward on ITS replica of the model (same flat
+           parameter arena, own BatchNorm buffers) and writes its gradient straight into its
+           row of the rank's peer-mapped gradient arena — all local workers are captured in ONE
+           CUDA graph with one stream per worker so small kernels of different workers overlap;
+    S3     Byzantine workers overwrite their row with an on-device attack;
+    S4/S5  rank 0 (the server) runs the aggregation kernels over a row table that mixes local
+           rows and peer-mapped rows of the other GPUs (NVLink P2P loads / TMA bulk copies from
+           inside the kernel — no NCCL gather, no host copy);
+    S6/S1' the SGD step is fused in the aggregation epilogue, and the same kernel stores the
+           updated parameters into every rank's parameter arena (model publication).
+
+Ranks synchronise twice per step (gradients ready / parameters published) with a 4-byte NCCL
+all-reduce used purely as a barrier; everything else is device-to-device.
+"""
+
+from __future__ import annotations
+
+import copy
+
+import torch
+import torch.distributed as dist
+
+from .arena import FlatModel
+from .peer import DeviceBuffer, PeerArena
+from ..garfieldpp import tools
+from ..garfieldpp.datasets import DatasetManager
+from ..ops import _lib, attacks, gar as gar_ops
+from ..ops.optim import FlatOptimizer
+
+__all__ = ["SSMWEngine"]
+
+
+class _LocalWorker:
+    """One worker hosted by this rank: model replica, static input buffers, gradient row."""
+
+    def __init__(self, wid, replica, row, loss_fn, batch_shape, target_shape, target_dtype, device, attack=None):
+        self.wid, self.replica, self.row, self.loss_fn, self.attack = wid, replica, row, loss_fn, attack
+        self.data = torch.zeros(batch_shape, device=device)
+        self.target = torch.zeros(target_shape, dtype=target_dtype, device=device)
+        self.loss = torch.zeros((), device=device)
+        self.stream = torch.cuda.Stream(device=device) if device.type == "cuda" else None
+        replica.bind_grads(row)  # permanent: autograd accumulates in place into the arena row
+
+    def forward_backward(self):
+        self.row.zero_()
+        self.replica.module.train()
+        loss = self.loss_fn(self.replica.module(self.data), self.target)
+        loss.backward()
+        self.loss.copy_(loss.detach())
+
+
+class SSMWEngine:
+    def __init__(self, model, dataset, loss, num_workers, f, gar, batch, optimizer="sgd", opt_args=None, byzantine=None,
+                 device=None, group=None, use_graphs=True, train_set=None, seed=1234, gar_kwargs=None):
+        self.rank = dist.get_rank(group) if dist.is_initialized() else 0
+        self.world = dist.get_world_size(group) if dist.is_initialized() else 1
+        self.group = group
+        self.device = torch.device(device) if device is not None else torch.device("cuda", torch.cuda.current_device())
+        self.n, self.f, self.gar_name, self.batch = num_workers, f, gar, batch
+        self.gar_kwargs = dict(gar_kwargs or {})
+        self.byzantine = dict(byzantine or {})
+        self.is_server = self.rank == 0
+        if self.device.type != "cuda" or not gar_ops.available():
+            raise RuntimeError("SSMWEngine needs a CUDA device and the sm_100a library")
+
+        torch.manual_seed(seed)
+        module = tools.select_model(model, self.device, dataset)
+        self.d = sum(p.numel() for p in module.parameters())
+        self.pitch = (self.d + 63) // 64 * 64
+        self.local_ids = [w for w in range(self.n) if w % self.world == self.rank]
+        self.max_local = (self.n + self.world - 1) // self.world
+
+        # peer-mapped arenas: parameters (one per rank) and gradient rows (max_local per rank)
+        self.param_arena = PeerArena(self.pitch, self.device, group)
+        self.grad_arena = PeerArena(self.max_local * self.pitch, self.device, group)
+        self.flat = self.param_arena.local[:self.d]
+        self.master = FlatModel(module, self.device, flat=None)
+        if self.world > 1:  # everyone starts from rank 0's initialisation
+            dist.broadcast(self.master.flat, src=0, group=group)
+            for buf in self.master.module.buffers():
+                dist.broadcast(buf, src=0, group=group)
+        self.flat.copy_(self.master.flat)
+        self.master = FlatModel(module, self.device, flat=self.flat)  # re-alias onto the arena
+
+        loss_fn = tools.select_loss(loss)
+        self.train_sets = {}
+        self.workers = []
+        for j, wid in enumerate(self.local_ids):
+            replica = FlatModel(copy.deepcopy(module), self.device, flat=self.flat)
+            row = self.grad_arena.local[j * self.pitch:j * self.pitch + self.d]
+            if train_set is not None:
+                batches = train_set(wid)
+            else:
+                batches = DatasetManager(dataset, batch, self.n, self.n + 1, wid + 1).get_train_set()
+            self.train_sets[wid] = batches
+            x0, y0 = batches[0]
+            self.workers.append(_LocalWorker(wid, replica, row, loss_fn, tuple(x0.shape), tuple(y0.shape), y0.dtype, self.device,
+                                             attack=self.byzantine.get(wid)))
+
+        # server state
+        self.optimizer = FlatOptimizer(self.flat, optimizer, **(opt_args or {})) if self.is_server else None
+        self.rows = None
+        if self.is_server:
+            self.rows = []
+            for wid in range(self.n):
+                owner, j = wid % self.world, wid // self.world
+                self.rows.append(self.grad_arena.peer(owner)[j * self.pitch:j * self.pitch + self.d])
+            self.mirrors = [self.param_arena.peer(r)[:self.d] for r in range(self.world) if r != self.rank]
+        self._flag = torch.zeros(1, device=self.device)
+        self._graph = None
+        self.use_graphs = use_graphs
+        self.steps_done = 0
+        self.h2d_bytes = 0
+
+    # ------------------------------------------------------------------------------------------
+    def _barrier(self):
+        if self.world > 1:
+            dist.all_reduce(self._flag, group=self.group)
+
+    def load_batches(self, iter_num):
+        """Host→device copy of this step's batch of every local worker (pinned source, async)."""
+        nbytes = 0
+        for w in self.workers:
+            batches = self.train_sets[w.wid]
+            x, y = batches[iter_num % len(batches)]
+            w.data.copy_(x, non_blocking=True)
+            w.target.copy_(y, non_blocking=True)
+            nbytes += x.numel() * x.element_size() + y.numel() * y.element_size()
+        self.h2d_bytes = nbytes
+        return nbytes
+
+    def _run_workers(self):
+        main = torch.cuda.current_stream(self.device)
+        for w in self.workers:
+            w.stream.wait_stream(main)
+            with torch.cuda.stream(w.stream):
+                w.forward_backward()
+        for w in self.workers:
+            main.wait_stream(w.stream)
+
+    def _capture(self):
+        side = torch.cuda.Stream(device=self.device)
+        side.wait_stream(torch.cuda.current_stream(self.device))
+        with torch.cuda.stream(side):
+            for _ in range(3):
+                self._run_workers()
+        torch.cuda.current_stream(self.device).wait_stream(side)
+        torch.cuda.synchronize(self.device)
+        graph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(graph):
+            self._run_workers()
+        self._graph = graph
+
+    def compute_gradients(self):
+        if not self.workers:
+            return
+        if self.use_graphs:
+            if self._graph is None:
+                self._capture()
+            self._graph.replay()
+        else:
+            self._run_workers()
+        for w in self.workers:
+            if w.attack is not None:
+                self._attack(w)
+
+    def _attack(self, w):
+        if w.attack == "random":
+            w.row.copy_(attacks.random_like(w.row))
+        elif w.attack == "reverse":
+            w.row.copy_(attacks.reverse(w.row))
+        elif w.attack == "drop":
+            w.row.copy_(attacks.drop(w.row))
+        elif w.attack in ("lie", "empire"):
+            honest = [o.row for o in self.workers if o.attack is None] or [w.row]
+            w.row.copy_(attacks.lie(honest) if w.attack == "lie" else attacks.empire(honest))
+        else:
+            raise ValueError("unknown attack %r" % (w.attack,))
+
+    def aggregate_and_update(self):
+        """Server only: fused gather + GAR + optimizer step + parameter publication."""
+        opt = self.optimizer
+        if opt.name == "sgd":
+            gar_ops.aggregate(self.gar_name, self.rows, self.f, update=opt.sgd_fusion(self.mirrors), want_out=False,
+                              **self.gar_kwargs)
+            opt.note_fused_step()
+        else:
+            grad = gar_ops.aggregate(self.gar_name, self.rows, self.f, **self.gar_kwargs)
+            opt.step(grad, mirrors=self.mirrors)
+
+    def step(self, iter_num, load=True):
+        """One training iteration. Returns the mean loss of this rank's workers (device scalar)."""
+        if load:
+            self.load_batches(iter_num)
+        self.compute_gradients()
+        self._barrier()                      # all gradient rows are complete
+        if self.is_server:
+            self.aggregate_and_update()
+        self._barrier()                      # parameters published to every arena
+        self.steps_done += 1
+        if self.workers:
+            return torch.stack([w.loss for w in self.workers]).mean()
+        return torch.zeros((), device=self.device)
+
+    def close(self):
+        self._graph = None
+        torch.cuda.synchronize(self.device)
+        self.grad_arena.close()
+        self.param_arena.close()
