@@ -19,6 +19,7 @@
 
 #include <cfloat>
 #include <cmath>
+#include <mutex>
 
 #include "../cpu/combinations.hpp"
 #include "gar_common.cuh"
@@ -511,4 +512,110 @@ extern "C" GB_API int gb_pairwise_select(float const* const* rows, int n, int64_
     if (cuda_check(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)), "pairwise smem attribute")) return 1;
     kern<<<static_cast<int>(grid), kThreads, smem, static_cast<cudaStream_t>(stream)>>>(a);
     return cuda_check(cudaGetLastError(), "pairwise launch");
+}
+
+
+// ------------------------------------------------------------- allocation-free variant ---
+//
+// Some hosts of this library may not allocate device memory at the moment they need an
+// aggregation: a serving or training process that handed the whole HBM to its own pool at
+// start-up (a later cudaMalloc fails or fragments that pool), a steady-state loop running under
+// a fixed memory plan, or a latency-critical path that cannot afford cudaMalloc's device-wide
+// synchronisation. For them the scratch of the pairwise kernel (per-CTA partial distance
+// matrices + the completion counter) lives in this fixed array inside the library image instead
+// of a caller-provided buffer. Every GPU that loads the library carries the array until exit.
+//
+// Limit: kStaticMaxRows gradients per call (the array holds 256 + 296·16·16·4 bytes, i.e. the
+// partials of the largest grid this library launches on a B200 for n <= 16).
+constexpr int kStaticMaxRows = 16;
+constexpr long long kStaticScratchBytes = 256 + 296LL * kStaticMaxRows * kStaticMaxRows * static_cast<long long>(sizeof(float));
+static __device__ __align__(256) unsigned char g_pairwise_static_scratch[kStaticScratchBytes];
+
+namespace {
+// Device address of the array, looked up once per device. In host code the symbol above is only
+// a stand-in; the address a kernel can dereference comes from cudaGetSymbolAddress.
+std::mutex g_static_mutex;
+void* g_static_scratch_ptr[64] = {nullptr};
+
+int static_scratch_for_current_device(void** out) {
+    int dev = 0;
+    if (gb::cuda_check(cudaGetDevice(&dev), "no-alloc pairwise: cudaGetDevice")) return 1;
+    if (dev < 0 || dev >= 64) return gb::cuda_fail("no-alloc pairwise: device ordinal out of range (0..63)");
+    std::lock_guard<std::mutex> lock(g_static_mutex);
+    if (g_static_scratch_ptr[dev] == nullptr) {
+        void* ptr = nullptr;
+        if (gb::cuda_check(cudaGetSymbolAddress(&ptr, g_pairwise_static_scratch), "no-alloc pairwise: cudaGetSymbolAddress")) return 1;
+        g_static_scratch_ptr[dev] = ptr;
+    }
+    *out = g_static_scratch_ptr[dev];
+    return 0;
+}
+}  // namespace
+
+// Same computation and outputs as gb_pairwise_select, but the caller passes no scratch buffer and
+// nothing is allocated (no cudaMalloc / cudaFree, no allocating library call): the scratch is the
+// library's own fixed device array.
+//   * n is limited to 16 rows; larger n is refused with an error (use gb_pairwise_select).
+//   * The first call on each device resolves the array's device address (with that device
+//     current). Make that first call outside of any stream capture.
+//   * All calls on a device share the one array and it keeps whatever the previous call left; the
+//     words that must start at zero are cleared on `stream` before the kernel. Two calls that can
+//     overlap on the GPU (different streams, no dependency between them) therefore race on the
+//     scratch: serialise them.
+extern "C" GB_API int gb_pairwise_select_noalloc(float const* const* rows, int n, int64_t d, int mode, int f, int m, int neighbors,
+                                                 int squared, float* dist, float* W, int* info, void* stream) {
+    using namespace gb;
+    if (n < 1) return cuda_fail("no-alloc pairwise: need at least one row");
+    if (n > kStaticMaxRows) return cuda_fail("no-alloc pairwise: at most 16 rows fit the built-in scratch array; use gb_pairwise_select with a caller-provided buffer for larger n");
+    if (d < 1) return cuda_fail("no-alloc pairwise: empty rows");
+    if (dist == nullptr) return cuda_fail("no-alloc pairwise: missing distance output buffer");
+    if (mode != kSelectNone && (W == nullptr || info == nullptr)) return cuda_fail("no-alloc pairwise: selection needs W and info buffers");
+    switch (mode) {
+        case kSelectNone: break;
+        case kSelectKrum:
+            if (f < 1 || n < 2 * f + 3 || m < 1 || m > n - f - 2 || neighbors < 1 || neighbors > n - 1) return cuda_fail("no-alloc pairwise: invalid Krum parameters");
+            break;
+        case kSelectBulyanPython:
+        case kSelectBulyanNative:
+            if (f < 1 || n < 4 * f + 3 || m < 1 || m > n - f - 2) return cuda_fail("no-alloc pairwise: invalid Bulyan parameters");
+            break;
+        case kSelectMda:
+            if (f < 1 || n < 2 * f + 1) return cuda_fail("no-alloc pairwise: invalid MDA parameters");
+            break;  // C(16, k) <= 12870 subsets: always within the in-kernel search limit
+        case kSelectClosest:
+            if (n < 2 || m < 1 || m > n - 1) return cuda_fail("no-alloc pairwise: invalid closest-to-last parameters");
+            break;
+        default: return cuda_fail("no-alloc pairwise: unknown selection mode");
+    }
+    void* scratch = nullptr;
+    if (static_scratch_for_current_device(&scratch)) return 1;
+
+    PairwiseArgs a{};
+    for (int i = 0; i < n; ++i) a.rows.p[i] = rows[i];
+    a.n = n; a.d = d; a.dist = dist; a.W = W; a.info = info;
+    a.sel.mode = mode; a.sel.f = f; a.sel.m = m; a.sel.neighbors = neighbors; a.sel.squared = squared;
+    a.tile = pick_tile(n);
+    a.use_tma = rows_aligned(a.rows, n) ? 1 : 0;
+
+    int const nn = n * n;
+    int const slot_floats = ((kConsumerWarps * nn + 31) / 32) * 32;
+    size_t smem = sizeof(float) * (static_cast<size_t>(slot_floats) + static_cast<size_t>(kStages) * n * a.tile);
+    if (smem < sizeof(SelectScratch)) smem = sizeof(SelectScratch);
+    long long const tiles = (d + a.tile - 1) / a.tile;
+    int const ctas_per_sm = smem <= 100 * 1024 ? 2 : 1;
+    long long grid = static_cast<long long>(device_sm_count()) * ctas_per_sm;
+    long long const fit = (kStaticScratchBytes - 256) / (static_cast<long long>(nn) * static_cast<long long>(sizeof(float)));
+    if (grid > fit) grid = fit;  // a GPU with more SMs than a B200 simply runs fewer CTAs
+    if (grid > tiles) grid = tiles;
+    if (grid < 1) grid = 1;
+    a.counter = static_cast<unsigned int*>(scratch);
+    a.partials = reinterpret_cast<float*>(static_cast<unsigned char*>(scratch) + 256);
+
+    cudaStream_t const st = static_cast<cudaStream_t>(stream);
+    // the completion counter must be zero when the kernel starts, whatever an earlier call left behind
+    if (cuda_check(cudaMemsetAsync(scratch, 0, 256, st), "no-alloc pairwise: clearing the counter")) return 1;
+    auto kern = pairwise_kernel;
+    if (cuda_check(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)), "no-alloc pairwise: smem attribute")) return 1;
+    kern<<<static_cast<int>(grid), kThreads, smem, st>>>(a);
+    return cuda_check(cudaGetLastError(), "no-alloc pairwise: launch");
 }

@@ -119,6 +119,16 @@ GB_API int gb_coordwise(float const* const* rows, int n, int64_t d, int rule, in
 GB_API int64_t gb_pairwise_scratch_bytes(int n);
 GB_API int gb_pairwise_select(float const* const* rows, int n, int64_t d, int mode, int f, int m, int neighbors, int squared,
                               void* scratch, int64_t scratch_bytes, float* dist, float* W, int* info, void* stream);
+/* gb_pairwise_select for callers that may not allocate device memory (a process whose HBM was
+ * handed to its own pool at start-up, a loop under a fixed memory plan, a path that cannot take
+ * cudaMalloc's device-wide synchronisation): same outputs, no scratch argument, no allocation of
+ * any kind — the scratch is a fixed 303 360-byte device array inside the library, which limits
+ * n to 16 rows (larger n returns an error). The first call on each device looks up that array's
+ * device address: issue it with the device current and outside any stream capture. Calls share
+ * the array, so calls that may overlap on the GPU race — serialise them.
+ * This entry point has no counterpart in the reference. */
+GB_API int gb_pairwise_select_noalloc(float const* const* rows, int n, int64_t d, int mode, int f, int m, int neighbors,
+                                      int squared, float* dist, float* W, int* info, void* stream);
 
 /* Flat-arena optimizer steps (torch.optim semantics). ref: garfieldpp/server.py:277-287,
  * garfieldpp/tools.py:107-123 (sgd, adam, adamw, rmsprop, adagrad — run on the HOST there). */
