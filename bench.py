@@ -190,7 +190,9 @@ def run_ours(args):
             "dtype": "fp32 (TF32 convolutions = torch default, same as the reference)", "data": "synthetic",
             "impl": "ours",
             "config": {"model": "resnet50 (torchvision, 10 classes, 3x32x32 inputs)", "global_batch": N_WORKERS * BATCH,
-                       "seq_len": None, "parallelism": "ssmw n=8 f=1 over %d gpu(s), server on rank 0" % world,
+                       "seq_len": None, "parallelism": ("ssmw n=8 f=1 over %d gpu(s); workers r, r+N, ... on rank r; the server's aggregation + optimizer "
+                                       "are sharded by coordinate range over the ranks (peer-memory loads/stores)" % world) if world > 1
+                       else "ssmw n=8 f=1, all roles on 1 gpu",
                        "gar": args.gar, "optimizer": "sgd lr=0.2 momentum=0.9 wd=5e-4 (fused in the GAR epilogue)",
                        "l2": "per-step working set 8 x 94 MB gradient rows = 753 MB > 126 MB L2 (no flush needed)",
                        "d": primary["d"]},

@@ -23,6 +23,7 @@
 
 #include "../cpu/combinations.hpp"
 #include "gar_common.cuh"
+#include "gar_select.cuh"
 #include "garfield_b200.h"
 #include "launch.cuh"
 
@@ -110,191 +111,6 @@ __device__ __forceinline__ void flush(float (&acc)[kG][kG], int bi, int bj, int 
             if (lane == 0 && i < n && j < n && i < j) slot[i * n + j] += total;
             acc[r][c] = 0.0f;
         }
-}
-
-// ------------------------------------------------------------------------ selection ---
-
-struct SelectScratch {      // lives in dynamic shared memory of the last CTA (ring is idle by then)
-    double D[kMaxRows * kMaxRows];       // distances used for scoring (sqrt applied when !squared)
-    double kept[kMaxRows * kMaxRows];    // Bulyan native: distances kept after pruning
-    double score[kMaxRows];
-    int order[kMaxRows];
-    double best_diam[kThreads];
-    unsigned long long best_pos[kThreads];
-};
-
-// lexicographic (non-finite last, score, index) comparison
-__device__ __forceinline__ bool before(double sa, int a, double sb, int b) {
-    bool const fa = isfinite(sa), fb = isfinite(sb);
-    if (fa != fb) return fa;
-    if (fa && sa != sb) return sa < sb;
-    return a < b;
-}
-
-// order[] = indices of rows [0, cnt) by increasing score (stable); executed by one warp.
-__device__ void rank_rows(SelectScratch& S, int cnt) {
-    int const lane = threadIdx.x & 31;
-    for (int i = lane; i < cnt; i += 32) {
-        int rank = 0;
-        for (int j = 0; j < cnt; ++j) rank += before(S.score[j], j, S.score[i], i) ? 1 : 0;
-        S.order[rank] = i;
-    }
-    __syncwarp();
-}
-
-// score_i = Σ of the k smallest D[i][j], j != i, j < cnt (ascending summation order).
-// `keep_out` (optional) receives the kept distances (Bulyan native pruning).
-__device__ void neighbour_scores(SelectScratch& S, int n, int cnt, int k, bool prune) {
-    int const lane = threadIdx.x & 31;
-    for (int i = lane; i < cnt; i += 32) {
-        double vals[kMaxRows];
-        int ids[kMaxRows];
-        int len = 0;
-        for (int j = 0; j < cnt; ++j) {
-            if (j == i) continue;
-            double const v = S.D[i * n + j];
-            int pos = len++;
-            while (pos > 0 && (vals[pos - 1] > v)) {  // insertion sort, stable in j
-                vals[pos] = vals[pos - 1];
-                ids[pos] = ids[pos - 1];
-                --pos;
-            }
-            vals[pos] = v;
-            ids[pos] = j;
-        }
-        double s = 0.0;
-        for (int t = 0; t < k && t < len; ++t) s += vals[t];
-        S.score[i] = s;
-        if (prune) {
-            for (int j = 0; j < cnt; ++j) S.kept[i * n + j] = 0.0;
-            for (int t = 0; t < k && t < len; ++t) S.kept[i * n + ids[t]] = vals[t];
-        }
-    }
-    __syncwarp();
-}
-
-// Runs in the last CTA. D2 (global, float) holds the final squared distances.
-__device__ void run_selection(PairwiseArgs const& a, SelectScratch& S) {
-    int const n = a.n;
-    SelectArgs const sel = a.sel;
-    int const tid = threadIdx.x;
-    if (sel.mode == kSelectNone) return;
-
-    for (int e = tid; e < n * n; e += blockDim.x) {
-        float const v = a.dist[e];
-        double dv = sel.squared ? static_cast<double>(v) : sqrt(static_cast<double>(v));
-        // native MDA counts a non-finite distance as the largest finite one instead of skipping the subset
-        if (sel.mode == kSelectMda && sel.squared && !isfinite(dv) && (e / n) != (e % n)) dv = DBL_MAX;
-        S.D[e] = dv;
-    }
-    int const theta = (sel.mode == kSelectBulyanPython || sel.mode == kSelectBulyanNative) ? n - 2 * sel.f - 2 : 1;
-    for (int e = tid; e < theta * n; e += blockDim.x) a.W[e] = 0.0f;
-    __syncthreads();
-
-    if (sel.mode == kSelectMda) {
-        // every thread scans a contiguous range of subset ranks; strict '<' keeps the first minimum
-        unsigned const k = static_cast<unsigned>(n - sel.f);
-        unsigned long long const total = binomial(static_cast<unsigned>(n), k);
-        unsigned long long const lo = total * tid / blockDim.x, hi = total * (tid + 1ull) / blockDim.x;
-        double best = INFINITY;
-        unsigned long long best_pos = ~0ull;
-        if (lo < hi) {
-            int idx[kMaxRows];
-            combination_unrank(static_cast<unsigned>(n), k, lo, idx);
-            for (unsigned long long pos = lo; pos < hi; ++pos) {
-                double diam = 0.0;
-                for (unsigned x = 0; x + 1 < k; ++x)
-                    for (unsigned y = x + 1; y < k; ++y) diam = fmax(diam, S.D[idx[x] * n + idx[y]]);
-                if (diam < best) {
-                    best = diam;
-                    best_pos = pos;
-                }
-                combination_next(static_cast<unsigned>(n), k, idx);
-            }
-        }
-        S.best_diam[tid] = best;
-        S.best_pos[tid] = best_pos;
-        __syncthreads();
-        if (tid == 0) {
-            double win = INFINITY;
-            unsigned long long win_pos = ~0ull;
-            for (unsigned t = 0; t < blockDim.x; ++t)  // ranges are in rank order: first strict minimum wins
-                if (S.best_diam[t] < win) {
-                    win = S.best_diam[t];
-                    win_pos = S.best_pos[t];
-                }
-            a.info[0] = 1;
-            if (win_pos != ~0ull) {
-                int idx[kMaxRows];
-                combination_unrank(static_cast<unsigned>(n), k, win_pos, idx);
-                for (unsigned x = 0; x < k; ++x) {
-                    a.W[idx[x]] = 1.0f / static_cast<float>(k);
-                    a.info[1 + x] = idx[x];
-                }
-            }
-        }
-        return;
-    }
-
-    if (tid >= 32) return;  // the remaining modes need one warp
-    int const lane = tid;
-
-    if (sel.mode == kSelectClosest) {
-        int const cnt = n - 1;  // the last row is the reference vector
-        for (int i = lane; i < cnt; i += 32) S.score[i] = S.D[i * n + (n - 1)];
-        __syncwarp();
-        rank_rows(S, cnt);
-        for (int r = lane; r < sel.m; r += 32) {
-            a.W[S.order[r]] = 1.0f / static_cast<float>(sel.m);
-            a.info[1 + r] = S.order[r];
-        }
-        if (lane == 0) a.info[0] = 1;
-        return;
-    }
-
-    if (sel.mode == kSelectKrum) {
-        neighbour_scores(S, n, n, sel.neighbors, false);
-        rank_rows(S, n);
-        for (int r = lane; r < sel.m; r += 32) {
-            a.W[S.order[r]] = 1.0f / static_cast<float>(sel.m);
-            a.info[1 + r] = S.order[r];
-        }
-        if (lane == 0) a.info[0] = 1;
-        return;
-    }
-
-    int const m_max = n - sel.f - 2;
-    if (sel.mode == kSelectBulyanPython) {
-        neighbour_scores(S, n, n, sel.m, false);  // python Bulyan sums the m nearest
-        rank_rows(S, n);                          // scores are never updated (reference quirk Q2)
-        for (int r = 0; r < theta; ++r) {
-            int const take = min(sel.m, m_max - r);
-            for (int t = lane; t < take; t += 32) a.W[r * n + S.order[r + t]] = 1.0f / static_cast<float>(take);
-        }
-        for (int t = lane; t < min(sel.m, m_max); t += 32) a.info[1 + t] = S.order[t];
-        if (lane == 0) a.info[0] = theta;
-        return;
-    }
-
-    // kSelectBulyanNative: real score updates with pruned distances
-    neighbour_scores(S, n, n, m_max, true);
-    for (int r = 0; r < theta; ++r) {
-        rank_rows(S, n);
-        int const take = sel.m - r;
-        for (int t = lane; t < take; t += 32) a.W[r * n + S.order[t]] = 1.0f / static_cast<float>(take);
-        if (r == 0)
-            for (int t = lane; t < take; t += 32) a.info[1 + t] = S.order[t];
-        __syncwarp();
-        if (r + 1 >= theta) break;
-        int const gone = S.order[0];
-        __syncwarp();
-        for (int i = lane; i < n; i += 32) {
-            if (i == gone) S.score[i] = INFINITY;
-            else if (isfinite(S.score[i])) S.score[i] -= S.kept[i * n + gone];
-        }
-        __syncwarp();
-    }
-    if (lane == 0) a.info[0] = theta;
 }
 
 // ------------------------------------------------------------------------- kernel ---
@@ -514,6 +330,54 @@ extern "C" GB_API int gb_pairwise_select(float const* const* rows, int n, int64_
     return cuda_check(cudaGetLastError(), "pairwise launch");
 }
 
+
+// ------------------------------------------------------------------ selection only ---
+//
+// Coordinate-sharded aggregation (garfield_b200/parallel/engine.py): every GPU computes the
+// PARTIAL squared distances of its coordinate slice, the n×n partials are summed across GPUs
+// (n² floats), and each GPU then runs this one-CTA kernel on the summed matrix to obtain the
+// (identical) averaging weights for its slice. Same selection code as the fused kernels.
+namespace gb {
+namespace {
+struct SelectOnlyArgs {
+    int n;
+    float* dist;
+    float* W;
+    int* info;
+    SelectArgs sel;
+};
+__global__ void __launch_bounds__(kThreads) select_only_kernel(const __grid_constant__ SelectOnlyArgs a) {
+    extern __shared__ __align__(128) unsigned char smem_raw[];
+    int const nn = a.n * a.n;
+    for (int e = threadIdx.x; e < nn; e += blockDim.x) {  // normalise: +inf diagonal, non-finite → +inf
+        float const v = a.dist[e];
+        bool const diag = (e / a.n) == (e % a.n);
+        a.dist[e] = (!diag && fabsf(v) <= FLT_MAX) ? v : INFINITY;
+    }
+    __syncthreads();
+    run_selection(a, *reinterpret_cast<SelectScratch*>(smem_raw));
+}
+}  // namespace
+}  // namespace gb
+
+extern "C" GB_API int gb_select_only(float* dist, int n, int mode, int f, int m, int neighbors, int squared, float* W, int* info, void* stream) {
+    using namespace gb;
+    if (n < 1 || n > kMaxRows) return cuda_fail("select_only: need 1 <= n <= 64 rows");
+    if (dist == nullptr || W == nullptr || info == nullptr) return cuda_fail("select_only: missing buffers");
+    if (mode == kSelectMda) {
+        bool over = false;
+        unsigned long long const total = binomial(static_cast<unsigned>(n), static_cast<unsigned>(n - f), &over);
+        if (f < 1 || n < 2 * f + 1 || over || total > (1ull << 26)) return cuda_fail("select_only: invalid or too large MDA problem");
+    }
+    SelectOnlyArgs a{};
+    a.n = n; a.dist = dist; a.W = W; a.info = info;
+    a.sel.mode = mode; a.sel.f = f; a.sel.m = m; a.sel.neighbors = neighbors; a.sel.squared = squared;
+    auto kern = select_only_kernel;
+    size_t const smem = sizeof(SelectScratch);
+    if (cuda_check(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)), "select_only smem attribute")) return 1;
+    kern<<<1, kThreads, smem, static_cast<cudaStream_t>(stream)>>>(a);
+    return cuda_check(cudaGetLastError(), "select_only launch");
+}
 
 // ------------------------------------------------------------- allocation-free variant ---
 //

@@ -32,6 +32,10 @@ def _declare(h):
     h.gb_pairwise_scratch_bytes.restype = i64
     h.gb_pairwise_scratch_bytes.argtypes = [i32]
     h.gb_pairwise_select.argtypes = [pp, i32, i64, i32, i32, i32, i32, i32, vp, i64, vp, vp, vp, vp]
+    h.gb_gram_scratch_bytes.restype = i64
+    h.gb_gram_scratch_bytes.argtypes = [i32]
+    h.gb_gram_select_tc.argtypes = [pp, i32, i64, i32, i32, i32, i32, i32, vp, i64, vp, vp, vp, vp]
+    h.gb_select_only.argtypes = [vp, i32, i32, i32, i32, i32, i32, vp, vp, vp]
     h.gb_sgd_step.argtypes = [vp, vp, vp, i64, f32, f32, f32, f32, i32, i32, pp, i32, vp]
     h.gb_adam_step.argtypes = [vp, vp, vp, vp, i64, f32, f32, f32, f32, f32, i32, i32, vp]
     h.gb_rmsprop_step.argtypes = [vp, vp, vp, vp, i64, f32, f32, f32, f32, f32, vp]

@@ -111,12 +111,28 @@ def coordwise(gradients, rule, f=0, beta=0, upper=False, p=0.9, seed=0, W=None, 
     return out
 
 
-def select(gradients, mode, f=0, m=0, neighbors=0, squared=True):
+TENSOR_CORE_MIN_ROWS = [17]  # `engine="auto"` uses the tcgen05 Gram kernel from this many rows (<= 32)
+
+
+def select(gradients, mode, f=0, m=0, neighbors=0, squared=True, engine="auto"):
     """Distances + selection in one launch. Returns the device workspace dict with
-    `dist` (n×n), `W` (n×n buffer, first θ rows valid) and `info`."""
+    `dist` (n×n), `W` (n×n buffer, first θ rows valid) and `info`.
+
+    engine: "simt" = exact direct-difference kernel, "tc" = tcgen05 TF32 Gram kernel (2..32
+    aligned rows), "auto" = tc for TENSOR_CORE_MIN_ROWS <= n <= 32 when the rows qualify."""
     rows, n, d, device = _prep(gradients)
     lib = _lib.require()
     ws = _Workspace.get(device, n)
+    aligned = all(r.data_ptr() % 16 == 0 for r in rows)
+    use_tc = engine == "tc" or (engine == "auto" and TENSOR_CORE_MIN_ROWS[0] <= n <= 32 and aligned and d >= 4096)
+    if use_tc:
+        with torch.cuda.device(device):
+            _lib.check(lib.gb_gram_select_tc(
+                _lib.row_table(rows), n, d, MODES[mode], int(f), int(m), int(neighbors), int(bool(squared)),
+                ws["scratch"].data_ptr(), ws["scratch"].numel(), ws["dist"].data_ptr(), ws["W"].data_ptr(),
+                ws["info"].data_ptr(), _lib.stream_ptr(device)))
+        _lib.count()
+        return ws
     with torch.cuda.device(device):
         _lib.check(lib.gb_pairwise_select(
             _lib.row_table(rows), n, d, MODES[mode], int(f), int(m), int(neighbors), int(bool(squared)),
@@ -126,9 +142,9 @@ def select(gradients, mode, f=0, m=0, neighbors=0, squared=True):
     return ws
 
 
-def pairwise_sqdist(gradients):
+def pairwise_sqdist(gradients, engine="simt"):
     """n×n matrix of squared L2 distances (device tensor; +inf diagonal and non-finite)."""
-    return select(gradients, "none")["dist"].clone()
+    return select(gradients, "none", engine=engine)["dist"].clone()
 
 
 def weighted(gradients, W, theta=1, **kw):
@@ -210,3 +226,55 @@ def aggregate(name, gradients, f, m=None, update=None, want_out=True, **kw):
         mode = kw.get("mode", "mid")
         return aksel(gradients, (n + 1) // 2 if mode == "mid" else n - f, **common)
     raise KeyError("unknown aggregation rule %r" % (name,))
+
+
+def select_only(ws, n, device, mode, f=0, m=0, neighbors=0, squared=True):
+    """Run the selection logic on `ws["dist"]` (already summed over shards) → `ws["W"]`."""
+    lib = _lib.require()
+    with torch.cuda.device(device):
+        _lib.check(lib.gb_select_only(ws["dist"].data_ptr(), n, MODES[mode], int(f), int(m), int(neighbors), int(bool(squared)),
+                                      ws["W"].data_ptr(), ws["info"].data_ptr(), _lib.stream_ptr(device)))
+    _lib.count()
+    return ws
+
+
+_DISTANCE_RULES = {
+    # name: (selection mode, squared/native flag, neighbours(n, f), phase-2 builder)
+    "krum": ("krum", False), "native-krum": ("krum", True), "bulyan": ("bulyan_python", False),
+    "native-bulyan": ("bulyan_native", True), "brute": ("mda", False), "mda": ("mda", False), "native-brute": ("mda", True),
+}
+
+
+def aggregate_sharded(name, slice_rows, f, allreduce, m=None, update=None, want_out=True, **kw):
+    """Coordinate-sharded form of `aggregate`: `slice_rows` are this rank's coordinate slice of the
+    n gradients; `allreduce(tensor)` sums a small device tensor over the ranks in place.
+
+    Per-coordinate rules need no communication. Distance-based rules compute the partial squared
+    distances of the slice, all-reduce the n×n matrix, run the (replicated) selection and apply the
+    resulting weights to the slice — the robust analogue of a reduce-scatter."""
+    n = len(slice_rows)
+    common = dict(update=update, want_out=want_out)
+    if name == "aksel":
+        med = coordwise(slice_rows, "median_lower")
+        rows = list(slice_rows) + [med]
+        ws = select(rows, "none", engine="simt")
+        allreduce(ws["dist"])
+        mode = kw.get("mode", "mid")
+        select_only(ws, n + 1, rows[0].device, "closest", m=(n + 1) // 2 if mode == "mid" else n - f, squared=True)
+        return coordwise(rows, "linear", W=ws["W"], theta=1, **common)
+    if name not in _DISTANCE_RULES:
+        return aggregate(name, slice_rows, f, m=m, **common, **kw)
+    mode, native = _DISTANCE_RULES[name]
+    ws = select(slice_rows, "none", engine=kw.get("engine", "auto"))
+    allreduce(ws["dist"])
+    device = slice_rows[0].device
+    m_eff = n - f - 2 if m is None else m
+    if mode == "krum":
+        select_only(ws, n, device, "krum", f=f, m=m_eff, neighbors=n - f - 2 if native else n - f - 1, squared=native)
+        return coordwise(slice_rows, "linear", W=ws["W"], theta=1, **common)
+    if mode == "mda":
+        select_only(ws, n, device, "mda", f=f, squared=native)
+        return coordwise(slice_rows, "linear", W=ws["W"], theta=1, **common)
+    theta = n - 2 * f - 2
+    select_only(ws, n, device, mode, f=f, m=m_eff, squared=native)
+    return coordwise(slice_rows, "averaged_median", beta=theta - 2 * f, upper=native, W=ws["W"], theta=theta, **common)

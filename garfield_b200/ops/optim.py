@@ -92,6 +92,17 @@ class FlatOptimizer(torch.optim.Optimizer):
     def note_fused_step(self):
         self.steps += 1
 
+    def rebind(self, flat_param):
+        """Continue optimising another flat tensor of the same shape (double-buffered arenas):
+        hyper-parameters, step count and state buffers are kept."""
+        if flat_param.shape != self.param.shape:
+            raise ValueError("rebind needs a tensor of the same shape")
+        slot = self.state.pop(self.param, {})
+        self.param = flat_param
+        self.param_groups[0]["params"] = [flat_param]
+        self.state[flat_param] = slot
+        return self
+
     # -- the update ------------------------------------------------------------------------
     @torch.no_grad()
     def step(self, grad=None, mirrors=()):

@@ -38,9 +38,11 @@ __all__ = ["SSMWEngine"]
 class _LocalWorker:
     """One worker hosted by this rank: model replica, static input buffers, gradient row."""
 
-    def __init__(self, wid, replica, row, loss_fn, batch_shape, target_shape, target_dtype, device, attack=None):
+    def __init__(self, wid, replica, row, loss_fn, batch_shape, target_shape, target_dtype, device, attack=None, channels_last=False):
         self.wid, self.replica, self.row, self.loss_fn, self.attack = wid, replica, row, loss_fn, attack
         self.data = torch.zeros(batch_shape, device=device)
+        if channels_last and len(batch_shape) == 4:
+            self.data = self.data.contiguous(memory_format=torch.channels_last)
         self.target = torch.zeros(target_shape, dtype=target_dtype, device=device)
         self.loss = torch.zeros((), device=device)
         self.stream = torch.cuda.Stream(device=device) if device.type == "cuda" else None
@@ -56,7 +58,8 @@ class _LocalWorker:
 
 class SSMWEngine:
     def __init__(self, model, dataset, loss, num_workers, f, gar, batch, optimizer="sgd", opt_args=None, byzantine=None,
-                 device=None, group=None, use_graphs=True, train_set=None, seed=1234, gar_kwargs=None):
+                 device=None, group=None, use_graphs=True, train_set=None, seed=1234, gar_kwargs=None, sharded=None,
+                 channels_last=True):
         self.rank = dist.get_rank(group) if dist.is_initialized() else 0
         self.world = dist.get_world_size(group) if dist.is_initialized() else 1
         self.group = group
@@ -64,12 +67,18 @@ class SSMWEngine:
         self.n, self.f, self.gar_name, self.batch = num_workers, f, gar, batch
         self.gar_kwargs = dict(gar_kwargs or {})
         self.byzantine = dict(byzantine or {})
-        self.is_server = self.rank == 0
+        # sharded=True: the (trusted) server's aggregation, optimizer state and publication are split by
+        # coordinate range over all ranks — same result, balanced NVLink traffic.
+        self.sharded = (self.world > 1) if sharded is None else (bool(sharded) and self.world > 1)
+        self.is_server = self.rank == 0 or self.sharded
         if self.device.type != "cuda" or not gar_ops.available():
             raise RuntimeError("SSMWEngine needs a CUDA device and the sm_100a library")
 
         torch.manual_seed(seed)
         module = tools.select_model(model, self.device, dataset)
+        self.channels_last = bool(channels_last)
+        if self.channels_last:
+            module = module.to(memory_format=torch.channels_last)
         self.d = sum(p.numel() for p in module.parameters())
         self.pitch = (self.d + 63) // 64 * 64
         self.local_ids = [w for w in range(self.n) if w % self.world == self.rank]
@@ -79,38 +88,46 @@ class SSMWEngine:
         self.param_arena = PeerArena(self.pitch, self.device, group)
         self.grad_arena = PeerArena(self.max_local * self.pitch, self.device, group)
         self.flat = self.param_arena.local[:self.d]
-        self.master = FlatModel(module, self.device, flat=None)
+        self.master = FlatModel(module, self.device, flat=None, channels_last=self.channels_last)
         if self.world > 1:  # everyone starts from rank 0's initialisation
             dist.broadcast(self.master.flat, src=0, group=group)
             for buf in self.master.module.buffers():
                 dist.broadcast(buf, src=0, group=group)
         self.flat.copy_(self.master.flat)
-        self.master = FlatModel(module, self.device, flat=self.flat)  # re-alias onto the arena
+        self.master = FlatModel(module, self.device, flat=self.flat, channels_last=self.channels_last)  # re-alias onto the arena
 
         loss_fn = tools.select_loss(loss)
         self.train_sets = {}
         self.workers = []
         for j, wid in enumerate(self.local_ids):
-            replica = FlatModel(copy.deepcopy(module), self.device, flat=self.flat)
+            replica = FlatModel(copy.deepcopy(module), self.device, flat=self.flat, channels_last=self.channels_last)
             row = self.grad_arena.local[j * self.pitch:j * self.pitch + self.d]
             if train_set is not None:
                 batches = train_set(wid)
             else:
                 batches = DatasetManager(dataset, batch, self.n, self.n + 1, wid + 1).get_train_set()
+            if self.channels_last and batches[0][0].dim() == 4:  # host batches in NHWC so the H2D copy is a plain memcpy
+                batches = [(self._pin(x.contiguous(memory_format=torch.channels_last)), y) for x, y in batches]
             self.train_sets[wid] = batches
             x0, y0 = batches[0]
             self.workers.append(_LocalWorker(wid, replica, row, loss_fn, tuple(x0.shape), tuple(y0.shape), y0.dtype, self.device,
-                                             attack=self.byzantine.get(wid)))
+                                             attack=self.byzantine.get(wid), channels_last=self.channels_last))
 
-        # server state
-        self.optimizer = FlatOptimizer(self.flat, optimizer, **(opt_args or {})) if self.is_server else None
-        self.rows = None
-        if self.is_server:
+        # server state (whole vector on rank 0, or this rank's coordinate slice when sharded)
+        if self.sharded:
+            per = (self.pitch // 64 + self.world - 1) // self.world * 64   # slice length, multiple of 64 floats
+            self.lo = min(self.d, self.rank * per)
+            self.hi = min(self.d, self.lo + per)
+        else:
+            self.lo, self.hi = 0, self.d
+        self.optimizer, self.rows = None, None
+        if self.is_server and self.hi > self.lo:
+            self.optimizer = FlatOptimizer(self.flat[self.lo:self.hi], optimizer, **(opt_args or {}))
             self.rows = []
             for wid in range(self.n):
                 owner, j = wid % self.world, wid // self.world
-                self.rows.append(self.grad_arena.peer(owner)[j * self.pitch:j * self.pitch + self.d])
-            self.mirrors = [self.param_arena.peer(r)[:self.d] for r in range(self.world) if r != self.rank]
+                self.rows.append(self.grad_arena.peer(owner)[j * self.pitch + self.lo:j * self.pitch + self.hi])
+            self.mirrors = [self.param_arena.peer(r)[self.lo:self.hi] for r in range(self.world) if r != self.rank]
         self._flag = torch.zeros(1, device=self.device)
         self._graph = None
         self.use_graphs = use_graphs
@@ -118,6 +135,10 @@ class SSMWEngine:
         self.h2d_bytes = 0
 
     # ------------------------------------------------------------------------------------------
+    @staticmethod
+    def _pin(tensor):
+        return tensor.pin_memory() if torch.cuda.is_available() else tensor
+
     def _barrier(self):
         if self.world > 1:
             dist.all_reduce(self._flag, group=self.group)
@@ -182,16 +203,24 @@ class SSMWEngine:
         else:
             raise ValueError("unknown attack %r" % (w.attack,))
 
+    def _allreduce(self, tensor):
+        dist.all_reduce(tensor, group=self.group)
+
     def aggregate_and_update(self):
-        """Server only: fused gather + GAR + optimizer step + parameter publication."""
+        """Server side: fused gather + GAR + optimizer step + parameter publication, on the whole
+        vector (rank 0) or on this rank's coordinate slice (sharded)."""
         opt = self.optimizer
+        if self.sharded:
+            if opt is None:  # empty slice: still take part in the distance all-reduce
+                raise RuntimeError("empty coordinate slice: use fewer ranks than d / 64")
+            run = lambda **kw: gar_ops.aggregate_sharded(self.gar_name, self.rows, self.f, self._allreduce, **kw, **self.gar_kwargs)
+        else:
+            run = lambda **kw: gar_ops.aggregate(self.gar_name, self.rows, self.f, **kw, **self.gar_kwargs)
         if opt.name == "sgd":
-            gar_ops.aggregate(self.gar_name, self.rows, self.f, update=opt.sgd_fusion(self.mirrors), want_out=False,
-                              **self.gar_kwargs)
+            run(update=opt.sgd_fusion(self.mirrors), want_out=False)
             opt.note_fused_step()
         else:
-            grad = gar_ops.aggregate(self.gar_name, self.rows, self.f, **self.gar_kwargs)
-            opt.step(grad, mirrors=self.mirrors)
+            opt.step(run(), mirrors=self.mirrors)
 
     def step(self, iter_num, load=True):
         """One training iteration. Returns the mean loss of this rank's workers (device scalar)."""

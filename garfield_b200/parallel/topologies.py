@@ -1,0 +1,309 @@
+"""Device-resident engines for the replicated-server (MSMW / ByzSGD) and decentralized (LEARN)
+topologies, built from the same fused gather+GAR kernels as the SSMW engine.
+
+Every model replica lives in a peer-mapped parameter arena, every gradient in a peer-mapped
+gradient row; "pulling" a peer's model or gradient is just putting its peer pointer in the row
+table of an aggregation kernel, so the reference's
+
+    models = ps.get_models(num_ps - fps);  ps.write_model(gar(models, f=fps))        (ByzSGD/trainer.py:241-244)
+    models = ps.get_models(n - f) → gar → ps.write_model      ("contract", LEARN/trainer.py:252-258)
+    aggr_grads = ps.get_aggr_grads(n - f) → gar               (avg_agree, LEARN/trainer.py:208-222)
+
+each become ONE kernel whose loads go over NVLink (north-star paths 3 and 4). Results are written
+into the second half of a double-buffered arena, so peers still reading the previous model are
+never raced; buffers swap after a barrier.
+
+Replica placement: replica k (server or node) lives on rank k mod world, so the engines also run
+on a single GPU (all replicas co-located), which is how the GPU tests exercise them.
+"""
+
+from __future__ import annotations
+
+import copy
+import math
+
+import torch
+import torch.distributed as dist
+
+from .arena import FlatModel
+from .peer import PeerArena
+from ..garfieldpp import tools
+from ..garfieldpp.datasets import DatasetManager
+from ..ops import attacks, gar as gar_ops
+from ..ops.optim import FlatOptimizer
+
+__all__ = ["DecentralizedEngine", "MSMWEngine"]
+
+
+class _Base:
+    def _init_dist(self, group, device):
+        self.group = group
+        self.rank = dist.get_rank(group) if dist.is_initialized() else 0
+        self.world = dist.get_world_size(group) if dist.is_initialized() else 1
+        self.device = torch.device(device) if device is not None else torch.device("cuda", torch.cuda.current_device())
+        self._flag = torch.zeros(1, device=self.device)
+        if not gar_ops.available():
+            raise RuntimeError("the device engines need a CUDA device and the sm_100a library")
+
+    def _barrier(self):
+        if self.world > 1:
+            dist.all_reduce(self._flag, group=self.group)
+
+    @staticmethod
+    def _attack_row(kind, row, honest_rows):
+        if kind == "random":
+            row.copy_(attacks.random_like(row))
+        elif kind == "reverse":
+            row.copy_(attacks.reverse(row))
+        elif kind == "drop":
+            row.copy_(attacks.drop(row))
+        elif kind == "lie":
+            row.copy_(attacks.lie(honest_rows or [row]))
+        elif kind == "empire":
+            row.copy_(attacks.empire(honest_rows or [row]))
+        else:
+            raise ValueError("unknown attack %r" % (kind,))
+
+
+class DecentralizedEngine(_Base):
+    """LEARN: n nodes, each a worker + a server with ITS OWN model replica.
+
+    Per step and node: gradient on the node's own model → every node aggregates ALL nodes' gradients
+    (fused peer gather + GAR) → optional ⌈log2(i+1)⌉ agreement rounds on the aggregated gradients
+    (`non_iid`) → SGD step → contract: every node replaces its model by the GAR of all nodes' models.
+    Each worker computes ONE gradient per step (on its own node's model) that all nodes pull; the
+    reference instead lets every server request a fresh gradient from every worker (n² backward
+    passes) — equivalent when replicas agree, which the contract step enforces.
+    """
+
+    def __init__(self, model, dataset, loss, num_nodes, f, gar, batch, optimizer="sgd", opt_args=None, byzantine=None,
+                 non_iid=False, device=None, group=None, seed=1234):
+        self._init_dist(group, device)
+        self.n, self.f, self.gar_name, self.non_iid = num_nodes, f, gar, non_iid
+        self.byzantine = dict(byzantine or {})
+        torch.manual_seed(seed)
+        module = tools.select_model(model, self.device, dataset)
+        self.d = sum(p.numel() for p in module.parameters())
+        self.pitch = (self.d + 63) // 64 * 64
+        self.local_ids = [k for k in range(self.n) if k % self.world == self.rank]
+        slots = (self.n + self.world - 1) // self.world
+        self.slots = slots
+        # per node: 2 parameter buffers (double-buffered), 1 gradient row, 2 aggregated-gradient buffers
+        self.params = PeerArena(slots * 2 * self.pitch, self.device, group)
+        self.grads = PeerArena(slots * self.pitch, self.device, group)
+        self.aggrs = PeerArena(slots * 2 * self.pitch, self.device, group)
+        init = FlatModel(module, self.device)
+        if self.world > 1:
+            dist.broadcast(init.flat, src=0, group=group)
+        self.cur = 0            # which parameter buffer is live
+        loss_fn = tools.select_loss(loss)
+        self.nodes = []
+        for j, k in enumerate(self.local_ids):
+            live = self._param(self.rank, j, 0)
+            live.copy_(init.flat)
+            self._param(self.rank, j, 1).copy_(init.flat)
+            replica = FlatModel(copy.deepcopy(module), self.device, flat=live)
+            batches = DatasetManager(dataset, batch, self.n, self.n, k).get_train_set()
+            opt = FlatOptimizer(live, optimizer, **(opt_args or {}))
+            self.nodes.append(dict(id=k, slot=j, replica=replica, batches=batches, opt=opt, loss_fn=loss_fn,
+                                   attack=self.byzantine.get(k), loss=torch.zeros((), device=self.device)))
+        self.steps_done = 0
+
+    # arena views -----------------------------------------------------------------------------
+    def _param(self, rank, slot, which):
+        base = (slot * 2 + which) * self.pitch
+        return self.params.peer(rank)[base:base + self.d]
+
+    def _grad(self, rank, slot):
+        return self.grads.peer(rank)[slot * self.pitch:slot * self.pitch + self.d]
+
+    def _aggr(self, rank, slot, which):
+        base = (slot * 2 + which) * self.pitch
+        return self.aggrs.peer(rank)[base:base + self.d]
+
+    def _all(self, getter, *extra):
+        return [getter(k % self.world, k // self.world, *extra) for k in range(self.n)]
+
+    def model_of(self, node_index):
+        """Live flat model of local node `node_index` (position in local_ids)."""
+        return self._param(self.rank, self.nodes[node_index]["slot"], self.cur)
+
+    # step ------------------------------------------------------------------------------------
+    def step(self, iter_num):
+        n, f = self.n, self.f
+        # 1. local gradients (on each node's own live model)
+        for node in self.nodes:
+            row = self._grad(self.rank, node["slot"])
+            replica = node["replica"]
+            row.zero_()
+            replica.bind_grads(row)
+            data, target = node["batches"][iter_num % len(node["batches"])]
+            replica.module.train()
+            loss = node["loss_fn"](replica.module(data.to(self.device, non_blocking=True)), target.to(self.device, non_blocking=True))
+            loss.backward()
+            replica.unbind_grads()
+            node["loss"].copy_(loss.detach())
+        for node in self.nodes:
+            if node["attack"]:
+                honest = [self._grad(self.rank, o["slot"]) for o in self.nodes if not o["attack"]]
+                self._attack_row(node["attack"], self._grad(self.rank, node["slot"]), honest)
+        self._barrier()
+        # 2. every node aggregates all nodes' gradients (peer pointers → fused gather + GAR)
+        rounds = int(math.ceil(math.log2(iter_num + 1))) if (self.non_iid and iter_num > 0) else 0
+        rows = self._all(self._grad)
+        which = 0
+        for node in self.nodes:
+            out = self._aggr(self.rank, node["slot"], which)
+            out.copy_(gar_ops.aggregate(self.gar_name, rows, f))
+        # 3. agreement rounds on the aggregated gradients (double-buffered)
+        for _ in range(rounds):
+            self._barrier()
+            peers = self._all(self._aggr, which)
+            for node in self.nodes:
+                self._aggr(self.rank, node["slot"], 1 - which).copy_(gar_ops.aggregate(self.gar_name, peers, f))
+            which = 1 - which
+        # 4. optimizer step on each node's live model
+        for node in self.nodes:
+            node["opt"].step(self._aggr(self.rank, node["slot"], which))
+        self._barrier()
+        # 5. contract: model := GAR(all nodes' live models), written into the other buffer
+        models = self._all(self._param, self.cur)
+        for node in self.nodes:
+            self._param(self.rank, node["slot"], 1 - self.cur).copy_(gar_ops.aggregate(self.gar_name, models, f))
+        self._barrier()
+        self.cur = 1 - self.cur
+        for node in self.nodes:  # re-alias replicas and optimizers onto the now-live buffer
+            live = self._param(self.rank, node["slot"], self.cur)
+            node["replica"] = FlatModel(node["replica"].module, self.device, flat=live)
+            node["opt"].rebind(live)
+        self.steps_done += 1
+        return torch.stack([node["loss"] for node in self.nodes]).mean() if self.nodes else torch.zeros((), device=self.device)
+
+    def close(self):
+        torch.cuda.synchronize(self.device)
+        for arena in (self.aggrs, self.grads, self.params):
+            arena.close()
+
+
+class MSMWEngine(_Base):
+    """ByzSGD: `num_ps` server replicas (possibly Byzantine) + `num_workers` workers.
+
+    Per step: every worker first pulls the live models of ALL servers and takes their
+    coordinate-wise median (fused peer gather + median straight into the worker's model — path 3),
+    computes its gradient on that model; every server aggregates all workers' gradients with the
+    gradient GAR and steps; then every server replaces its model by the model GAR of all servers'
+    models (double-buffered). Byzantine servers publish an attacked model instead of their own.
+    """
+
+    def __init__(self, model, dataset, loss, num_workers, num_ps, fw, fps, gar, batch, mar="median", optimizer="sgd", opt_args=None,
+                 byzantine_workers=None, byzantine_servers=None, device=None, group=None, seed=1234):
+        self._init_dist(group, device)
+        self.n, self.num_ps, self.fw, self.fps = num_workers, num_ps, fw, fps
+        self.gar_name, self.mar_name = gar, mar
+        self.byz_w, self.byz_s = dict(byzantine_workers or {}), dict(byzantine_servers or {})
+        torch.manual_seed(seed)
+        module = tools.select_model(model, self.device, dataset)
+        self.d = sum(p.numel() for p in module.parameters())
+        self.pitch = (self.d + 63) // 64 * 64
+        self.local_workers = [w for w in range(self.n) if w % self.world == self.rank]
+        self.local_servers = [s for s in range(num_ps) if s % self.world == self.rank]
+        w_slots = (self.n + self.world - 1) // self.world
+        s_slots = (num_ps + self.world - 1) // self.world
+        self.grads = PeerArena(w_slots * self.pitch, self.device, group)
+        self.wmodels = PeerArena(max(1, w_slots) * self.pitch, self.device, group)      # workers' private models (local use only)
+        self.smodels = PeerArena(s_slots * 3 * self.pitch, self.device, group)          # per server: 2 model buffers + 1 published copy
+        init = FlatModel(module, self.device)
+        if self.world > 1:
+            dist.broadcast(init.flat, src=0, group=group)
+        loss_fn = tools.select_loss(loss)
+        self.cur = 0
+        self.workers, self.servers = [], []
+        for j, w in enumerate(self.local_workers):
+            mine = self.wmodels.local[j * self.pitch:j * self.pitch + self.d]
+            mine.copy_(init.flat)
+            replica = FlatModel(copy.deepcopy(module), self.device, flat=mine)
+            batches = DatasetManager(dataset, batch, self.n, self.n + num_ps, w + num_ps).get_train_set()
+            self.workers.append(dict(id=w, slot=j, replica=replica, batches=batches, loss_fn=loss_fn, attack=self.byz_w.get(w),
+                                     loss=torch.zeros((), device=self.device)))
+        for j, s in enumerate(self.local_servers):
+            for which in range(3):
+                self._smodel(self.rank, j, which).copy_(init.flat)
+            opt = FlatOptimizer(self._smodel(self.rank, j, 0), optimizer, **(opt_args or {}))
+            self.servers.append(dict(id=s, slot=j, opt=opt, attack=self.byz_s.get(s)))
+        self._barrier()
+
+    def _smodel(self, rank, slot, which):
+        base = (slot * 3 + which) * self.pitch
+        return self.smodels.peer(rank)[base:base + self.d]
+
+    def _published(self):
+        """What every server shows to its peers (slot 2): its live model, or an attack."""
+        return [self._smodel(s % self.world, s // self.world, 2) for s in range(self.num_ps)]
+
+    def _grad(self, rank, slot):
+        return self.grads.peer(rank)[slot * self.pitch:slot * self.pitch + self.d]
+
+    def server_model(self, index=0):
+        return self._smodel(self.rank, self.servers[index]["slot"], self.cur)
+
+    def step(self, iter_num):
+        # 0. servers publish (honest copy or attack) — previous step's barrier ordered the writes
+        for srv in self.servers:
+            live, shown = self._smodel(self.rank, srv["slot"], self.cur), self._smodel(self.rank, srv["slot"], 2)
+            shown.copy_(live)
+            if srv["attack"]:
+                self._attack_row(srv["attack"], shown, [live])
+        self._barrier()
+        published = self._published()
+        # 1. workers: model := median of all servers' published models (fused pull), then gradient
+        for wrk in self.workers:
+            mine = self.wmodels.local[wrk["slot"] * self.pitch:wrk["slot"] * self.pitch + self.d]
+            gar_ops.coordwise(published, "median_lower", out=mine) if self.num_ps > 1 else mine.copy_(published[0])
+            row = self._grad(self.rank, wrk["slot"])
+            row.zero_()
+            wrk["replica"].bind_grads(row)
+            data, target = wrk["batches"][iter_num % len(wrk["batches"])]
+            wrk["replica"].module.train()
+            loss = wrk["loss_fn"](wrk["replica"].module(data.to(self.device, non_blocking=True)), target.to(self.device, non_blocking=True))
+            loss.backward()
+            wrk["replica"].unbind_grads()
+            wrk["loss"].copy_(loss.detach())
+        for wrk in self.workers:
+            if wrk["attack"]:
+                honest = [self._grad(self.rank, o["slot"]) for o in self.workers if not o["attack"]]
+                self._attack_row(wrk["attack"], self._grad(self.rank, wrk["slot"]), honest)
+        self._barrier()
+        # 2. servers: aggregate all workers' gradients (peer rows) + fused SGD on the live model
+        rows = [self._grad(w % self.world, w // self.world) for w in range(self.n)]
+        for srv in self.servers:
+            opt = srv["opt"]
+            if opt.name == "sgd":
+                gar_ops.aggregate(self.gar_name, rows, self.fw, update=opt.sgd_fusion(), want_out=False)
+                opt.note_fused_step()
+            else:
+                opt.step(gar_ops.aggregate(self.gar_name, rows, self.fw))
+            self._smodel(self.rank, srv["slot"], 2).copy_(self._smodel(self.rank, srv["slot"], self.cur))
+            if srv["attack"]:
+                self._attack_row(srv["attack"], self._smodel(self.rank, srv["slot"], 2), [self._smodel(self.rank, srv["slot"], self.cur)])
+        self._barrier()
+        # 3. servers agree: model := model-GAR of all servers' published models → other buffer
+        if self.num_ps > 1:
+            published = self._published()
+            for srv in self.servers:
+                nxt = self._smodel(self.rank, srv["slot"], 1 - self.cur)
+                if self.mar_name in ("vanilla", "crash"):
+                    nxt.copy_(torch.stack(published).mean(0) if self.mar_name == "vanilla" else published[0])
+                else:
+                    nxt.copy_(gar_ops.aggregate(self.mar_name, published, self.fps))
+            self._barrier()
+            self.cur = 1 - self.cur
+            for srv in self.servers:
+                live = self._smodel(self.rank, srv["slot"], self.cur)
+                srv["opt"].rebind(live)
+        losses = [w["loss"] for w in self.workers if not w["attack"]]
+        return torch.stack(losses).mean() if losses else torch.zeros((), device=self.device)
+
+    def close(self):
+        torch.cuda.synchronize(self.device)
+        for arena in (self.smodels, self.wmodels, self.grads):
+            arena.close()

@@ -119,6 +119,19 @@ GB_API int gb_coordwise(float const* const* rows, int n, int64_t d, int rule, in
 GB_API int64_t gb_pairwise_scratch_bytes(int n);
 GB_API int gb_pairwise_select(float const* const* rows, int n, int64_t d, int mode, int f, int m, int neighbors, int squared,
                               void* scratch, int64_t scratch_bytes, float* dist, float* W, int* info, void* stream);
+/* Selection logic alone on a (summed) n×n squared-distance matrix already in device memory — used
+ * when the distance pass is sharded over coordinates/GPUs and the partial matrices were all-reduced.
+ * `dist` is normalised in place (+inf diagonal, non-finite → +inf). Same modes as gb_pairwise_select.
+ * ref: py_krum/krum.cu:104-150 (host sort/nth_element), py_bulyan/bulyan.cu:294-316 */
+GB_API int gb_select_only(float* dist, int n, int mode, int f, int m, int neighbors, int squared, float* W, int* info, void* stream);
+/* Tensor-core variant of gb_pairwise_select for 2 <= n <= 32 sixteen-byte-aligned rows: the Gram
+ * matrix X·Xᵀ is accumulated with tcgen05.mma (kind::tf32) in TMEM from TMA-bulk-copied tiles, then
+ * D_ij = G_ii + G_jj − 2·G_ij and the same in-kernel selection. TF32 operand precision (see
+ * csrc/cuda/gar_gram_tc.cu); returns an error without launching when the inputs do not qualify.
+ * ref: py_krum/krum.cu:87-98, py_bulyan/bulyan.cu:286-293 (K1+K2 launched n(n-1)/2 times) */
+GB_API int64_t gb_gram_scratch_bytes(int n);
+GB_API int gb_gram_select_tc(float const* const* rows, int n, int64_t d, int mode, int f, int m, int neighbors, int squared,
+                             void* scratch, int64_t scratch_bytes, float* dist, float* W, int* info, void* stream);
 /* gb_pairwise_select for callers that may not allocate device memory (a process whose HBM was
  * handed to its own pool at start-up, a loop under a fixed memory plan, a path that cannot take
  * cudaMalloc's device-wide synchronisation): same outputs, no scratch argument, no allocation of

@@ -1,0 +1,44 @@
+"""Run under torchrun by tests/test_multi_gpu.py: sharded vs single-server aggregation over peer memory."""
+import os
+import pathlib
+import sys
+
+sys.path.insert(0, str(pathlib.Path(__file__).resolve().parent.parent))
+os.environ.setdefault("GARFIELD_SYNTHETIC_SIZE", "1500")
+
+import torch  # noqa: E402
+import torch.distributed as dist  # noqa: E402
+
+from garfield_b200.parallel.engine import SSMWEngine  # noqa: E402
+
+
+def main():
+    local = int(os.environ["LOCAL_RANK"])
+    torch.cuda.set_device(local)
+    dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    rank, world = dist.get_rank(), dist.get_world_size()
+    for gar, n, f in (("krum", 8, 1), ("median", 8, 1), ("bulyan", 8, 1), ("brute", 7, 2), ("aksel", 7, 1)):
+        finals = []
+        for sharded in (False, True):
+            eng = SSMWEngine("cifarnet", "synthetic-cifar10", "cross-entropy", n, f, gar, 16, "sgd", dict(lr=0.05, momentum=0.9),
+                             byzantine={n - 1: "reverse"}, use_graphs=False, sharded=sharded, seed=99)
+            for i in range(3):
+                eng.step(i)
+            torch.cuda.synchronize()
+            flat = eng.flat.clone()
+            gathered = [torch.empty_like(flat) for _ in range(world)]
+            dist.all_gather(gathered, flat)
+            for other in gathered[1:]:
+                assert torch.equal(gathered[0], other), "%s: parameter replicas diverged (sharded=%s)" % (gar, sharded)
+            assert torch.isfinite(flat).all()
+            finals.append(flat)
+            eng.close()
+        if gar != "aksel":  # aksel keeps the (n+1)//2 closest to the median: near-ties may legitimately flip with the summation order
+            torch.testing.assert_close(finals[0], finals[1], rtol=1e-4, atol=1e-6, msg=lambda m: "%s sharded != centralized: %s" % (gar, m))
+        if rank == 0:
+            print("ok", gar, flush=True)
+    dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

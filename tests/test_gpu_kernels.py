@@ -177,3 +177,60 @@ def test_attacks_cuda():
     torch.testing.assert_close(attacks.lie(est), stack.mean(0) + 1.035 * stack.std(0), rtol=1e-5, atol=1e-6)
     torch.testing.assert_close(attacks.empire(est), -10 * stack.mean(0), rtol=1e-5, atol=1e-6)
     torch.testing.assert_close(attacks.lie(est[:1]), est[0])
+
+
+@pytest.mark.parametrize("n,d", [(2, 4096), (8, 100000), (13, 70001), (16, 300003), (17, 50000), (23, 123457), (32, 65536 + 5)])
+def test_tcgen05_gram_distances(n, d):
+    """Tensor-core (tcgen05 / TMEM, TF32 operands) Gram distances vs the fp64 reference."""
+    gar = cuda_lib()
+    g = make(n, d, seed=n * 3 + d, spread=1.0)
+    got = gar.pairwise_sqdist(g, engine="tc").cpu().double()
+    mat = torch.stack(g).cpu().double()
+    want = torch.cdist(mat, mat).pow(2)
+    norms = mat.pow(2).sum(1)
+    scale = norms[:, None] + norms[None, :]
+    err = (got - want).abs()
+    err.fill_diagonal_(0.0)
+    assert torch.isinf(got.diagonal()).all()
+    assert (err / scale).max().item() < 2e-3, (err / scale).max().item()
+    exact = gar.pairwise_sqdist(g, engine="simt").cpu().double()
+    rel = ((got - exact).abs() / scale)
+    rel.fill_diagonal_(0.0)
+    assert rel.max().item() < 2e-3
+
+
+def test_tcgen05_gram_selection_matches_exact_kernel():
+    gar = cuda_lib()
+    n, f, d = 23, 5, 200000
+    g = make(n, d, seed=77, spread=1.0)
+    for mode, kw in (("krum", dict(f=f, m=n - f - 2, neighbors=n - f - 2, squared=True)),
+                     ("bulyan_native", dict(f=f, m=n - f - 2, squared=True))):
+        theta = n - 2 * f - 2 if mode.startswith("bulyan") else 1
+        w_exact = gar.select(g, mode, engine="simt", **kw)["W"][:theta].clone()
+        w_tc = gar.select(g, mode, engine="tc", **kw)["W"][:theta].clone()
+        assert torch.equal(w_exact != 0, w_tc != 0), mode
+
+
+def test_device_topology_engines_single_gpu():
+    """MSMW and decentralized engines with every replica co-located on one GPU: honest replicas
+    stay in agreement and the loss is finite under Byzantine workers and servers."""
+    import os
+    os.environ.setdefault("GARFIELD_SYNTHETIC_SIZE", "1500")
+    from garfield_b200.parallel.topologies import DecentralizedEngine, MSMWEngine
+    cuda_lib()
+    eng = MSMWEngine("cifarnet", "synthetic-cifar10", "cross-entropy", 5, 3, 1, 1, "krum", 16, mar="median",
+                     opt_args=dict(lr=0.05, momentum=0.9), byzantine_workers={4: "reverse"}, byzantine_servers={2: "random"})
+    losses = [eng.step(i).item() for i in range(4)]
+    assert all(l == l for l in losses)
+    a = eng._smodel(0, 0, eng.cur).clone()
+    b = eng._smodel(0, 1, eng.cur).clone()
+    torch.testing.assert_close(a, b)          # the two honest servers agree after the model GAR
+    assert torch.isfinite(a).all()
+    eng.close()
+    dec = DecentralizedEngine("cifarnet", "synthetic-cifar10", "cross-entropy", 6, 1, "median", 16, opt_args=dict(lr=0.05),
+                              byzantine={5: "random"}, non_iid=True)
+    losses = [dec.step(i).item() for i in range(3)]
+    assert all(l == l for l in losses)
+    m0, m1 = dec.model_of(0).clone(), dec.model_of(1).clone()
+    torch.testing.assert_close(m0, m1)        # contract step: every node holds the same aggregated model
+    dec.close()
