@@ -41,7 +41,7 @@ METRIC = "images/sec ResNet-50 n=8 f=1 per GAR (Krum/Median/Bulyan); GAR latency
 def parse_args(argv=None):
     ap = argparse.ArgumentParser(description=__doc__, formatter_class=argparse.RawTextHelpFormatter)
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=30)
+    ap.add_argument("--steps", type=int, default=100)
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--gar", default="krum", help="primary rule for `value` (krum | median | bulyan | ...)")
@@ -68,7 +68,7 @@ class ClockSampler:
                     self.samples.append([c.strip() for c in out.split(",")])
             except Exception:
                 pass
-            self._stop.wait(0.2)
+            self._stop.wait(0.05)
 
     def __enter__(self):
         self._thread = threading.Thread(target=self._loop, daemon=True)
@@ -107,6 +107,27 @@ def init_dist(gpus):
     if world != gpus and rank == 0:
         print("warning: --gpus %d but WORLD_SIZE=%d (launch with torchrun --nproc-per-node %d)" % (gpus, world, gpus), file=sys.stderr)
     return rank, world, local
+
+
+def timed_run(engine, steps, first_iter):
+    """Device time (ms, max over ranks) of `engine.run(first_iter, steps)` — the public end-to-end loop
+    (per-step pinned-host→device input copies and per-step loss read-backs included)."""
+    import torch
+    import torch.distributed as dist
+    if engine.world > 1:
+        dist.barrier()
+    torch.cuda.synchronize()
+    start, stop = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    start.record()
+    losses = engine.run(first_iter, steps)
+    stop.record()
+    torch.cuda.synchronize()
+    assert len(losses) == steps and all(l == l for l in losses), "every step must return a finite loss"
+    ms = torch.tensor([start.elapsed_time(stop)], device=engine.device)
+    if engine.world > 1:
+        dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+        dist.barrier()
+    return float(ms.item()), 4 * steps
 
 
 def timed_steps(engine, steps, first_iter, load, read_loss):
@@ -151,7 +172,7 @@ def run_gar(gar, args, rank, world, local, full):
         ms_dev, _ = timed_steps(engine, steps, it, load=False, read_loss=False)
         it += steps
         launches = _lib.launches[0] - launches0
-        ms_e2e, d2h = timed_steps(engine, steps, it, load=True, read_loss=True)
+        ms_e2e, d2h = timed_run(engine, steps, it)
         it += steps
     result = {
         "gar": gar, "steps": steps, "ms_per_step": ms_dev / steps, "images_per_s": images / (ms_dev / 1e3),

@@ -130,6 +130,7 @@ class SSMWEngine:
             self.mirrors = [self.param_arena.peer(r)[self.lo:self.hi] for r in range(self.world) if r != self.rank]
         self._flag = torch.zeros(1, device=self.device)
         self._graph = None
+        self._copy_stream = None
         self.use_graphs = use_graphs
         self.steps_done = 0
         self.h2d_bytes = 0
@@ -154,6 +155,58 @@ class SSMWEngine:
             nbytes += x.numel() * x.element_size() + y.numel() * y.element_size()
         self.h2d_bytes = nbytes
         return nbytes
+
+    # -- pipelined public loop: prefetch of step i+1's inputs and deferred loss read-back ---------
+    def _prefetch(self, iter_num):
+        """Start the pinned-host → device copy of step `iter_num`'s batches on the copy stream."""
+        if self._copy_stream is None:
+            self._copy_stream = torch.cuda.Stream(device=self.device)
+            for w in self.workers:
+                w.stage_data, w.stage_target = torch.empty_like(w.data), torch.empty_like(w.target)
+        nbytes = 0
+        self._copy_stream.wait_stream(torch.cuda.current_stream(self.device))  # staging buffers are free again
+        with torch.cuda.stream(self._copy_stream):
+            for w in self.workers:
+                batches = self.train_sets[w.wid]
+                x, y = batches[iter_num % len(batches)]
+                w.stage_data.copy_(x, non_blocking=True)
+                w.stage_target.copy_(y, non_blocking=True)
+                nbytes += x.numel() * x.element_size() + y.numel() * y.element_size()
+        self.h2d_bytes = nbytes
+
+    def _commit_prefetch(self):
+        """Make the prefetched batches the inputs of the next step (device-to-device, on the main stream)."""
+        torch.cuda.current_stream(self.device).wait_stream(self._copy_stream)
+        for w in self.workers:
+            w.data.copy_(w.stage_data, non_blocking=True)
+            w.target.copy_(w.stage_target, non_blocking=True)
+
+    def run(self, first_iter, steps):
+        """Train `steps` iterations end to end and return the per-step mean losses (Python floats).
+
+        Every step's batches are copied from pinned host memory while the previous step computes,
+        and every step's loss is read back to the host one step later, so the host never stalls the
+        device; all copies and reads happen inside this call."""
+        losses, pending = [], None
+        host = [torch.zeros((), pin_memory=True) for _ in range(2)]
+        self._prefetch(first_iter)
+        for i in range(steps):
+            self._commit_prefetch()
+            if i + 1 < steps:
+                self._prefetch(first_iter + i + 1)
+            loss = self.step(first_iter + i, load=False)
+            slot = host[i % 2]
+            slot.copy_(loss, non_blocking=True)
+            done = torch.cuda.Event()
+            done.record()
+            if pending is not None:
+                pending[0].synchronize()
+                losses.append(float(pending[1]))
+            pending = (done, slot)
+        if pending is not None:
+            pending[0].synchronize()
+            losses.append(float(pending[1]))
+        return losses
 
     def _run_workers(self):
         main = torch.cuda.current_stream(self.device)

@@ -1,0 +1,72 @@
+"""TF-side compatibility layer: numpy aggregator façade, numpy attacks, cluster JSON, gRPC pulls."""
+
+import socket
+
+import numpy as np
+import pytest
+import torch
+
+from garfield_b200.compat import Aggregator_tf, Attacker, Network
+from garfield_b200.compat import grpc_exchange
+from garfield_b200.compat.aggregator_tf import average_nan
+
+
+def test_aggregator_facade_matches_registry():
+    import aggregators
+    rng = np.random.RandomState(0)
+    grads = [rng.randn(500).astype(np.float32) for _ in range(11)]
+    rows = [torch.from_numpy(g) for g in grads]
+    for agg, name in (("Average", "average"), ("Median", "median"), ("Krum", "krum"), ("Bulyan", "bulyan"), ("Brute", "brute"),
+                      ("Aksel", "aksel")):
+        got = Aggregator_tf(agg, 11, 2, device="cpu").aggregate(grads)
+        np.testing.assert_allclose(got, aggregators.gars[name](gradients=rows, f=2).numpy(), rtol=1e-5, atol=1e-6)
+    native = Aggregator_tf("Krum", 11, 2, native=True, device="cpu").aggregate(grads)
+    np.testing.assert_allclose(native, aggregators.gars["native-krum"](gradients=rows, f=2).numpy(), rtol=1e-5, atol=1e-6)
+    bad = [g.copy() for g in grads[:3]]
+    bad[0][0] = np.nan
+    assert average_nan(bad)[0] == pytest.approx((bad[1][0] + bad[2][0]) / 2)
+
+
+def test_numpy_attacks():
+    g = np.arange(8, dtype=np.float32)
+    assert Attacker("Reverse").attack(gradient=g).tolist() == (-100 * g).tolist()
+    assert Attacker("Random").attack(gradient=g).shape == g.shape
+    dropped = Attacker("PartialDrop").attack(gradient=np.ones(10000, np.float32), probability=0.3)
+    assert 0.25 < (dropped == 0).mean() < 0.35
+    others = [g + 1, g + 2]
+    stack = np.stack(others + [g])
+    np.testing.assert_allclose(Attacker("LittleIsEnough").attack(gradient=g, byz_gradients=others), stack.mean(0) + 1.035 * stack.std(0), rtol=1e-6)
+    np.testing.assert_allclose(Attacker("FallEmpires").attack(gradient=g, byz_gradients=others), -10 * stack.mean(0), rtol=1e-6)
+    with pytest.raises(AssertionError):
+        Attacker("Nope")
+
+
+def test_network_config():
+    cfg = {"cluster": {"ps": ["a:1000"], "worker": ["b:2000", "c:2001"]},
+           "task": {"type": "worker", "index": 1, "strategy_gradient": "Krum", "strategy_model": "Median", "attack": "Random"}}
+    net = Network(cfg)
+    assert net.get_task_type() == "worker" and net.get_task_index() == 1 and net.get_my_node() == "c:2001"
+    assert net.get_my_port() == 2001 and net.get_all_other_worker() == ["b:2000"] and net.get_all_ps() == ["a:1000"]
+    assert net.get_gradient_strategy() == "Krum" and net.get_model_strategy() == "Median" and net.get_my_attack() == "Random"
+
+
+def test_grpc_pull_service():
+    pytest.importorskip("grpc")
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        port = s.getsockname()[1]
+    servicer = grpc_exchange.MessageExchangeServicer(timeout=10)
+    server = grpc_exchange.serve(servicer, port)
+    try:
+        client = grpc_exchange.Client("127.0.0.1:%d" % port)
+        model = np.linspace(0, 1, 1000, dtype=np.float32)
+        servicer.commit_model(model)
+        servicer.commit_gradient(model * 2)
+        np.testing.assert_array_equal(client.get_model(0), model)
+        np.testing.assert_array_equal(client.get_gradient(0), model * 2)
+        import threading
+        threading.Timer(0.2, lambda: servicer.commit_model(model + 1)).start()
+        np.testing.assert_array_equal(client.get_model(1), model + 1)   # blocks until iteration 1 is committed
+        client.close()
+    finally:
+        server.stop(0)

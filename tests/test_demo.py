@@ -1,0 +1,43 @@
+"""LEARN web demo: POST / starts a run, GET /status reports progress then the final accuracy."""
+
+import importlib.util
+import json
+import pathlib
+import threading
+import time
+import urllib.request
+from http.server import ThreadingHTTPServer
+
+ROOT = pathlib.Path(__file__).resolve().parent.parent
+
+
+def test_demo_http_roundtrip():
+    spec = importlib.util.spec_from_file_location("learn_demo", ROOT / "applications" / "LEARN" / "demo.py")
+    demo = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(demo)
+    demo.EPOCHS = 1
+    server = ThreadingHTTPServer(("127.0.0.1", 0), demo.Handler)
+    port = server.server_address[1]
+    threading.Thread(target=server.serve_forever, daemon=True).start()
+    try:
+        base = "http://127.0.0.1:%d" % port
+        assert b"LEARN" in urllib.request.urlopen(base + "/", timeout=10).read()
+        req = urllib.request.Request(base + "/", data=json.dumps({"n": 4, "f": 1, "gar": "median"}).encode(), method="POST")
+        trainer_id = json.loads(urllib.request.urlopen(req, timeout=10).read())["trainer_id"]
+        deadline = time.time() + 120
+        status = {}
+        while time.time() < deadline:
+            status = json.loads(urllib.request.urlopen(base + "/status?trainer_id=%d" % trainer_id, timeout=10).read())
+            assert "error" not in status, status
+            if "result" in status:
+                break
+            time.sleep(0.2)
+        assert 0.0 <= status.get("result", -1) <= 100.0, status
+        bad = urllib.request.Request(base + "/", data=b"n=3&f=2&gar=median", method="POST")
+        try:
+            urllib.request.urlopen(bad, timeout=10)
+            assert False, "invalid (n, f) must be rejected"
+        except urllib.error.HTTPError as err:
+            assert err.code == 400
+    finally:
+        server.shutdown()
