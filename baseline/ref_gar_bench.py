@@ -1,0 +1,57 @@
+#!/usr/bin/env python
+"""GAR latency of the UNMODIFIED reference rules (baseline/_ref/pytorch_impl/libs/aggregators) on this
+box, with the synchronisation the reference's own gar_bench.py lacks. Prints one JSON line per point.
+
+    python baseline/ref_gar_bench.py [--device cuda] [--n 8 --f 1 --d 23528522] [--gars krum,median,bulyan]
+"""
+import argparse
+import json
+import pathlib
+import sys
+import time
+
+HERE = pathlib.Path(__file__).resolve().parent
+LIBS = HERE / "_ref" / "pytorch_impl" / "libs"
+sys.path = [str(LIBS)] + [p for p in sys.path if p and pathlib.Path(p).resolve() not in (HERE.parent, HERE)]
+sys.modules["native"] = None  # reference natives need a torch-header JIT build that fails on torch 2.11
+
+import torch  # noqa: E402
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--device", default="cuda" if torch.cuda.is_available() else "cpu")
+    ap.add_argument("--n", type=int, default=8)
+    ap.add_argument("--f", type=int, default=1)
+    ap.add_argument("--d", type=int, default=23528522)
+    ap.add_argument("--gars", default="average,median,krum,bulyan,brute,aksel")
+    ap.add_argument("--reps", type=int, default=3)
+    args = ap.parse_args()
+    stdout = sys.stdout
+    import aggregators  # the reference's registry (wraps stdout on import)
+    sys.stdout = stdout
+    assert str(LIBS) in aggregators.__file__
+    dev = torch.device(args.device)
+    torch.manual_seed(1234)
+    grads = [torch.randn(args.d, device=dev) for _ in range(args.n)]
+    for name in args.gars.split(","):
+        rule = aggregators.gars[name]
+        if rule.check(gradients=grads, f=args.f) is not None:
+            continue
+        times = []
+        for it in range(args.reps + 1):
+            if dev.type == "cuda":
+                torch.cuda.synchronize()
+            t0 = time.perf_counter()
+            rule(gradients=grads, f=args.f)
+            if dev.type == "cuda":
+                torch.cuda.synchronize()
+            if it:
+                times.append((time.perf_counter() - t0) * 1e3)
+        times.sort()
+        print(json.dumps({"impl": "reference", "gar": name, "n": args.n, "f": args.f, "d": args.d, "device": str(dev),
+                          "ms": times[len(times) // 2]}), flush=True)
+
+
+if __name__ == "__main__":
+    main()

@@ -1,0 +1,195 @@
+// gemm_tc: C[M,N] = A[M,K] · B[N,K]ᵀ (+ bias[N]) (ReLU), fp32 output, on the 5th-generation tensor
+// cores: TMA 2-D tiled loads (128-byte swizzle) → 4-stage mbarrier ring → tcgen05.mma
+// (kind::tf32 for fp32 operands, kind::f16 for bf16 operands) accumulating in TMEM → tcgen05.ld
+// epilogue with fused bias / ReLU. Warp-specialised: warp 0 = TMA producer, warp 1 = MMA issuer
+// (one elected thread), warps 2-5 = epilogue (one TMEM lane quadrant each).
+//
+// This is the framework's own GEMM for nn.Linear forward / dgrad / wgrad (the reference relies on
+// cuBLAS through ATen: garfieldpp/models/nets.py:47-57, 68-77). Both operands are
+// K-major ("NT"), which is nn.Linear's natural layout: y = x[M,K] · W[N,K]ᵀ.
+//
+// Tile: 128 (M) × BN (N ∈ {128, 256}) × 128 bytes of K per stage (32 tf32 or 64 bf16 elements =
+// 4 MMAs of K = 32 bytes). Out-of-range rows/columns are zero-filled by TMA and masked in the epilogue,
+// so M, N, K need not be tile multiples (K·sizeof(T) must be a multiple of 16 bytes for the tensor map).
+
+#include <cuda.h>
+
+#include <cstring>
+#include <mutex>
+
+#include "garfield_b200.h"
+#include "launch.cuh"
+#include "ptx.cuh"
+
+namespace gb {
+namespace {
+
+constexpr int kGemmThreads = 32 * 6;
+constexpr int kGemmStages = 4;
+constexpr int kBM = 128;
+constexpr int kRowBytes = 128;  // bytes of K per stage and per smem row (one swizzle atom wide)
+
+struct GemmShared {
+    uint64_t full[kGemmStages];
+    uint64_t empty[kGemmStages];
+    uint64_t accum_done;
+    uint32_t tmem_base;
+};
+
+template <int BN, bool TF32>
+__global__ void __launch_bounds__(kGemmThreads, 1)
+gemm_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b, float* __restrict__ C,
+               const float* __restrict__ bias, int M, int N, int K, long long ldc, int relu) {
+    extern __shared__ __align__(1024) unsigned char smem_raw[];
+    __shared__ GemmShared sh;
+    constexpr uint32_t kABytes = kBM * kRowBytes, kBBytes = BN * kRowBytes, kStageBytes = kABytes + kBBytes;
+    constexpr int kElemsPerStage = TF32 ? 32 : 64;  // K elements per stage
+    int const warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    int const tile_n = blockIdx.x, tile_m = blockIdx.y;
+    int const k_steps = (K + kElemsPerStage - 1) / kElemsPerStage;
+
+    if (threadIdx.x == 0) {
+        for (int s = 0; s < kGemmStages; ++s) {
+            ptx::mbar_init(&sh.full[s], 1);
+            ptx::mbar_init(&sh.empty[s], 1);
+        }
+        ptx::mbar_init(&sh.accum_done, 1);
+        ptx::fence_mbar_init();
+        ptx::prefetch_tensormap(&map_a);
+        ptx::prefetch_tensormap(&map_b);
+    }
+    if (warp == 1) ptx::tmem_alloc<BN>(&sh.tmem_base);
+    ptx::tc_fence_before();
+    __syncthreads();
+    ptx::tc_fence_after();
+    uint32_t const tmem = sh.tmem_base;
+
+    if (warp == 0) {
+        if (ptx::elect_one()) {
+            for (int it = 0; it < k_steps; ++it) {
+                int const s = it % kGemmStages;
+                uint32_t const phase = static_cast<uint32_t>((it / kGemmStages) & 1);
+                ptx::mbar_wait(&sh.empty[s], phase ^ 1u);
+                ptx::mbar_arrive_expect_tx(&sh.full[s], kStageBytes);
+                unsigned char* dst = smem_raw + static_cast<size_t>(s) * kStageBytes;
+                ptx::tma_load_2d(dst, &map_a, it * kElemsPerStage, tile_m * kBM, &sh.full[s]);
+                ptx::tma_load_2d(dst + kABytes, &map_b, it * kElemsPerStage, tile_n * BN, &sh.full[s]);
+            }
+        }
+    } else if (warp == 1) {
+        if (ptx::elect_one()) {
+            uint32_t const idesc = TF32 ? ptx::make_idesc(2u, 2u, kBM, BN) : ptx::make_idesc(1u, 1u, kBM, BN);
+            for (int it = 0; it < k_steps; ++it) {
+                int const s = it % kGemmStages;
+                uint32_t const phase = static_cast<uint32_t>((it / kGemmStages) & 1);
+                ptx::mbar_wait(&sh.full[s], phase);
+                ptx::tc_fence_after();
+                uint32_t const a_base = ptx::smem_u32(smem_raw + static_cast<size_t>(s) * kStageBytes);
+                uint32_t const b_base = a_base + kABytes;
+#pragma unroll
+                for (int k = 0; k < 4; ++k) {  // 4 × 32 bytes of K inside the 128-byte swizzle atom
+                    uint64_t const adesc = ptx::make_smem_desc(a_base + k * 32u, 16u, 1024u, 2u);
+                    uint64_t const bdesc = ptx::make_smem_desc(b_base + k * 32u, 16u, 1024u, 2u);
+                    if (TF32) ptx::mma_tf32_ss(tmem, adesc, bdesc, idesc, (it > 0 || k > 0) ? 1u : 0u);
+                    else ptx::mma_f16_ss(tmem, adesc, bdesc, idesc, (it > 0 || k > 0) ? 1u : 0u);
+                }
+                ptx::mma_commit(&sh.empty[s]);
+            }
+            ptx::mma_commit(&sh.accum_done);
+        }
+    } else {
+        int const quad = warp & 3;
+        int const row = tile_m * kBM + quad * 32 + lane;
+        ptx::mbar_wait(&sh.accum_done, 0u);
+        ptx::tc_fence_after();
+#pragma unroll 1
+        for (int c0 = 0; c0 < BN; c0 += 16) {
+            uint32_t v[16];
+            ptx::tmem_ld_32x32b_x16(tmem + (static_cast<uint32_t>(quad * 32) << 16) + static_cast<uint32_t>(c0), v);
+            ptx::tmem_ld_wait();
+            int const col0 = tile_n * BN + c0;
+            if (row < M && col0 < N) {
+                float* out = C + static_cast<long long>(row) * ldc + col0;
+#pragma unroll
+                for (int j = 0; j < 16; ++j) {
+                    if (col0 + j < N) {
+                        float x = __uint_as_float(v[j]);
+                        if (bias != nullptr) x += bias[col0 + j];
+                        if (relu) x = fmaxf(x, 0.0f);
+                        out[j] = x;
+                    }
+                }
+            }
+        }
+    }
+    ptx::tc_fence_before();
+    __syncthreads();
+    if (warp == 1) ptx::tmem_dealloc<BN>(tmem);
+}
+
+using EncodeFn = CUresult (*)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                              const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                              CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+EncodeFn encode_fn() {
+    static EncodeFn fn = nullptr;
+    static std::once_flag once;
+    std::call_once(once, [] {
+        void* ptr = nullptr;
+        cudaDriverEntryPointQueryResult status;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &ptr, cudaEnableDefault, &status) == cudaSuccess &&
+            status == cudaDriverEntryPointSuccess)
+            fn = reinterpret_cast<EncodeFn>(ptr);
+    });
+    return fn;
+}
+
+// Row-major [rows, K] matrix with K contiguous; box = (128 bytes of K) × box_rows, 128B swizzle.
+bool make_map(CUtensorMap* map, const void* base, long long rows, long long k, long long ld_elems, int elem_bytes, int box_rows) {
+    EncodeFn fn = encode_fn();
+    if (fn == nullptr) return false;
+    cuuint64_t dims[2] = {static_cast<cuuint64_t>(k), static_cast<cuuint64_t>(rows)};
+    cuuint64_t strides[1] = {static_cast<cuuint64_t>(ld_elems) * static_cast<cuuint64_t>(elem_bytes)};
+    cuuint32_t box[2] = {static_cast<cuuint32_t>(kRowBytes / elem_bytes), static_cast<cuuint32_t>(box_rows)};
+    cuuint32_t estr[2] = {1, 1};
+    CUtensorMapDataType const dtype = elem_bytes == 4 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16;
+    return fn(map, dtype, 2, const_cast<void*>(base), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+              CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+}
+
+template <int BN, bool TF32>
+cudaError_t launch_gemm(CUtensorMap const& ma, CUtensorMap const& mb, float* C, const float* bias, int M, int N, int K, long long ldc,
+                        int relu, cudaStream_t stream) {
+    auto kern = gemm_tc_kernel<BN, TF32>;
+    size_t const smem = static_cast<size_t>(kGemmStages) * (kBM + BN) * kRowBytes;
+    cudaError_t err = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem));
+    if (err != cudaSuccess) return err;
+    dim3 grid((N + BN - 1) / BN, (M + kBM - 1) / kBM);
+    kern<<<grid, kGemmThreads, smem, stream>>>(ma, mb, C, bias, M, N, K, ldc, relu);
+    return cudaGetLastError();
+}
+
+}  // namespace
+}  // namespace gb
+
+// C[M,N] (fp32, row stride ldc) = A[M,K] · B[N,K]ᵀ (+ bias) (ReLU). dtype: 0 = fp32 operands (TF32 MMA),
+// 1 = bf16 operands. lda / ldb are row strides in elements; base pointers and row strides must be
+// 16-byte aligned.
+extern "C" GB_API int gb_gemm_nt(void const* A, void const* B, float* C, float const* bias, int M, int N, int K, int64_t lda, int64_t ldb,
+                                 int64_t ldc, int dtype, int relu, void* stream) {
+    using namespace gb;
+    if (M < 1 || N < 1 || K < 1) return cuda_fail("gemm: empty problem");
+    if (dtype != 0 && dtype != 1) return cuda_fail("gemm: dtype must be 0 (fp32/tf32) or 1 (bf16)");
+    int const eb = dtype == 0 ? 4 : 2;
+    if ((reinterpret_cast<uintptr_t>(A) & 15u) || (reinterpret_cast<uintptr_t>(B) & 15u) || (lda * eb) % 16 || (ldb * eb) % 16)
+        return cuda_fail("gemm: operands must be 16-byte aligned with row strides that are multiples of 16 bytes");
+    CUtensorMap ma, mb;
+    int const bn = N > 128 ? 256 : 128;
+    if (!make_map(&ma, A, M, K, lda, eb, kBM) || !make_map(&mb, B, N, K, ldb, eb, bn))
+        return cuda_fail("gemm: cuTensorMapEncodeTiled failed (driver entry point unavailable or bad shape)");
+    cudaStream_t const st = static_cast<cudaStream_t>(stream);
+    cudaError_t err;
+    if (dtype == 0) err = bn == 256 ? launch_gemm<256, true>(ma, mb, C, bias, M, N, K, ldc, relu, st) : launch_gemm<128, true>(ma, mb, C, bias, M, N, K, ldc, relu, st);
+    else err = bn == 256 ? launch_gemm<256, false>(ma, mb, C, bias, M, N, K, ldc, relu, st) : launch_gemm<128, false>(ma, mb, C, bias, M, N, K, ldc, relu, st);
+    return cuda_check(err, "gemm launch");
+}

@@ -51,6 +51,7 @@ _MODELS = {
     "efficientnetb0": _zoo.EfficientNetB0, "regnetx200": _zoo.RegNetX_200MF, "pimanet": _zoo.PimaNet,
     # extras beyond the reference's table (local CIFAR-style variants and the rest of the zoo)
     "resnet50-cifar": _zoo.ResNet50, "resnet34-cifar": _zoo.ResNet34, "vgg16-cifar": _zoo.VGG16, "lenet": _zoo.LeNet,
+    "cifarnet-native": _zoo.NativeCifarnet, "convnet-native": _zoo.NativeNet,  # hand-written sm_100a kernels end to end
     "shufflenetv2": _zoo.ShuffleNetV2, "pnasneta": _zoo.PNASNetA, "regnety400": _zoo.RegNetY_400MF,
 }
 

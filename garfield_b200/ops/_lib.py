@@ -36,6 +36,14 @@ def _declare(h):
     h.gb_gram_scratch_bytes.argtypes = [i32]
     h.gb_gram_select_tc.argtypes = [pp, i32, i64, i32, i32, i32, i32, i32, vp, i64, vp, vp, vp, vp]
     h.gb_select_only.argtypes = [vp, i32, i32, i32, i32, i32, i32, vp, vp, vp]
+    h.gb_gemm_nt.argtypes = [vp, vp, vp, vp, i32, i32, i32, i64, i64, i64, i32, i32, vp]
+    h.gb_conv2d_forward.argtypes = [vp, vp, vp, vp] + [i32] * 10 + [vp]
+    h.gb_conv2d_backward.argtypes = [vp, vp, vp, vp, vp, vp] + [i32] * 9 + [vp]
+    h.gb_maxpool2d_forward.argtypes = [vp, vp, vp, i32, i32, i32, i32, i32, vp]
+    h.gb_maxpool2d_backward.argtypes = [vp, vp, vp, i32, i32, i32, vp]
+    h.gb_softmax_loss.argtypes = [vp, vp, vp, vp, i32, i32, i32, vp]
+    h.gb_batchnorm_forward.argtypes = [vp] * 8 + [i32, i32, i32, f32, f32, i32, vp]
+    h.gb_batchnorm_backward.argtypes = [vp] * 8 + [i32, i32, i32, vp]
     h.gb_sgd_step.argtypes = [vp, vp, vp, i64, f32, f32, f32, f32, i32, i32, pp, i32, vp]
     h.gb_adam_step.argtypes = [vp, vp, vp, vp, i64, f32, f32, f32, f32, f32, i32, i32, vp]
     h.gb_rmsprop_step.argtypes = [vp, vp, vp, vp, i64, f32, f32, f32, f32, f32, vp]

@@ -143,6 +143,28 @@ GB_API int gb_gram_select_tc(float const* const* rows, int n, int64_t d, int mod
 GB_API int gb_pairwise_select_noalloc(float const* const* rows, int n, int64_t d, int mode, int f, int m, int neighbors,
                                       int squared, float* dist, float* W, int* info, void* stream);
 
+/* C[M,N] (fp32, row stride ldc) = A[M,K] · B[N,K]^T (+ bias[N]) (ReLU) on tcgen05 tensor cores with TMA
+ * tiled loads and a TMEM accumulator. dtype 0: fp32 operands read as TF32; 1: bf16 operands.
+ * Operands K-major, 16-byte aligned, row strides (in elements) multiples of 16 bytes.
+ * ref: nn.Linear forward/backward through cuBLAS (garfieldpp/models/nets.py:47-57). */
+GB_API int gb_gemm_nt(void const* A, void const* B, float* C, float const* bias, int M, int N, int K, int64_t lda, int64_t ldb,
+                      int64_t ldc, int dtype, int relu, void* stream);
+
+/* Layer kernels of the small reference networks (fp32, NCHW). ref: cuDNN/ATen behind nn.Conv2d, MaxPool2d,
+ * BatchNorm2d, NLLLoss/CrossEntropyLoss (garfieldpp/models/nets.py:40-144, garfieldpp/tools.py:47-57). */
+GB_API int gb_conv2d_forward(float const* x, float const* w, float const* bias, float* y, int n, int cin, int h, int wd, int cout, int kh, int kw,
+                             int stride, int pad, int relu, void* stream);
+GB_API int gb_conv2d_backward(float const* x, float const* w, float const* dy, float* dx, float* dw, float* db, int n, int cin, int h, int wd,
+                              int cout, int kh, int kw, int stride, int pad, void* stream);
+GB_API int gb_maxpool2d_forward(float const* x, float* y, int* arg, int planes, int h, int w, int k, int stride, void* stream);
+GB_API int gb_maxpool2d_backward(float const* dy, int const* arg, float* dx, int planes, int hw_in, int hw_out, void* stream);
+/* mode 0: inputs are log-probabilities (NLLLoss); 1: raw logits (CrossEntropyLoss). dlogits = d(mean loss)/d(input). */
+GB_API int gb_softmax_loss(float const* in, int64_t const* target, float* row_loss, float* dlogits, int rows, int classes, int mode, void* stream);
+GB_API int gb_batchnorm_forward(float const* x, float const* gamma, float const* beta, float* y, float* save_mean, float* save_invstd,
+                                float* running_mean, float* running_var, int n, int c, int hw, float eps, float momentum, int relu, void* stream);
+GB_API int gb_batchnorm_backward(float const* x, float const* dy, float const* gamma, float const* save_mean, float const* save_invstd, float* dx,
+                                 float* dgamma, float* dbeta, int n, int c, int hw, void* stream);
+
 /* Flat-arena optimizer steps (torch.optim semantics). ref: garfieldpp/server.py:277-287,
  * garfieldpp/tools.py:107-123 (sgd, adam, adamw, rmsprop, adagrad — run on the HOST there). */
 GB_API int gb_sgd_step(float* param, float const* grad, float* mom, int64_t d, float lr, float momentum, float dampening,

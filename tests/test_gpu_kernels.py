@@ -234,3 +234,118 @@ def test_device_topology_engines_single_gpu():
     m0, m1 = dec.model_of(0).clone(), dec.model_of(1).clone()
     torch.testing.assert_close(m0, m1)        # contract step: every node holds the same aggregated model
     dec.close()
+
+
+@pytest.mark.parametrize("m,n,k", [(128, 128, 64), (25, 10, 84), (200, 120, 400), (77, 300, 1000), (512, 1024, 4096), (1000, 4096, 25088 // 8)])
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+def test_tcgen05_gemm_nt(m, n, k, dtype):
+    from garfield_b200.ops import nn as gnn
+    cuda_lib()
+    gen = torch.Generator().manual_seed(m + n + k)
+    a = torch.randn(m, k, generator=gen).cuda().to(dtype)
+    b = torch.randn(n, k, generator=gen).cuda().to(dtype)
+    bias = torch.randn(n, generator=gen).cuda()
+    want = a.double() @ b.double().t() + bias.double()
+    got = gnn.gemm_nt(a, b, bias=bias)
+    scale = (a.double().abs() @ b.double().abs().t()).clamp_min(1.0)   # error budget ∝ Σ|a||b|
+    tol = 2e-3 if dtype == torch.float32 else 1e-5                      # TF32 operand rounding vs exact bf16 products
+    assert ((got.double() - want).abs() / scale).max().item() < tol
+    relu = gnn.gemm_nt(a, b, bias=bias, relu=True)
+    torch.testing.assert_close(relu, got.clamp_min(0.0))
+
+
+def test_tcgen05_linear_autograd():
+    from garfield_b200.ops import nn as gnn
+    cuda_lib()
+    torch.manual_seed(0)
+    x = torch.randn(50, 400, device="cuda", requires_grad=True)
+    layer = gnn.Linear(400, 120).cuda()
+    ref = torch.nn.Linear(400, 120).cuda()
+    ref.load_state_dict(layer.state_dict())
+    x2 = x.detach().clone().requires_grad_(True)
+    y = layer(x)
+    y.square().sum().backward()
+    torch.backends.cuda.matmul.allow_tf32 = False
+    y2 = ref(x2)
+    y2.square().sum().backward()
+    torch.testing.assert_close(y, y2, rtol=5e-3, atol=5e-3)
+    torch.testing.assert_close(x.grad, x2.grad, rtol=2e-2, atol=2e-2)
+    torch.testing.assert_close(layer.weight.grad, ref.weight.grad, rtol=2e-2, atol=5e-2)
+    torch.testing.assert_close(layer.bias.grad, ref.bias.grad, rtol=1e-3, atol=1e-3)
+
+
+def test_small_cnn_layer_kernels_match_torch():
+    from garfield_b200.ops import nn as gnn
+    cuda_lib()
+    torch.manual_seed(3)
+    F = torch.nn.functional
+    for (n, cin, h, cout, k, stride, pad) in [(25, 3, 32, 6, 5, 1, 0), (8, 6, 14, 16, 5, 1, 0), (4, 5, 11, 7, 3, 2, 1), (2, 1, 28, 10, 5, 1, 0)]:
+        x = torch.randn(n, cin, h, h, device="cuda", requires_grad=True)
+        w = torch.randn(cout, cin, k, k, device="cuda", requires_grad=True)
+        b = torch.randn(cout, device="cuda", requires_grad=True)
+        xr, wr, br = (t.detach().double().cpu().requires_grad_(True) for t in (x, w, b))
+        y = gnn.conv2d(x, w, b, stride, pad, relu=True)
+        yr = torch.relu(F.conv2d(xr, wr, br, stride, pad))
+        torch.testing.assert_close(y.cpu().double(), yr, rtol=1e-4, atol=1e-4)
+        g = torch.randn_like(y)
+        y.backward(g)
+        yr.backward(g.cpu().double())
+        for got, want in ((x.grad, xr.grad), (w.grad, wr.grad), (b.grad, br.grad)):
+            torch.testing.assert_close(got.cpu().double(), want, rtol=1e-3, atol=1e-3)
+    x = torch.randn(6, 4, 13, 13, device="cuda", requires_grad=True)
+    xr = x.detach().cpu().requires_grad_(True)
+    for kernel, stride in ((2, 2), (3, 2)):
+        y, yr = gnn.max_pool2d(x, kernel, stride), F.max_pool2d(xr, kernel, stride)
+        torch.testing.assert_close(y.cpu(), yr)
+        g = torch.randn_like(y)
+        x.grad = None; xr.grad = None
+        y.backward(g); yr.backward(g.cpu())
+        torch.testing.assert_close(x.grad.cpu(), xr.grad)
+    logits = torch.randn(50, 10, device="cuda", requires_grad=True)
+    target = torch.randint(0, 10, (50,), device="cuda")
+    lr = logits.detach().cpu().requires_grad_(True)
+    loss, loss_r = gnn.cross_entropy(logits, target), F.cross_entropy(lr, target.cpu())
+    loss.backward(); loss_r.backward()
+    torch.testing.assert_close(loss.cpu(), loss_r, rtol=1e-5, atol=1e-6)
+    torch.testing.assert_close(logits.grad.cpu(), lr.grad, rtol=1e-5, atol=1e-6)
+    logp = torch.log_softmax(torch.randn(33, 10, device="cuda"), 1).requires_grad_(True)
+    lp = logp.detach().cpu().requires_grad_(True)
+    a, b2 = gnn.nll_loss(logp, target[:33]), F.nll_loss(lp, target[:33].cpu())
+    a.backward(); b2.backward()
+    torch.testing.assert_close(a.cpu(), b2, rtol=1e-5, atol=1e-6)
+    torch.testing.assert_close(logp.grad.cpu(), lp.grad, rtol=1e-5, atol=1e-6)
+    x = torch.randn(16, 12, 7, 7, device="cuda", requires_grad=True)
+    gamma, beta = torch.rand(12, device="cuda", requires_grad=True), torch.randn(12, device="cuda", requires_grad=True)
+    rm, rv = torch.zeros(12, device="cuda"), torch.ones(12, device="cuda")
+    xr, gr, br = (t.detach().cpu().requires_grad_(True) for t in (x, gamma, beta))
+    rmr, rvr = torch.zeros(12), torch.ones(12)
+    y = gnn.batch_norm_train(x, gamma, beta, rm, rv)
+    yr = F.batch_norm(xr, rmr, rvr, gr, br, True, 0.1, 1e-5)
+    torch.testing.assert_close(y.cpu(), yr, rtol=1e-4, atol=1e-4)
+    torch.testing.assert_close(rm.cpu(), rmr, rtol=1e-4, atol=1e-5)
+    torch.testing.assert_close(rv.cpu(), rvr, rtol=1e-4, atol=1e-5)
+    g = torch.randn_like(y)
+    y.backward(g); yr.backward(g.cpu())
+    for got, want in ((x.grad, xr.grad), (gamma.grad, gr.grad), (beta.grad, br.grad)):
+        torch.testing.assert_close(got.cpu(), want, rtol=1e-3, atol=1e-4)
+
+
+def test_native_cifarnet_matches_torch_model():
+    """CifarNet on hand-written kernels only (conv/pool/tcgen05 GEMM) vs the torch-op model: same
+    state_dict, same loss and gradients up to TF32 rounding of the linear layers."""
+    from garfield_b200.garfieldpp import tools
+    from garfield_b200.ops import nn as gnn
+    cuda_lib()
+    torch.manual_seed(0)
+    torch.backends.cuda.matmul.allow_tf32 = False
+    ours = tools.select_model("cifarnet-native", torch.device("cuda"), "cifar10")
+    ref = tools.select_model("cifarnet", torch.device("cuda"), "cifar10")
+    ref.load_state_dict(ours.state_dict())
+    x, t = torch.randn(25, 3, 32, 32, device="cuda"), torch.randint(0, 10, (25,), device="cuda")
+    la = gnn.cross_entropy(ours(x), t)
+    lb = torch.nn.functional.cross_entropy(ref(x), t)
+    la.backward(); lb.backward()
+    assert abs(la.item() - lb.item()) < 5e-3
+    for (name, p), q in zip(ours.named_parameters(), ref.parameters()):
+        denom = q.grad.abs().max().item() + 1e-6
+        assert (p.grad - q.grad).abs().max().item() / denom < 3e-2, name
