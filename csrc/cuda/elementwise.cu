@@ -10,6 +10,7 @@
 #include <cmath>
 
 #include "gar_common.cuh"
+#include "ptx.cuh"
 #include "garfield_b200.h"
 #include "launch.cuh"
 
@@ -206,6 +207,61 @@ GB_API int gb_broadcast_copy(float const* src, float* const* dsts, int n_dst, in
         for (int k = 0; k < kMaxMirrors; ++k)
             if (k < mir.n) mir.p[k][i] = v;
     }, "broadcast copy");
+}
+
+}  // extern "C"
+
+// --------------------------------------------------------------- cross-GPU readiness flags ---
+//
+// Device-side replacement of the reference's RPC completion / quorum wait (garfieldpp/server.py:134-155):
+// a producer publishes "my buffer for epoch e is complete" with a system-scope release store into a
+// peer-mapped flag word; a consumer kernel spins (system-scope acquire loads) on a table of such
+// flags until all reached the epoch or a deadline passed. Late peers are counted, not waited for:
+// the robust rules tolerate f stale rows by construction.
+//
+// Only meaningful between kernels running on DIFFERENT GPUs (one process per GPU): two kernels that
+// wait on each other on one GPU may never be co-scheduled.
+
+namespace gb {
+namespace {
+__global__ void flag_signal_kernel(uint32_t* flag, uint32_t value) {
+    __threadfence_system();  // everything this stream wrote before is visible before the flag flips
+    ptx::st_release_sys(flag, value);
+}
+
+struct FlagTable {
+    uint32_t* p[kMaxRows];
+};
+
+__global__ void flag_wait_kernel(FlagTable flags, int count, uint32_t value, unsigned long long timeout_ns, uint32_t* late) {
+    int const i = threadIdx.x;
+    if (i >= count) return;
+    unsigned long long const deadline = ptx::globaltimer_ns() + timeout_ns;
+    bool ready = false;
+    while (!(ready = (static_cast<int32_t>(ptx::ld_acquire_sys(flags.p[i]) - value) >= 0))) {
+        if (ptx::globaltimer_ns() > deadline) break;
+        __nanosleep(200);
+    }
+    if (!ready && late != nullptr) atomicAdd(late, 1u);
+}
+}  // namespace
+}  // namespace gb
+
+extern "C" {
+
+GB_API int gb_flag_signal(uint32_t* flag, uint32_t value, void* stream) {
+    flag_signal_kernel<<<1, 1, 0, static_cast<cudaStream_t>(stream)>>>(flag, value);
+    return cuda_check(cudaGetLastError(), "flag signal");
+}
+
+// Wait until every flags[i] >= value (wrap-safe) or `timeout_ns` elapsed; *late += number of flags that
+// did not make it. count <= 64.
+GB_API int gb_flag_wait(uint32_t* const* flags, int count, uint32_t value, uint64_t timeout_ns, uint32_t* late, void* stream) {
+    if (count < 1 || count > kMaxRows) return cuda_fail("flag wait: need 1..64 flags");
+    FlagTable table{};
+    for (int i = 0; i < count; ++i) table.p[i] = flags[i];
+    flag_wait_kernel<<<1, 64, 0, static_cast<cudaStream_t>(stream)>>>(table, count, value, timeout_ns, late);
+    return cuda_check(cudaGetLastError(), "flag wait");
 }
 
 }  // extern "C"

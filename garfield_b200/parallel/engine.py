@@ -59,7 +59,7 @@ class _LocalWorker:
 class SSMWEngine:
     def __init__(self, model, dataset, loss, num_workers, f, gar, batch, optimizer="sgd", opt_args=None, byzantine=None,
                  device=None, group=None, use_graphs=True, train_set=None, seed=1234, gar_kwargs=None, sharded=None,
-                 channels_last=True):
+                 channels_last=True, sync="nccl", flag_timeout=5.0):
         self.rank = dist.get_rank(group) if dist.is_initialized() else 0
         self.world = dist.get_world_size(group) if dist.is_initialized() else 1
         self.group = group
@@ -129,6 +129,20 @@ class SSMWEngine:
                 self.rows.append(self.grad_arena.peer(owner)[j * self.pitch + self.lo:j * self.pitch + self.hi])
             self.mirrors = [self.param_arena.peer(r)[self.lo:self.hi] for r in range(self.world) if r != self.rank]
         self._flag = torch.zeros(1, device=self.device)
+        # sync="flags": ranks synchronise through peer-mapped epoch flags polled by a tiny kernel with a
+        # deadline (late peers are counted in `late_peers` and NOT waited for — their rows are stale, which
+        # the robust rule tolerates like any other Byzantine input) instead of NCCL barriers.
+        self.sync = sync if self.world > 1 else "none"
+        self.flag_timeout_ns = int(flag_timeout * 1e9)
+        self.epoch = 0
+        if self.sync == "flags":
+            self.flag_arena = PeerArena(64, self.device, group)
+            self._late = torch.zeros(1, dtype=torch.int32, device=self.device)
+            word = lambda r, k: self.flag_arena.peer(r).data_ptr() + 4 * k      # flag k of rank r (uint32)
+            self._my_grad_flag, self._my_param_flag = word(self.rank, 0), word(self.rank, 1)
+            self._grad_flags = [word(r, 0) for r in range(self.world)]
+            servers = range(self.world) if self.sharded else [0]
+            self._param_flags = [word(r, 1) for r in servers]
         self._graph = None
         self._copy_stream = None
         self.use_graphs = use_graphs
@@ -275,10 +289,45 @@ class SSMWEngine:
         else:
             opt.step(run(), mirrors=self.mirrors)
 
-    def step(self, iter_num, load=True):
-        """One training iteration. Returns the mean loss of this rank's workers (device scalar)."""
+    # -- flag synchronisation -------------------------------------------------------------------------
+    def _signal(self, flag_ptr, value):
+        import ctypes
+        lib = _lib.require()
+        _lib.check(lib.gb_flag_signal(ctypes.c_void_p(flag_ptr), value, _lib.stream_ptr(self.device)))
+        _lib.count()
+
+    def _wait(self, flag_ptrs, value):
+        import ctypes
+        lib = _lib.require()
+        table = (ctypes.c_void_p * len(flag_ptrs))(*flag_ptrs)
+        _lib.check(lib.gb_flag_wait(table, len(flag_ptrs), value, self.flag_timeout_ns, self._late.data_ptr(), _lib.stream_ptr(self.device)))
+        _lib.count()
+
+    @property
+    def late_peers(self):
+        """Number of (peer, wait) pairs that missed a deadline so far (flags mode; synchronises)."""
+        return int(self._late.item()) if self.sync == "flags" else 0
+
+    def step(self, iter_num, load=True, stall=False):
+        """One training iteration. Returns the mean loss of this rank's workers (device scalar).
+        `stall=True` (fault injection, flags mode) makes this rank withhold its "gradients ready" signal."""
         if load:
             self.load_batches(iter_num)
+        if self.sync == "flags":
+            self.epoch += 1
+            if self.epoch > 1:
+                self._wait(self._param_flags, self.epoch - 1)      # every shard published the previous update
+            self.compute_gradients()
+            if not stall:
+                self._signal(self._my_grad_flag, self.epoch)
+            if self.is_server:
+                self._wait(self._grad_flags, self.epoch)           # all ranks' gradient rows are complete (or late)
+                self.aggregate_and_update()
+                self._signal(self._my_param_flag, self.epoch)
+            self.steps_done += 1
+            if self.workers:
+                return torch.stack([w.loss for w in self.workers]).mean()
+            return torch.zeros((), device=self.device)
         self.compute_gradients()
         self._barrier()                      # all gradient rows are complete
         if self.is_server:
@@ -292,5 +341,7 @@ class SSMWEngine:
     def close(self):
         self._graph = None
         torch.cuda.synchronize(self.device)
+        if self.sync == "flags":
+            self.flag_arena.close()
         self.grad_arena.close()
         self.param_arena.close()

@@ -182,6 +182,12 @@ GB_API int gb_scale(float const* in, float* out, int64_t d, float factor, void* 
 GB_API int gb_attack_drop(float const* in, float* out, int64_t d, float p, uint64_t seed, void* stream);
 GB_API int gb_attack_collude(float const* const* rows, int fw, int64_t d, int kind, float coeff, int nan_single, float* out, void* stream);
 
+/* Cross-GPU readiness flags (system-scope release store / acquire-load spin with a deadline): the
+ * device-side counterpart of the reference's RPC completion + "first n-f replies" quorum wait
+ * (garfieldpp/server.py:134-155). Only for kernels on different GPUs. */
+GB_API int gb_flag_signal(uint32_t* flag, uint32_t value, void* stream);
+GB_API int gb_flag_wait(uint32_t* const* flags, int count, uint32_t value, uint64_t timeout_ns, uint32_t* late, void* stream);
+
 GB_API int gb_axpby(float const* x, float* y, int64_t d, float a, float b, void* stream);
 GB_API int gb_broadcast_copy(float const* src, float* const* dsts, int n_dst, int64_t d, void* stream);
 

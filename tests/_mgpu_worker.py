@@ -37,6 +37,28 @@ def main():
             torch.testing.assert_close(finals[0], finals[1], rtol=1e-4, atol=1e-6, msg=lambda m: "%s sharded != centralized: %s" % (gar, m))
         if rank == 0:
             print("ok", gar, flush=True)
+    # device-side flag synchronisation (no NCCL barrier) gives the same parameters, and a rank that
+    # withholds its signal only costs the others one deadline
+    finals = []
+    for sync in ("nccl", "flags"):
+        eng = SSMWEngine("cifarnet", "synthetic-cifar10", "cross-entropy", 8, 1, "median", 16, "sgd", dict(lr=0.05, momentum=0.9),
+                         use_graphs=False, sharded=True, seed=5, sync=sync, flag_timeout=0.2)
+        for i in range(4):
+            eng.step(i)
+        torch.cuda.synchronize()
+        finals.append(eng.flat.clone())
+        if sync == "flags":
+            assert eng.late_peers == 0
+            eng.step(4, stall=(rank == world - 1))      # the last rank never announces its gradients
+            torch.cuda.synchronize()
+            late = torch.tensor([eng.late_peers], device="cuda")
+            dist.all_reduce(late)
+            assert late.item() >= 1, "the stalled rank must be reported late"
+            assert torch.isfinite(eng.flat).all()
+        eng.close()
+    torch.testing.assert_close(finals[0], finals[1], rtol=0, atol=0)
+    if rank == 0:
+        print("ok flags", flush=True)
     dist.destroy_process_group()
 
 
