@@ -70,3 +70,44 @@ def test_grpc_pull_service():
         client.close()
     finally:
         server.stop(0)
+
+
+def test_tf_style_pull_deployment_in_threads():
+    """1 PS + 4 workers (one Byzantine 'Reverse'), Krum gradients, pull-based gRPC on localhost."""
+    pytest.importorskip("grpc")
+    import importlib.util
+    import os
+    import pathlib
+    import threading
+    import types
+    os.environ.setdefault("GARFIELD_SYNTHETIC", "1")
+    os.environ.setdefault("GARFIELD_SYNTHETIC_SIZE", "600")
+    root = pathlib.Path(__file__).resolve().parent.parent
+    load = lambda name: importlib.util.spec_from_file_location(name, root / "applications" / "TF_style" / (name + ".py"))
+    gen_spec = load("config_generator"); gen = importlib.util.module_from_spec(gen_spec); gen_spec.loader.exec_module(gen)
+    tr_spec = load("trainer"); trainer = importlib.util.module_from_spec(tr_spec); tr_spec.loader.exec_module(trainer)
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        base = s.getsockname()[1]
+    configs = gen.generate(1, 5, base_port=base, strategy_gradient="Krum", byz_workers=1, attack="Reverse")
+    results, errors = {}, []
+
+    def run(name, cfg):
+        args = types.SimpleNamespace(config=cfg, log=False, max_iter=3, dataset="mnist", model="convnet", loss="nll", batch_size=8,
+                                     nbbyzwrks=1, native=False, device="cpu")
+        try:
+            results[name] = trainer.run_node(args)
+        except Exception as err:  # surfaced below
+            errors.append((name, repr(err)))
+
+    threads = [threading.Thread(target=run, args=item) for item in configs.items()]
+    for t in threads:
+        t.start()
+    for t in threads:
+        t.join(timeout=180)
+    assert not errors, errors
+    assert len(results) == 6
+    ps = results["ps0"]
+    assert len(ps.servicer.model_history) == 4 and np.isfinite(ps.flat()).all()
+    for node in results.values():
+        node.stop()
