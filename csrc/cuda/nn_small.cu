@@ -260,6 +260,55 @@ __global__ void __launch_bounds__(kNnThreads) bn_bwd_kernel(int n, int c, int hw
     }
 }
 
+
+// Global average pooling over the spatial dims of NCHW planes: y[p] = mean(x[p, :]); backward broadcasts dy/hw.
+__global__ void __launch_bounds__(kNnThreads) avgpool_fwd_kernel(long long planes, int hw, const float* __restrict__ x, float* __restrict__ y) {
+    long long const p = static_cast<long long>(blockIdx.x) * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    if (p >= planes) return;
+    int const lane = threadIdx.x & 31;
+    float s = 0.0f;
+    for (int i = lane; i < hw; i += 32) s += x[p * hw + i];
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+    if (lane == 0) y[p] = s / static_cast<float>(hw);
+}
+
+__global__ void __launch_bounds__(kNnThreads) avgpool_bwd_kernel(long long total, int hw, const float* __restrict__ dy, float* __restrict__ dx) {
+    float const inv = 1.0f / static_cast<float>(hw);
+    for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < total; i += static_cast<long long>(gridDim.x) * blockDim.x)
+        dx[i] = dy[i / hw] * inv;
+}
+
+// Inverted dropout with a counter-based Philox mask: y = keep ? x / (1 - p) : 0. The same (seed, index) pair
+// regenerates the mask in the backward pass, so no mask tensor is stored.
+__global__ void __launch_bounds__(kNnThreads) dropout_kernel(long long total, float p, unsigned long long seed, const float* __restrict__ x,
+                                                             float* __restrict__ y) {
+    float const scale = 1.0f / (1.0f - p);
+    long long const quads = (total + 3) / 4;
+    for (long long q = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; q < quads; q += static_cast<long long>(gridDim.x) * blockDim.x) {
+        uint4 const r = philox4x32(seed, static_cast<unsigned long long>(q), 3u);
+        uint32_t const bits[4] = {r.x, r.y, r.z, r.w};
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            long long const i = q * 4 + k;
+            if (i < total) y[i] = (u01(bits[k]) >= p) ? x[i] * scale : 0.0f;
+        }
+    }
+}
+
+// Binary cross-entropy on probabilities (nn.BCELoss, mean reduction, log clamped at -100 like torch):
+// per-element loss and d(mean loss)/d(prob).
+__global__ void __launch_bounds__(kNnThreads) bce_kernel(long long total, const float* __restrict__ prob, const float* __restrict__ target,
+                                                         float* __restrict__ loss, float* __restrict__ dprob) {
+    float const inv = 1.0f / static_cast<float>(total);
+    for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < total; i += static_cast<long long>(gridDim.x) * blockDim.x) {
+        float const q = prob[i], t = target[i];
+        float const lq = fmaxf(logf(q), -100.0f), l1q = fmaxf(logf(1.0f - q), -100.0f);
+        loss[i] = -(t * lq + (1.0f - t) * l1q);
+        if (dprob != nullptr) dprob[i] = (q - t) / fmaxf(q * (1.0f - q), 1e-12f) * inv;
+    }
+}
+
 }  // namespace
 }  // namespace gb
 
@@ -315,6 +364,32 @@ GB_API int gb_batchnorm_backward(float const* x, float const* dy, float const* g
                                  float* dgamma, float* dbeta, int n, int c, int hw, void* stream) {
     bn_bwd_kernel<<<c, kNnThreads, 0, static_cast<cudaStream_t>(stream)>>>(n, c, hw, x, dy, gamma, save_mean, save_invstd, dx, dgamma, dbeta);
     return cuda_check(cudaGetLastError(), "batchnorm backward");
+}
+
+
+GB_API int gb_global_avgpool_forward(float const* x, float* y, int64_t planes, int hw, void* stream) {
+    if (planes < 1 || hw < 1) return cuda_fail("avgpool: empty input");
+    avgpool_fwd_kernel<<<static_cast<int>((planes + 7) / 8), kNnThreads, 0, static_cast<cudaStream_t>(stream)>>>(planes, hw, x, y);
+    return cuda_check(cudaGetLastError(), "avgpool forward");
+}
+
+GB_API int gb_global_avgpool_backward(float const* dy, float* dx, int64_t planes, int hw, void* stream) {
+    long long const total = static_cast<long long>(planes) * hw;
+    avgpool_bwd_kernel<<<nn_grid(total), kNnThreads, 0, static_cast<cudaStream_t>(stream)>>>(total, hw, dy, dx);
+    return cuda_check(cudaGetLastError(), "avgpool backward");
+}
+
+// y = dropout(x) with keep probability 1-p; calling it again on dy with the same seed gives dx.
+GB_API int gb_dropout(float const* x, float* y, int64_t total, float p, uint64_t seed, void* stream) {
+    if (p < 0.0f || p >= 1.0f) return cuda_fail("dropout: need 0 <= p < 1");
+    dropout_kernel<<<nn_grid((total + 3) / 4), kNnThreads, 0, static_cast<cudaStream_t>(stream)>>>(total, p, seed, x, y);
+    return cuda_check(cudaGetLastError(), "dropout");
+}
+
+GB_API int gb_bce_loss(float const* prob, float const* target, float* loss, float* dprob, int64_t total, void* stream) {
+    if (total < 1) return cuda_fail("bce: empty input");
+    bce_kernel<<<nn_grid(total), kNnThreads, 0, static_cast<cudaStream_t>(stream)>>>(total, prob, target, loss, dprob);
+    return cuda_check(cudaGetLastError(), "bce loss");
 }
 
 }  // extern "C"

@@ -46,6 +46,11 @@ def _declare(h):
     h.gb_batchnorm_backward.argtypes = [vp] * 8 + [i32, i32, i32, vp]
     h.gb_flag_signal.argtypes = [vp, ctypes.c_uint32, vp]
     h.gb_flag_wait.argtypes = [pp, i32, ctypes.c_uint32, u64, vp, vp]
+    h.gb_multi_copy.argtypes = [pp, vp, vp, i32, vp, vp]
+    h.gb_global_avgpool_forward.argtypes = [vp, vp, i64, i32, vp]
+    h.gb_global_avgpool_backward.argtypes = [vp, vp, i64, i32, vp]
+    h.gb_dropout.argtypes = [vp, vp, i64, f32, u64, vp]
+    h.gb_bce_loss.argtypes = [vp, vp, vp, vp, i64, vp]
     h.gb_sgd_step.argtypes = [vp, vp, vp, i64, f32, f32, f32, f32, i32, i32, pp, i32, vp]
     h.gb_adam_step.argtypes = [vp, vp, vp, vp, i64, f32, f32, f32, f32, f32, i32, i32, vp]
     h.gb_rmsprop_step.argtypes = [vp, vp, vp, vp, i64, f32, f32, f32, f32, f32, vp]

@@ -258,3 +258,95 @@ def batch_norm_train(x, gamma, beta, running_mean=None, running_var=None, eps=1e
         y = torch.nn.functional.batch_norm(x, running_mean, running_var, gamma, beta, True, momentum, eps)
         return torch.relu(y) if relu else y
     return _BatchNormFn.apply(x, gamma, beta, running_mean, running_var, eps, momentum, relu)
+
+
+class _GlobalAvgPoolFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x):
+        x = x.contiguous().float()
+        n, c = x.shape[0], x.shape[1]
+        hw = x.numel() // (n * c)
+        y = torch.empty(n, c, device=x.device)
+        with torch.cuda.device(x.device):
+            _lib.check(_lib.require().gb_global_avgpool_forward(_ptr(x), _ptr(y), n * c, hw, _lib.stream_ptr(x.device)))
+        _lib.count()
+        ctx.shape = x.shape
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        dy = dy.contiguous().float()
+        dx = torch.empty(ctx.shape, device=dy.device)
+        n, c = ctx.shape[0], ctx.shape[1]
+        with torch.cuda.device(dy.device):
+            _lib.check(_lib.require().gb_global_avgpool_backward(_ptr(dy), _ptr(dx), n * c, dx.numel() // (n * c), _lib.stream_ptr(dy.device)))
+        _lib.count()
+        return dx
+
+
+def global_avg_pool(x):
+    """Mean over the spatial dimensions: [N, C, H, W] → [N, C]."""
+    if not _on_device(x):
+        return x.mean(dim=tuple(range(2, x.dim())))
+    return _GlobalAvgPoolFn.apply(x)
+
+
+class _DropoutFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, p, seed):
+        x = x.contiguous().float()
+        y = torch.empty_like(x)
+        with torch.cuda.device(x.device):
+            _lib.check(_lib.require().gb_dropout(_ptr(x), _ptr(y), x.numel(), float(p), int(seed), _lib.stream_ptr(x.device)))
+        _lib.count()
+        ctx.cfg = (float(p), int(seed))
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        p, seed = ctx.cfg
+        dy = dy.contiguous().float()
+        dx = torch.empty_like(dy)
+        with torch.cuda.device(dy.device):
+            _lib.check(_lib.require().gb_dropout(_ptr(dy), _ptr(dx), dy.numel(), p, seed, _lib.stream_ptr(dy.device)))
+        _lib.count()
+        return dx, None, None
+
+
+_dropout_calls = [0]
+
+
+def dropout(x, p=0.5, training=True, seed=None):
+    """Inverted dropout whose mask is regenerated (not stored) in the backward pass."""
+    if not training or p == 0.0:
+        return x
+    if not _on_device(x):
+        return torch.nn.functional.dropout(x, p, True)
+    if seed is None:
+        _dropout_calls[0] += 1
+        seed = (torch.initial_seed() * 0x9E3779B97F4A7C15 + _dropout_calls[0]) & 0x7FFFFFFFFFFFFFFF
+    return _DropoutFn.apply(x, p, seed)
+
+
+class _BceFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, prob, target):
+        prob, target = prob.contiguous().float(), target.contiguous().float()
+        loss, grad = torch.empty_like(prob), torch.empty_like(prob)
+        with torch.cuda.device(prob.device):
+            _lib.check(_lib.require().gb_bce_loss(_ptr(prob), _ptr(target), _ptr(loss), _ptr(grad), prob.numel(), _lib.stream_ptr(prob.device)))
+        _lib.count()
+        ctx.save_for_backward(grad)
+        return loss.mean()
+
+    @staticmethod
+    def backward(ctx, dloss):
+        (grad,) = ctx.saved_tensors
+        return grad * dloss, None
+
+
+def binary_cross_entropy(prob, target):
+    """nn.BCELoss (mean reduction) on probabilities."""
+    if not _on_device(prob):
+        return torch.nn.functional.binary_cross_entropy(prob, target)
+    return _BceFn.apply(prob, target)

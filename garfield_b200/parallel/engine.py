@@ -35,10 +35,25 @@ from ..ops.optim import FlatOptimizer
 __all__ = ["SSMWEngine"]
 
 
+def _skip_bn_counters(module):
+    """BatchNorm's `num_batches_tracked += 1` is a separate int64 kernel per layer and step (53 launches per
+    ResNet-50 pass) that only matters when momentum is None; keep the running statistics, drop the counter."""
+    import types
+
+    def forward(self, x):
+        return torch.nn.functional.batch_norm(x, self.running_mean, self.running_var, self.weight, self.bias,
+                                              self.training or self.running_mean is None, self.momentum, self.eps)
+
+    for m in module.modules():
+        if isinstance(m, torch.nn.modules.batchnorm._BatchNorm) and m.momentum is not None and m.track_running_stats:
+            m.forward = types.MethodType(forward, m)
+
+
 class _LocalWorker:
     """One worker hosted by this rank: model replica, static input buffers, gradient row."""
 
-    def __init__(self, wid, replica, row, loss_fn, batch_shape, target_shape, target_dtype, device, attack=None, channels_last=False):
+    def __init__(self, wid, replica, row, loss_fn, batch_shape, target_shape, target_dtype, device, attack=None, channels_last=False,
+                 gather=True):
         self.wid, self.replica, self.row, self.loss_fn, self.attack = wid, replica, row, loss_fn, attack
         self.data = torch.zeros(batch_shape, device=device)
         if channels_last and len(batch_shape) == 4:
@@ -46,20 +61,56 @@ class _LocalWorker:
         self.target = torch.zeros(target_shape, dtype=target_dtype, device=device)
         self.loss = torch.zeros((), device=device)
         self.stream = torch.cuda.Stream(device=device) if device.type == "cuda" else None
-        replica.bind_grads(row)  # permanent: autograd accumulates in place into the arena row
+        self.gather = gather
+        if not gather:
+            replica.bind_grads(row)  # autograd accumulates in place into the arena row (one add kernel per parameter)
 
     def forward_backward(self):
-        self.row.zero_()
-        self.replica.module.train()
-        loss = self.loss_fn(self.replica.module(self.data), self.target)
+        module = self.replica.module
+        module.train()
+        if not self.gather:
+            self.row.zero_()
+            loss = self.loss_fn(module(self.data), self.target)
+            loss.backward()
+            self.loss.copy_(loss.detach())
+            return
+        # let autograd hand over its freshly produced gradient tensors, then gather all of them into the
+        # row with ONE multi-tensor copy launch (the table lives in the kernel parameters → graph-safe)
+        params = list(module.parameters())
+        for p in params:
+            p.grad = None
+        loss = self.loss_fn(module(self.data), self.target)
         loss.backward()
         self.loss.copy_(loss.detach())
+        self._gather(params)
+        for p in params:
+            p.grad = None
+
+    def _gather(self, params):
+        import ctypes
+        srcs, offs, sizes, slow = [], [], [], []
+        for p, (off, n, shape) in zip(params, self.replica.slices):
+            g = p.grad
+            if g is None:
+                self.row[off:off + n].zero_()
+            elif g.dtype == torch.float32 and g.stride() == p.stride() and g.is_cuda:
+                srcs.append(g.data_ptr()); offs.append(off); sizes.append(n)
+            else:
+                slow.append((off, n, shape, g))
+        if srcs:
+            k = len(srcs)
+            lib = _lib.require()
+            _lib.check(lib.gb_multi_copy((ctypes.c_void_p * k)(*srcs), (ctypes.c_uint64 * k)(*offs), (ctypes.c_uint32 * k)(*sizes), k,
+                                         self.row.data_ptr(), _lib.stream_ptr(self.row.device)))
+            _lib.count((k + 111) // 112)
+        for off, n, shape, g in slow:
+            self.replica._view(self.row, off, n, shape).copy_(g)
 
 
 class SSMWEngine:
     def __init__(self, model, dataset, loss, num_workers, f, gar, batch, optimizer="sgd", opt_args=None, byzantine=None,
                  device=None, group=None, use_graphs=True, train_set=None, seed=1234, gar_kwargs=None, sharded=None,
-                 channels_last=True, sync="nccl", flag_timeout=5.0):
+                 channels_last=True, sync="nccl", flag_timeout=5.0, gather_grads=True, fast_bn=True):
         self.rank = dist.get_rank(group) if dist.is_initialized() else 0
         self.world = dist.get_world_size(group) if dist.is_initialized() else 1
         self.group = group
@@ -76,6 +127,8 @@ class SSMWEngine:
 
         torch.manual_seed(seed)
         module = tools.select_model(model, self.device, dataset)
+        if fast_bn:
+            _skip_bn_counters(module)
         self.channels_last = bool(channels_last)
         if self.channels_last:
             module = module.to(memory_format=torch.channels_last)
@@ -111,7 +164,7 @@ class SSMWEngine:
             self.train_sets[wid] = batches
             x0, y0 = batches[0]
             self.workers.append(_LocalWorker(wid, replica, row, loss_fn, tuple(x0.shape), tuple(y0.shape), y0.dtype, self.device,
-                                             attack=self.byzantine.get(wid), channels_last=self.channels_last))
+                                             attack=self.byzantine.get(wid), channels_last=self.channels_last, gather=gather_grads))
 
         # server state (whole vector on rank 0, or this rank's coordinate slice when sharded)
         if self.sharded:

@@ -165,6 +165,13 @@ GB_API int gb_batchnorm_forward(float const* x, float const* gamma, float const*
 GB_API int gb_batchnorm_backward(float const* x, float const* dy, float const* gamma, float const* save_mean, float const* save_invstd, float* dx,
                                  float* dgamma, float* dbeta, int n, int c, int hw, void* stream);
 
+GB_API int gb_global_avgpool_forward(float const* x, float* y, int64_t planes, int hw, void* stream);
+GB_API int gb_global_avgpool_backward(float const* dy, float* dx, int64_t planes, int hw, void* stream);
+/* Inverted dropout with a regenerable Philox mask (apply to dy with the same seed for the backward pass). */
+GB_API int gb_dropout(float const* x, float* y, int64_t total, float p, uint64_t seed, void* stream);
+/* nn.BCELoss (mean): per-element losses and d(mean loss)/d(prob). ref: garfieldpp/tools.py:52 */
+GB_API int gb_bce_loss(float const* prob, float const* target, float* loss, float* dprob, int64_t total, void* stream);
+
 /* Flat-arena optimizer steps (torch.optim semantics). ref: garfieldpp/server.py:277-287,
  * garfieldpp/tools.py:107-123 (sgd, adam, adamw, rmsprop, adagrad — run on the HOST there). */
 GB_API int gb_sgd_step(float* param, float const* grad, float* mom, int64_t d, float lr, float momentum, float dampening,
@@ -188,6 +195,10 @@ GB_API int gb_attack_collude(float const* const* rows, int fw, int64_t d, int ki
 GB_API int gb_flag_signal(uint32_t* flag, uint32_t value, void* stream);
 GB_API int gb_flag_wait(uint32_t* const* flags, int count, uint32_t value, uint64_t timeout_ns, uint32_t* late, void* stream);
 
+/* Gather `count` separate device tensors into their slots (element offsets) of one flat vector in one
+ * launch per 112 tensors; table passed in kernel parameters (CUDA-graph capturable).
+ * ref: torch.cat of the per-parameter gradients, garfieldpp/worker.py:93-94. */
+GB_API int gb_multi_copy(float const* const* srcs, uint64_t const* dst_offsets, uint32_t const* sizes, int count, float* dst, void* stream);
 GB_API int gb_axpby(float const* x, float* y, int64_t d, float a, float b, void* stream);
 GB_API int gb_broadcast_copy(float const* src, float* const* dsts, int n_dst, int64_t d, void* stream);
 

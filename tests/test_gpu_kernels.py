@@ -349,3 +349,65 @@ def test_native_cifarnet_matches_torch_model():
     for (name, p), q in zip(ours.named_parameters(), ref.parameters()):
         denom = q.grad.abs().max().item() + 1e-6
         assert (p.grad - q.grad).abs().max().item() / denom < 3e-2, name
+
+
+def test_engine_gradient_gather_matches_bound_grads():
+    """One multi-tensor gather launch after backward == autograd accumulating into rows bound as .grad;
+    channels-last arenas == NCHW arenas (in reference order); CUDA graph == eager."""
+    import os
+    os.environ.setdefault("GARFIELD_SYNTHETIC_SIZE", "1500")
+    from garfield_b200.parallel.engine import SSMWEngine
+    cuda_lib()
+    finals = {}
+    for tag, kw in (("bound", dict(gather_grads=False, fast_bn=False, use_graphs=False)),
+                    ("gather", dict(gather_grads=True, fast_bn=True, use_graphs=False)),
+                    ("graph", dict(gather_grads=True, fast_bn=True, use_graphs=True)),
+                    ("nchw", dict(gather_grads=True, fast_bn=True, use_graphs=False, channels_last=False))):
+        eng = SSMWEngine("cnn", "synthetic-cifar10", "cross-entropy", 7, 1, "median", 8, "sgd", dict(lr=0.02, momentum=0.9),
+                         byzantine={6: "reverse"}, seed=3, **kw)
+        for m in eng.master.module.modules():   # dropout would make the runs incomparable
+            if isinstance(m, (torch.nn.Dropout, torch.nn.Dropout2d)):
+                m.p = 0.0
+        for w in eng.workers:
+            for m in w.replica.module.modules():
+                if isinstance(m, (torch.nn.Dropout, torch.nn.Dropout2d)):
+                    m.p = 0.0
+        for i in range(3):
+            eng.step(i)
+        torch.cuda.synchronize()
+        finals[tag] = eng.master.to_reference_order(eng.flat).clone()
+        bn = [b.clone() for b in eng.workers[0].replica.module.buffers() if b.dtype == torch.float32]
+        finals[tag + "_bn"] = torch.cat([b.reshape(-1) for b in bn])
+        eng.close()
+    for tag in ("gather", "graph", "nchw"):
+        diff = (finals[tag] - finals["bound"]).abs()
+        assert diff.max().item() < 2e-3 and (diff > 2e-4).float().mean().item() < 1e-4, "%s vs bound: max %g" % (tag, diff.max().item())
+        torch.testing.assert_close(finals[tag + "_bn"], finals["bound_bn"], rtol=1e-3, atol=1e-4)
+
+
+def test_avgpool_dropout_bce_kernels():
+    from garfield_b200.ops import nn as gnn
+    cuda_lib()
+    F = torch.nn.functional
+    x = torch.randn(9, 7, 5, 5, device="cuda", requires_grad=True)
+    xr = x.detach().cpu().requires_grad_(True)
+    y, yr = gnn.global_avg_pool(x), xr.mean(dim=(2, 3))
+    torch.testing.assert_close(y.cpu(), yr, rtol=1e-5, atol=1e-6)
+    g = torch.randn_like(y)
+    y.backward(g); yr.backward(g.cpu())
+    torch.testing.assert_close(x.grad.cpu(), xr.grad, rtol=1e-5, atol=1e-6)
+    v = torch.randn(100003, device="cuda", requires_grad=True)
+    d = gnn.dropout(v, 0.3, True, seed=5)
+    kept = d != 0
+    assert 0.68 < kept.float().mean().item() < 0.72
+    torch.testing.assert_close(d[kept], v.detach()[kept] / 0.7)
+    d.sum().backward()
+    torch.testing.assert_close(v.grad, kept.float() / 0.7)            # same mask regenerated in backward
+    assert torch.equal(gnn.dropout(v, 0.3, False), v)
+    prob = torch.rand(64, 1, device="cuda").clamp(1e-4, 1 - 1e-4).requires_grad_(True)
+    tgt = (torch.rand(64, 1, device="cuda") > 0.5).float()
+    pr = prob.detach().cpu().requires_grad_(True)
+    a, b = gnn.binary_cross_entropy(prob, tgt), F.binary_cross_entropy(pr, tgt.cpu())
+    a.backward(); b.backward()
+    torch.testing.assert_close(a.cpu(), b, rtol=1e-5, atol=1e-6)
+    torch.testing.assert_close(prob.grad.cpu(), pr.grad, rtol=1e-4, atol=1e-6)
