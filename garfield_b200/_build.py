@@ -142,13 +142,26 @@ def build_all(force=False):
     return build_cpu(force), build_cuda(force)
 
 
+def _locked_build(builder):
+    """Run `builder` under an inter-process file lock: under torchrun every rank imports the package at
+    the same time and only one of them may compile/link (the others then find everything up to date)."""
+    import fcntl
+    LIBDIR.mkdir(parents=True, exist_ok=True)
+    with open(LIBDIR / ".build.lock", "w") as lock_file:
+        fcntl.flock(lock_file, fcntl.LOCK_EX)
+        try:
+            return builder()
+        finally:
+            fcntl.flock(lock_file, fcntl.LOCK_UN)
+
+
 def _load(key, path, builder):
     with _lock:
         if key in _handles:
             return _handles[key]
         if not os.environ.get("GARFIELD_NO_BUILD"):
             try:
-                builder()
+                _locked_build(builder)
             except Exception as err:
                 if not path.exists():
                     raise
