@@ -359,7 +359,7 @@ def test_engine_gradient_gather_matches_bound_grads():
     from garfield_b200.parallel.engine import SSMWEngine
     cuda_lib()
     finals = {}
-    for tag, kw in (("bound", dict(gather_grads=False, fast_bn=False, use_graphs=False)),
+    for tag, kw in (("bound", dict(gather_grads=False, fast_bn=False, use_graphs=False, split_backward=False)),
                     ("gather", dict(gather_grads=True, fast_bn=True, use_graphs=False)),
                     ("graph", dict(gather_grads=True, fast_bn=True, use_graphs=True)),
                     ("nchw", dict(gather_grads=True, fast_bn=True, use_graphs=False, channels_last=False))):
