@@ -47,6 +47,7 @@ def parse_args(argv=None):
     ap.add_argument("--gar", default="krum", help="primary rule for `value` (krum | median | bulyan | ...)")
     ap.add_argument("--also", default="median,bulyan", help="other rules reported under per_gar ('' to skip)")
     ap.add_argument("--no-graphs", action="store_true")
+    ap.add_argument("--sync", default="nccl", choices=["nccl", "flags"], help="inter-rank synchronisation (N > 1)")
     return ap.parse_args(argv)
 
 
@@ -159,7 +160,7 @@ def run_gar(gar, args, rank, world, local, full):
     from garfield_b200.ops import _lib
     from garfield_b200.parallel.engine import SSMWEngine
     torch.backends.cudnn.benchmark = True
-    engine = SSMWEngine(MODEL, DATASET, LOSS, N_WORKERS, F_BYZ, gar, BATCH, "sgd", OPT_ARGS, use_graphs=not args.no_graphs)
+    engine = SSMWEngine(MODEL, DATASET, LOSS, N_WORKERS, F_BYZ, gar, BATCH, "sgd", OPT_ARGS, use_graphs=not args.no_graphs, sync=args.sync)
     it = 0
     for _ in range(max(args.warmup, 3)):
         engine.step(it).item()

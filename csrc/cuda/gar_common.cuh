@@ -91,13 +91,22 @@ struct PairwiseArgs {
 
 // ------------------------------------------------------------------- sorting networks ---
 
-// Batcher odd-even merge sort on a register array (NP a power of two): 19 / 63 / 191 / 543
-// compare-exchanges for NP = 8 / 16 / 32 / 64. The comparator list is a constexpr table and
-// the network is expanded with a fold expression, so every register index is a constant
-// expression (a partially unrolled loop nest would push the array to local memory).
+// Batcher odd-even merge sort on a register array of NP values (NP any size <= 64): the network of
+// the next power of two, pruned of every comparator that touches a position >= NP (those positions
+// would hold +inf padding, which such a comparator never moves): 19 / 42 / 63 / 103 / 132 / 162 / 191 /
+// 384 / 543 compare-exchanges for NP = 8 / 12 / 16 / 20 / 24 / 28 / 32 / 48 / 64. The comparator list is a
+// constexpr table and the network is expanded with a fold expression, so every register index is a
+// constant expression (a partially unrolled loop nest would push the array to local memory).
 // NaNs must have been replaced beforehand (fminf/fmaxf drop them).
+constexpr int next_pow2(int v) {
+    int p = 1;
+    while (p < v) p <<= 1;
+    return p;
+}
+
 template <int NP>
 struct OddEvenNetwork {
+    static constexpr int kFull = next_pow2(NP);
     static constexpr int kMax = NP <= 2 ? 1 : NP * 9;  // >= comparator count for NP <= 64
     struct Table {
         int a[kMax];
@@ -107,11 +116,11 @@ struct OddEvenNetwork {
     static constexpr Table build() {
         Table t{};
         t.count = 0;
-        for (int p = 1; p < NP; p <<= 1)
+        for (int p = 1; p < kFull; p <<= 1)
             for (int k = p; k >= 1; k >>= 1)
-                for (int j = k % p; j + k < NP; j += 2 * k)
+                for (int j = k % p; j + k < kFull; j += 2 * k)
                     for (int i = 0; i < k; ++i)
-                        if ((i + j) / (2 * p) == (i + j + k) / (2 * p)) {
+                        if ((i + j) / (2 * p) == (i + j + k) / (2 * p) && i + j + k < NP) {
                             t.a[t.count] = i + j;
                             t.b[t.count] = i + j + k;
                             ++t.count;

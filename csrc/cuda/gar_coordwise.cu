@@ -69,7 +69,8 @@ extern "C" GB_API int gb_coordwise(float const* const* rows, int n, int64_t d, i
     a.tile = pick_tile(n);
     a.use_tma = aligned ? 1 : 0;  // otherwise every coordinate takes the scalar direct-load path
 
-    int const np = rule == kRuleLinear ? 1 : cnt <= 4 ? 4 : cnt <= 8 ? 8 : cnt <= 16 ? 16 : cnt <= 32 ? 32 : 64;
+    // register-array size of the sorting network: the next bucket >= cnt (pruned Batcher networks)
+    int const np = rule == kRuleLinear ? 1 : cnt <= 4 ? 4 : cnt <= 32 ? (cnt + 3) / 4 * 4 : cnt <= 48 ? 48 : 64;
     int const w_floats = theta > 0 ? ((np * n + 31) / 32) * 32 : 0;
     size_t const smem = sizeof(float) * (static_cast<size_t>(w_floats) + static_cast<size_t>(kStages) * n * a.tile);
     long long const tiles = (d + a.tile - 1) / a.tile;
@@ -80,13 +81,19 @@ extern "C" GB_API int gb_coordwise(float const* const* rows, int n, int64_t d, i
     cudaStream_t const st = static_cast<cudaStream_t>(stream);
 
     cudaError_t err;
+    int const g = static_cast<int>(grid);
     switch (np) {
-        case 1: err = launch_coordwise<1, kRuleLinear, true, 4>(a, static_cast<int>(grid), smem, st); break;
-        case 4: err = dispatch_coordwise<4>(a, static_cast<int>(grid), smem, st); break;
-        case 8: err = dispatch_coordwise<8>(a, static_cast<int>(grid), smem, st); break;
-        case 16: err = dispatch_coordwise<16>(a, static_cast<int>(grid), smem, st); break;
-        case 32: err = dispatch_coordwise<32>(a, static_cast<int>(grid), smem, st); break;
-        default: err = dispatch_coordwise<64>(a, static_cast<int>(grid), smem, st); break;
+        case 1: err = launch_coordwise<1, kRuleLinear, true, 4>(a, g, smem, st); break;
+        case 4: err = dispatch_coordwise<4>(a, g, smem, st); break;
+        case 8: err = dispatch_coordwise<8>(a, g, smem, st); break;
+        case 12: err = dispatch_coordwise<12>(a, g, smem, st); break;
+        case 16: err = dispatch_coordwise<16>(a, g, smem, st); break;
+        case 20: err = dispatch_coordwise<20>(a, g, smem, st); break;
+        case 24: err = dispatch_coordwise<24>(a, g, smem, st); break;
+        case 28: err = dispatch_coordwise<28>(a, g, smem, st); break;
+        case 32: err = dispatch_coordwise<32>(a, g, smem, st); break;
+        case 48: err = dispatch_coordwise<48>(a, g, smem, st); break;
+        default: err = dispatch_coordwise<64>(a, g, smem, st); break;
     }
     return cuda_check(err, "coordwise launch");
 }
