@@ -350,3 +350,53 @@ def binary_cross_entropy(prob, target):
     if not _on_device(prob):
         return torch.nn.functional.binary_cross_entropy(prob, target)
     return _BceFn.apply(prob, target)
+
+
+# ------------------------------------------------------------ fused channels-last BatchNorm (+ add) (+ ReLU) ---
+
+class _FusedBnFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, gamma, beta, residual, running_mean, running_var, eps, momentum, relu):
+        n, c, h, w = x.shape
+        rows = n * h * w
+        y = torch.empty_like(x)                      # keeps the channels-last strides of x
+        mean, invstd = torch.empty(c, device=x.device), torch.empty(c, device=x.device)
+        with torch.cuda.device(x.device):
+            _lib.check(_lib.require().gb_bn_nhwc_forward(_ptr(x), _ptr(residual), _ptr(gamma), _ptr(beta), _ptr(y), _ptr(mean), _ptr(invstd),
+                                                         _ptr(running_mean), _ptr(running_var), rows, c, float(eps), float(momentum),
+                                                         int(relu), _lib.stream_ptr(x.device)))
+        _lib.count()
+        ctx.save_for_backward(x, gamma, mean, invstd, y if relu else None)
+        ctx.cfg = (rows, c, relu, residual is not None)
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        x, gamma, mean, invstd, y = ctx.saved_tensors
+        rows, c, relu, has_res = ctx.cfg
+        if not dy.is_contiguous(memory_format=torch.channels_last):
+            dy = dy.contiguous(memory_format=torch.channels_last)
+        dx = torch.empty_like(x)
+        dres = torch.empty_like(x) if has_res else None
+        dgamma, dbeta = torch.empty(c, device=x.device), torch.empty(c, device=x.device)
+        with torch.cuda.device(x.device):
+            _lib.check(_lib.require().gb_bn_nhwc_backward(_ptr(x), _ptr(y), _ptr(dy), _ptr(gamma), _ptr(mean), _ptr(invstd), _ptr(dx), _ptr(dres),
+                                                          _ptr(dgamma), _ptr(dbeta), rows, c, int(relu), _lib.stream_ptr(x.device)))
+        _lib.count()
+        return dx, dgamma, dbeta, dres, None, None, None, None, None
+
+
+def fused_batch_norm(x, bn, residual=None, relu=True):
+    """`[relu](bn(x) [+ residual])` for a `BatchNorm2d` module `bn` in ONE kernel (training mode,
+    channels-last fp32 CUDA activations); anything else takes the equivalent torch ops."""
+    usable = (bn.training and x.is_cuda and x.dtype == torch.float32 and x.dim() == 4 and bn.affine and bn.momentum is not None
+              and x.shape[1] % 4 == 0 and x.is_contiguous(memory_format=torch.channels_last) and _lib.available()
+              and (residual is None or (residual.shape == x.shape and residual.is_contiguous(memory_format=torch.channels_last))))
+    if not usable:
+        y = torch.nn.functional.batch_norm(x, bn.running_mean, bn.running_var, bn.weight, bn.bias, bn.training or bn.running_mean is None,
+                                           bn.momentum if bn.momentum is not None else 0.1, bn.eps)
+        if residual is not None:
+            y = y + residual
+        return torch.relu(y) if relu else y
+    return _FusedBnFn.apply(x, bn.weight, bn.bias, residual, bn.running_mean if bn.track_running_stats else None,
+                            bn.running_var if bn.track_running_stats else None, bn.eps, bn.momentum, relu)

@@ -175,6 +175,9 @@ class SSMWEngine:
         module = tools.select_model(model, self.device, dataset)
         if fast_bn:
             _skip_bn_counters(module)
+            if channels_last:
+                from ..models.fused_resnet import fuse_resnet_blocks
+                fuse_resnet_blocks(module)   # BN + ReLU (+ residual add) in one hand-written kernel per block stage
         self.channels_last = bool(channels_last)
         if self.channels_last:
             module = module.to(memory_format=torch.channels_last)
@@ -447,6 +450,55 @@ class SSMWEngine:
         if self.workers:
             return torch.stack([w.loss for w in self.workers]).mean()
         return torch.zeros((), device=self.device)
+
+    # -- evaluation and checkpoints -----------------------------------------------------------------------
+    def accuracy(self, batches):
+        """Top-1 accuracy (percent) of the current parameters on `batches` [(x, y), ...], evaluated with
+        local worker 0's BatchNorm statistics (the master module never runs a training forward)."""
+        module = self.workers[0].replica.module if self.workers else self.master.module
+        was_training = module.training
+        module.eval()
+        correct = total = 0
+        with torch.no_grad():
+            for x, y in batches:
+                x = x.to(self.device, non_blocking=True)
+                if self.channels_last and x.dim() == 4:
+                    x = x.contiguous(memory_format=torch.channels_last)
+                correct += int(module(x).max(1)[1].eq(y.to(self.device)).sum())
+                total += y.numel()
+        module.train(was_training)
+        return 100.0 * correct / max(total, 1)
+
+    def save_checkpoint(self, path):
+        """Write `<path>.rank<r>`: parameters as a torch `state_dict` (logical layout), this rank's optimizer
+        shard, its workers' BatchNorm buffers, the step counter and the RNG state."""
+        self.wait_published()
+        torch.cuda.synchronize(self.device)
+        payload = {"format": 1, "step": self.steps_done, "lo": self.lo, "hi": self.hi, "world": self.world,
+                   "model": {k: v.detach().cpu().contiguous() for k, v in self.master.module.state_dict().items()},
+                   "optimizer": self.optimizer.state_dict() if self.optimizer is not None else None,
+                   "buffers": {w.wid: {k: v.detach().cpu() for k, v in w.replica.module.named_buffers()} for w in self.workers},
+                   "rng": {"cpu": torch.get_rng_state(), "cuda": torch.cuda.get_rng_state(self.device)}}
+        torch.save(payload, "%s.rank%d" % (path, self.rank))
+
+    def load_checkpoint(self, path):
+        """Restore what `save_checkpoint` wrote (same world size and sharding)."""
+        payload = torch.load("%s.rank%d" % (path, self.rank), map_location="cpu", weights_only=False)
+        if payload["world"] != self.world or (payload["lo"], payload["hi"]) != (self.lo, self.hi):
+            raise ValueError("checkpoint was written with a different world size / sharding")
+        self.master.load_state_dict(payload["model"])          # copies into the arena views
+        if self.optimizer is not None and payload["optimizer"] is not None:
+            self.optimizer.load_state_dict(payload["optimizer"])
+        for w in self.workers:
+            own = dict(w.replica.module.named_buffers())
+            with torch.no_grad():
+                for k, v in payload["buffers"].get(w.wid, {}).items():
+                    own[k].copy_(v)
+        self.steps_done = payload["step"]
+        torch.set_rng_state(payload["rng"]["cpu"])
+        torch.cuda.set_rng_state(payload["rng"]["cuda"], self.device)
+        self._barrier()
+        return payload["step"]
 
     def close(self):
         self._graph = None

@@ -165,6 +165,15 @@ GB_API int gb_batchnorm_forward(float const* x, float const* gamma, float const*
 GB_API int gb_batchnorm_backward(float const* x, float const* dy, float const* gamma, float const* save_mean, float const* save_invstd, float* dx,
                                  float* dgamma, float* dbeta, int n, int c, int hw, void* stream);
 
+/* Fused training-mode BatchNorm for channels-last activations [rows = N*H*W, C]: y = [ReLU](BN(x) [+ residual]) in one
+ * launch, and its backward (dx, dgamma, dbeta and the masked gradient of the skip path) in one launch.
+ * ref: cuDNN/ATen BatchNorm2d + ReLU + residual add in the torchvision ResNet blocks (garfieldpp/tools.py:69-75). */
+GB_API int gb_bn_nhwc_forward(float const* x, float const* residual, float const* gamma, float const* beta, float* y, float* save_mean,
+                              float* save_invstd, float* running_mean, float* running_var, int rows, int C, float eps, float momentum, int relu,
+                              void* stream);
+GB_API int gb_bn_nhwc_backward(float const* x, float const* y, float const* dy, float const* gamma, float const* save_mean,
+                               float const* save_invstd, float* dx, float* d_residual, float* dgamma, float* dbeta, int rows, int C, int relu,
+                               void* stream);
 GB_API int gb_global_avgpool_forward(float const* x, float* y, int64_t planes, int hw, void* stream);
 GB_API int gb_global_avgpool_backward(float const* dy, float* dx, int64_t planes, int hw, void* stream);
 /* Inverted dropout with a regenerable Philox mask (apply to dy with the same seed for the backward pass). */

@@ -412,3 +412,93 @@ def test_avgpool_dropout_bce_kernels():
     a.backward(); b.backward()
     torch.testing.assert_close(a.cpu(), b, rtol=1e-5, atol=1e-6)
     torch.testing.assert_close(prob.grad.cpu(), pr.grad, rtol=1e-4, atol=1e-6)
+
+
+def test_engine_checkpoint_resume_and_accuracy(tmp_path):
+    import os
+    os.environ.setdefault("GARFIELD_SYNTHETIC_SIZE", "1500")
+    from garfield_b200.garfieldpp.datasets import DatasetManager
+    from garfield_b200.parallel.engine import SSMWEngine
+    cuda_lib()
+    torch.backends.cudnn.deterministic = True
+    try:
+        def make_engine():
+            return SSMWEngine("cifarnet", "synthetic-cifar10", "cross-entropy", 7, 1, "krum", 16, "sgd", dict(lr=0.05, momentum=0.9),
+                              byzantine={6: "reverse"}, use_graphs=False, seed=11)
+        a = make_engine()
+        for i in range(3):
+            a.step(i)
+        a.save_checkpoint(str(tmp_path / "ck"))
+        for i in range(3, 6):
+            a.step(i)
+        torch.cuda.synchronize()
+        want = a.flat.clone()
+        test_set = DatasetManager("synthetic-cifar10", 16, 7, 8, 1).get_test_set()
+        acc = a.accuracy(test_set[:3])
+        assert 0.0 <= acc <= 100.0
+        a.close()
+        b = make_engine()
+        assert b.load_checkpoint(str(tmp_path / "ck")) == 3
+        for i in range(3, 6):
+            b.step(i)
+        torch.cuda.synchronize()
+        assert torch.equal(b.flat, want), (b.flat - want).abs().max().item()
+        b.close()
+    finally:
+        torch.backends.cudnn.deterministic = False
+
+
+def test_fused_nhwc_batchnorm_matches_torch():
+    from garfield_b200.ops import nn as gnn
+    cuda_lib()
+    torch.manual_seed(1)
+    for (n, c, h) in [(25, 64, 16), (25, 256, 8), (25, 2048, 1), (3, 12, 5)]:
+        for relu, with_res in ((True, False), (True, True), (False, False)):
+            x = torch.randn(n, c, h, h, device="cuda").contiguous(memory_format=torch.channels_last).requires_grad_(True)
+            res = torch.randn(n, c, h, h, device="cuda").contiguous(memory_format=torch.channels_last).requires_grad_(True) if with_res else None
+            bn = torch.nn.BatchNorm2d(c).cuda().train()
+            with torch.no_grad():
+                bn.weight.uniform_(0.5, 1.5); bn.bias.normal_()
+            ref = torch.nn.BatchNorm2d(c).cuda().train()
+            ref.load_state_dict(bn.state_dict())
+            xr = x.detach().clone().requires_grad_(True)
+            rr = res.detach().clone().requires_grad_(True) if with_res else None
+            y = gnn.fused_batch_norm(x, bn, residual=res, relu=relu)
+            yr = ref(xr)
+            if with_res:
+                yr = yr + rr
+            if relu:
+                yr = torch.relu(yr)
+            torch.testing.assert_close(y, yr, rtol=1e-4, atol=1e-4)
+            torch.testing.assert_close(bn.running_mean, ref.running_mean, rtol=1e-4, atol=1e-5)
+            torch.testing.assert_close(bn.running_var, ref.running_var, rtol=1e-4, atol=1e-5)
+            g = torch.randn_like(y)
+            y.backward(g); yr.backward(g)
+            torch.testing.assert_close(x.grad, xr.grad, rtol=1e-3, atol=1e-4)
+            torch.testing.assert_close(bn.weight.grad, ref.weight.grad, rtol=1e-3, atol=1e-3)
+            torch.testing.assert_close(bn.bias.grad, ref.bias.grad, rtol=1e-3, atol=1e-3)
+            if with_res:
+                torch.testing.assert_close(res.grad, rr.grad, rtol=1e-4, atol=1e-5)
+
+
+def test_fused_resnet50_matches_torchvision():
+    import copy
+    import torchvision
+    from garfield_b200.models.fused_resnet import fuse_resnet_blocks
+    cuda_lib()
+    torch.manual_seed(0)
+    ref = torchvision.models.resnet50(num_classes=10).cuda().to(memory_format=torch.channels_last).train()
+    ours = copy.deepcopy(ref)
+    assert fuse_resnet_blocks(ours) == 16
+    x = torch.randn(25, 3, 32, 32, device="cuda").contiguous(memory_format=torch.channels_last)
+    t = torch.randint(0, 10, (25,), device="cuda")
+    la = torch.nn.functional.cross_entropy(ours(x), t)
+    lb = torch.nn.functional.cross_entropy(ref(x), t)
+    la.backward(); lb.backward()
+    assert abs(la.item() - lb.item()) < 1e-3
+    worst = 0.0
+    for p, q in zip(ours.parameters(), ref.parameters()):
+        worst = max(worst, (p.grad - q.grad).abs().max().item() / (q.grad.abs().max().item() + 1e-6))
+    assert worst < 2e-2, worst
+    ours.eval(); ref.eval()
+    torch.testing.assert_close(ours(x), ref(x), rtol=1e-3, atol=1e-3)
