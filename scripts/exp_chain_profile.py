@@ -5,13 +5,18 @@ from torch.profiler import profile, ProfilerActivity
 
 torch.backends.cudnn.benchmark = True
 dev = torch.device("cuda")
+import sys
+sys.path.insert(0, ".")
 m = torchvision.models.resnet50(num_classes=10).to(dev).to(memory_format=torch.channels_last)
+if "--fused" in sys.argv:
+    from garfield_b200.models.fused_resnet import fuse_resnet_blocks
+    print("patched blocks:", fuse_resnet_blocks(m))
 x = torch.randn(25, 3, 32, 32, device=dev).contiguous(memory_format=torch.channels_last)
 y = torch.randint(0, 10, (25,), device=dev)
-for p in m.parameters():
-    p.grad = torch.zeros_like(p)
 lossf = torch.nn.CrossEntropyLoss()
 def run():
+    for p in m.parameters():
+        p.grad = None
     lossf(m(x), y).backward()
 s = torch.cuda.Stream(); s.wait_stream(torch.cuda.current_stream())
 with torch.cuda.stream(s):

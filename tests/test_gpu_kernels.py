@@ -487,18 +487,53 @@ def test_fused_resnet50_matches_torchvision():
     from garfield_b200.models.fused_resnet import fuse_resnet_blocks
     cuda_lib()
     torch.manual_seed(0)
+    # full-precision, deterministic convolutions: the only difference left between the two models is the
+    # BatchNorm/ReLU/add implementation (with TF32 convolutions a 50-layer net at batch 25 amplifies the
+    # convolution rounding noise into O(1) relative gradient differences between ANY two runs)
+    tf32, det = torch.backends.cudnn.allow_tf32, torch.backends.cudnn.deterministic
+    torch.backends.cudnn.allow_tf32, torch.backends.cudnn.deterministic = False, True
+    try:
+        _compare_fused_resnet(torchvision, fuse_resnet_blocks, copy)
+    finally:
+        torch.backends.cudnn.allow_tf32, torch.backends.cudnn.deterministic = tf32, det
+
+
+def _compare_fused_resnet(torchvision, fuse_resnet_blocks, copy):
+    import types
+    from garfield_b200.models.fused_resnet import _bottleneck_forward
     ref = torchvision.models.resnet50(num_classes=10).cuda().to(memory_format=torch.channels_last).train()
     ours = copy.deepcopy(ref)
     assert fuse_resnet_blocks(ours) == 16
     x = torch.randn(25, 3, 32, 32, device="cuda").contiguous(memory_format=torch.channels_last)
     t = torch.randint(0, 10, (25,), device="cuda")
-    la = torch.nn.functional.cross_entropy(ours(x), t)
-    lb = torch.nn.functional.cross_entropy(ref(x), t)
-    la.backward(); lb.backward()
-    assert abs(la.item() - lb.item()) < 1e-3
-    worst = 0.0
-    for p, q in zip(ours.parameters(), ref.parameters()):
-        worst = max(worst, (p.grad - q.grad).abs().max().item() / (q.grad.abs().max().item() + 1e-6))
-    assert worst < 2e-2, worst
+
+    def flat_grads(model, inp):
+        for p in model.parameters():
+            p.grad = None
+        loss = torch.nn.functional.cross_entropy(model(inp), t)
+        loss.backward()
+        return loss.item(), torch.cat([p.grad.reshape(-1) for p in model.parameters()])
+
+    loss_ref, g_ref = flat_grads(ref, x)
+    loss_ours, g_ours = flat_grads(ours, x)
+    # a 50-layer BatchNorm net at batch 25 is ill-conditioned at initialisation: measure how much the REFERENCE's
+    # own gradient moves under a 1e-6 relative input perturbation and require the fused model to be that close
+    _, g_pert = flat_grads(copy.deepcopy(ref), x * (1 + 1e-6))
+    noise = ((g_pert - g_ref).norm() / g_ref.norm()).item()
+    err = ((g_ours - g_ref).norm() / g_ref.norm()).item()
+    assert abs(loss_ours - loss_ref) < 1e-3
+    assert err < 3 * noise + 1e-4, (err, noise)
+    assert torch.nn.functional.cosine_similarity(g_ours, g_ref, dim=0).item() > 0.999
+    # one block in isolation is well conditioned: tight agreement
+    blk = copy.deepcopy(ref.layer2[1])
+    fused = copy.deepcopy(blk)
+    fused.forward = types.MethodType(_bottleneck_forward, fused)
+    xb = torch.randn(25, 512, 4, 4, device="cuda").contiguous(memory_format=torch.channels_last)
+    outs = []
+    for b in (blk, fused):
+        xi = xb.clone().requires_grad_(True)
+        b(xi).square().mean().backward()
+        outs.append(torch.cat([p.grad.reshape(-1) for p in b.parameters()] + [xi.grad.reshape(-1)]))
+    torch.testing.assert_close(outs[1], outs[0], rtol=1e-4, atol=1e-7)
     ours.eval(); ref.eval()
     torch.testing.assert_close(ours(x), ref(x), rtol=1e-3, atol=1e-3)
