@@ -29,7 +29,15 @@ datasets_list = ["mnist", "cifar10", "pima"]
 MNIST, CIFAR10, PIMA = 0, 1, 2
 
 _SHAPES = {"mnist": ((1, 28, 28), 10, 60000, 10000), "cifar10": ((3, 32, 32), 10, 50000, 10000)}
-_PIMA_CSV = pathlib.Path(__file__).with_name("pima_diabetes.csv")
+# The Pima table is public data (UCI / Kaggle) that this repository does not redistribute: it is read from the
+# first location that has it — next to this module, ~/data, $GARFIELD_PIMA_CSV, or a mounted reference checkout.
+_PIMA_CANDIDATES = (
+    pathlib.Path(__file__).with_name("pima_diabetes.csv"),
+    pathlib.Path.home() / "data" / "pima_diabetes.csv",
+    pathlib.Path(os.environ.get("GARFIELD_PIMA_CSV", "/nonexistent")),
+    pathlib.Path("/root/reference/pytorch_impl/libs/garfieldpp/pima_diabetes.csv"),
+    pathlib.Path(__file__).resolve().parents[2] / "baseline" / "_ref" / "pytorch_impl" / "libs" / "garfieldpp" / "pima_diabetes.csv",
+)
 
 
 class SyntheticDataset(torch.utils.data.Dataset):
@@ -54,9 +62,9 @@ class SyntheticDataset(torch.utils.data.Dataset):
 class PimaDiabetesDataset(torch.utils.data.Dataset):
     """Pima Indians diabetes table: 8 z-scored features → binary label (600 train / 168 test).
 
-    Reads `pima_diabetes.csv` next to this file (same format as the reference's bundled CSV,
-    garfieldpp/datasets.py:52-94) when present; otherwise a synthetic stand-in with the same
-    shape is generated from a fixed logistic model.
+    Reads `pima_diabetes.csv` (same format as the reference's bundled CSV, garfieldpp/datasets.py:52-94)
+    from the first of `_PIMA_CANDIDATES` that exists; otherwise a synthetic stand-in with the same shape
+    is generated from a fixed logistic model.
     """
     TRAIN_SPLIT = 600
     TEST_SPLIT = 168
@@ -71,9 +79,10 @@ class PimaDiabetesDataset(torch.utils.data.Dataset):
 
     @staticmethod
     def _load():
-        if _PIMA_CSV.exists():
-            import pandas as pd
-            return torch.tensor(pd.read_csv(_PIMA_CSV).values, dtype=torch.float64)
+        for candidate in _PIMA_CANDIDATES:
+            if candidate.is_file():
+                import pandas as pd
+                return torch.tensor(pd.read_csv(candidate).values, dtype=torch.float64)
         gen = torch.Generator().manual_seed(768)
         feats = torch.randn(768, 8, generator=gen, dtype=torch.float64) * 3 + 5
         weights = torch.tensor([0.4, 1.1, -0.2, 0.1, 0.3, 0.9, 0.5, 0.6], dtype=torch.float64)
