@@ -58,6 +58,14 @@ __global__ void __launch_bounds__(kBnThreads) bn_nhwc_fwd_kernel(int rows, int C
     int const quad = lane % QUADS, rlane = lane / QUADS + (32 / QUADS) * warp;
     int const c0 = (blockIdx.x * QUADS + quad) * 4;
     bool const live = c0 < C;                                            // C is a multiple of 4
+    {   // blockIdx.y = statistics group: a contiguous block of `rows` rows with its own mean/variance/running buffers
+        long long const goff = static_cast<long long>(blockIdx.y) * rows * C;
+        int const soff = blockIdx.y * C;
+        x += goff; y += goff;
+        if (residual != nullptr) residual += goff;
+        save_mean += soff; save_invstd += soff;
+        if (running_mean != nullptr) { running_mean += soff; running_var += soff; }
+    }
     // one-pass statistics around a per-channel pivot K (the first row): Σ(x−K) and Σ(x−K)² do not suffer the
     // cancellation of E[x²] − E[x]² because K is a sample of the same distribution
     float4 const K = live ? ld4(x + c0) : make_float4(0.f, 0.f, 0.f, 0.f);
@@ -126,6 +134,14 @@ __global__ void __launch_bounds__(kBnThreads) bn_nhwc_bwd_kernel(int rows, int C
     int const quad = lane % QUADS, rlane = lane / QUADS + (32 / QUADS) * warp;
     int const c0 = (blockIdx.x * QUADS + quad) * 4;
     bool const live = c0 < C;
+    {
+        long long const goff = static_cast<long long>(blockIdx.y) * rows * C;
+        int const soff = blockIdx.y * C;
+        x += goff; dy += goff; dx += goff;
+        if (y != nullptr) y += goff;
+        if (d_residual != nullptr) d_residual += goff;
+        save_mean += soff; save_invstd += soff; dgamma += soff; dbeta += soff;
+    }
     float4 mean = make_float4(0.f, 0.f, 0.f, 0.f), invstd = mean, g = mean;
     if (live) { mean = ld4(save_mean + c0); invstd = ld4(save_invstd + c0); g = ld4(gamma + c0); }
     float4 s1 = make_float4(0.f, 0.f, 0.f, 0.f), s2 = s1;
@@ -166,10 +182,10 @@ __global__ void __launch_bounds__(kBnThreads) bn_nhwc_bwd_kernel(int rows, int C
 }
 
 // Channel quads per CTA: as many as keep >= 64 CTAs in flight (128-byte rows for wide layers, more CTAs for narrow ones).
-inline int pick_quads(int C) {
+inline int pick_quads(int C, int groups = 1) {
     int const quads_total = C / 4;
     for (int q = 8; q > 1; q >>= 1)
-        if (quads_total / q >= 64) return q;
+        if (quads_total / q * groups >= 64) return q;
     return 1;
 }
 
@@ -180,13 +196,15 @@ using namespace gb;
 
 extern "C" {
 
-// x, y, residual: [rows, C] channels-last activations (C % 4 == 0, 16-byte aligned). relu / residual optional.
-GB_API int gb_bn_nhwc_forward(float const* x, float const* residual, float const* gamma, float const* beta, float* y, float* save_mean,
-                              float* save_invstd, float* running_mean, float* running_var, int rows, int C, float eps, float momentum, int relu,
-                              void* stream) {
-    if (rows < 1 || C < 4 || C % 4) return cuda_fail("bn_nhwc: need rows >= 1 and C a positive multiple of 4");
-    int const q = pick_quads(C);
-    int const grid = (C / 4 + q - 1) / q;
+// x, y, residual: [groups, rows, C] channels-last activations (C % 4 == 0, 16-byte aligned); every group of `rows`
+// rows is normalised with its own statistics (save_mean / save_invstd / running_*: [groups, C]; gamma / beta: [C],
+// shared). groups = 1 is plain BatchNorm2d; groups = G is G co-located workers' batches in one launch.
+GB_API int gb_bn_nhwc_forward_grouped(float const* x, float const* residual, float const* gamma, float const* beta, float* y, float* save_mean,
+                                      float* save_invstd, float* running_mean, float* running_var, int groups, int rows, int C, float eps,
+                                      float momentum, int relu, void* stream) {
+    if (groups < 1 || groups > 65535 || rows < 1 || C < 4 || C % 4) return cuda_fail("bn_nhwc: need 1 <= groups <= 65535, rows >= 1 and C a positive multiple of 4");
+    int const q = pick_quads(C, groups);
+    dim3 const grid((C / 4 + q - 1) / q, groups);
     cudaStream_t const st = static_cast<cudaStream_t>(stream);
 #define GB_BN_FWD(Q) bn_nhwc_fwd_kernel<Q><<<grid, kBnThreads, 0, st>>>(rows, C, x, residual, gamma, beta, eps, momentum, relu, y, save_mean, save_invstd, running_mean, running_var)
     if (q == 8) GB_BN_FWD(8); else if (q == 4) GB_BN_FWD(4); else if (q == 2) GB_BN_FWD(2); else GB_BN_FWD(1);
@@ -194,17 +212,31 @@ GB_API int gb_bn_nhwc_forward(float const* x, float const* residual, float const
     return cuda_check(cudaGetLastError(), "bn_nhwc forward");
 }
 
-GB_API int gb_bn_nhwc_backward(float const* x, float const* y, float const* dy, float const* gamma, float const* save_mean,
-                               float const* save_invstd, float* dx, float* d_residual, float* dgamma, float* dbeta, int rows, int C, int relu,
-                               void* stream) {
-    if (rows < 1 || C < 4 || C % 4) return cuda_fail("bn_nhwc: need rows >= 1 and C a positive multiple of 4");
-    int const q = pick_quads(C);
-    int const grid = (C / 4 + q - 1) / q;
+GB_API int gb_bn_nhwc_forward(float const* x, float const* residual, float const* gamma, float const* beta, float* y, float* save_mean,
+                              float* save_invstd, float* running_mean, float* running_var, int rows, int C, float eps, float momentum, int relu,
+                              void* stream) {
+    return gb_bn_nhwc_forward_grouped(x, residual, gamma, beta, y, save_mean, save_invstd, running_mean, running_var, 1, rows, C, eps, momentum,
+                                      relu, stream);
+}
+
+// dgamma / dbeta: [groups, C] (per-group parameter gradients — one row per co-located worker).
+GB_API int gb_bn_nhwc_backward_grouped(float const* x, float const* y, float const* dy, float const* gamma, float const* save_mean,
+                                       float const* save_invstd, float* dx, float* d_residual, float* dgamma, float* dbeta, int groups, int rows,
+                                       int C, int relu, void* stream) {
+    if (groups < 1 || groups > 65535 || rows < 1 || C < 4 || C % 4) return cuda_fail("bn_nhwc: need 1 <= groups <= 65535, rows >= 1 and C a positive multiple of 4");
+    int const q = pick_quads(C, groups);
+    dim3 const grid((C / 4 + q - 1) / q, groups);
     cudaStream_t const st = static_cast<cudaStream_t>(stream);
 #define GB_BN_BWD(Q) bn_nhwc_bwd_kernel<Q><<<grid, kBnThreads, 0, st>>>(rows, C, x, y, dy, gamma, save_mean, save_invstd, relu, dx, d_residual, dgamma, dbeta)
     if (q == 8) GB_BN_BWD(8); else if (q == 4) GB_BN_BWD(4); else if (q == 2) GB_BN_BWD(2); else GB_BN_BWD(1);
 #undef GB_BN_BWD
     return cuda_check(cudaGetLastError(), "bn_nhwc backward");
+}
+
+GB_API int gb_bn_nhwc_backward(float const* x, float const* y, float const* dy, float const* gamma, float const* save_mean,
+                               float const* save_invstd, float* dx, float* d_residual, float* dgamma, float* dbeta, int rows, int C, int relu,
+                               void* stream) {
+    return gb_bn_nhwc_backward_grouped(x, y, dy, gamma, save_mean, save_invstd, dx, d_residual, dgamma, dbeta, 1, rows, C, relu, stream);
 }
 
 }  // extern "C"

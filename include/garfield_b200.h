@@ -174,6 +174,14 @@ GB_API int gb_bn_nhwc_forward(float const* x, float const* residual, float const
 GB_API int gb_bn_nhwc_backward(float const* x, float const* y, float const* dy, float const* gamma, float const* save_mean,
                                float const* save_invstd, float* dx, float* d_residual, float* dgamma, float* dbeta, int rows, int C, int relu,
                                void* stream);
+/* The same kernels over `groups` consecutive blocks of `rows` rows, each normalised with its own statistics (save_* and
+ * running_*: [groups, C]; gamma/beta shared; dgamma/dbeta: [groups, C]) — the co-located workers of one GPU in one launch. */
+GB_API int gb_bn_nhwc_forward_grouped(float const* x, float const* residual, float const* gamma, float const* beta, float* y, float* save_mean,
+                                      float* save_invstd, float* running_mean, float* running_var, int groups, int rows, int C, float eps,
+                                      float momentum, int relu, void* stream);
+GB_API int gb_bn_nhwc_backward_grouped(float const* x, float const* y, float const* dy, float const* gamma, float const* save_mean,
+                                       float const* save_invstd, float* dx, float* d_residual, float* dgamma, float* dbeta, int groups, int rows,
+                                       int C, int relu, void* stream);
 GB_API int gb_global_avgpool_forward(float const* x, float* y, int64_t planes, int hw, void* stream);
 GB_API int gb_global_avgpool_backward(float const* dy, float* dx, int64_t planes, int hw, void* stream);
 /* Inverted dropout with a regenerable Philox mask (apply to dy with the same seed for the backward pass). */
