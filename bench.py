@@ -47,6 +47,8 @@ def parse_args(argv=None):
     ap.add_argument("--gar", default="krum", help="primary rule for `value` (krum | median | bulyan | ...)")
     ap.add_argument("--also", default="median,bulyan", help="other rules reported under per_gar ('' to skip)")
     ap.add_argument("--no-graphs", action="store_true")
+    ap.add_argument("--fuse-workers", default="auto", choices=["auto", "on", "off"],
+                    help="one batched forward/backward for the workers hosted by a GPU (auto: when a rank hosts >= 2 workers)")
     ap.add_argument("--sync", default="nccl", choices=["nccl", "flags"], help="inter-rank synchronisation (N > 1)")
     return ap.parse_args(argv)
 
@@ -160,7 +162,8 @@ def run_gar(gar, args, rank, world, local, full):
     from garfield_b200.ops import _lib
     from garfield_b200.parallel.engine import SSMWEngine
     torch.backends.cudnn.benchmark = True
-    engine = SSMWEngine(MODEL, DATASET, LOSS, N_WORKERS, F_BYZ, gar, BATCH, "sgd", OPT_ARGS, use_graphs=not args.no_graphs, sync=args.sync)
+    engine = SSMWEngine(MODEL, DATASET, LOSS, N_WORKERS, F_BYZ, gar, BATCH, "sgd", OPT_ARGS, use_graphs=not args.no_graphs, sync=args.sync,
+                        fuse_workers={"auto": None, "on": True, "off": False}[args.fuse_workers])
     it = 0
     for _ in range(max(args.warmup, 3)):
         engine.step(it).item()
@@ -180,6 +183,7 @@ def run_gar(gar, args, rank, world, local, full):
         "e2e_ms_per_step": ms_e2e / steps, "e2e_images_per_s": images / (ms_e2e / 1e3),
         "h2d_bytes_per_step": None,
         "d2h_bytes_per_step": d2h // steps, "gpu_launches": launches, "clocks": clocks.summary(), "d": engine.d,
+        "worker_fusion": engine.fused is not None,
     }
     h2d = torch.tensor([float(engine.h2d_bytes)], device=engine.device)
     if world > 1:
@@ -217,6 +221,8 @@ def run_ours(args):
                        else "ssmw n=8 f=1, all roles on 1 gpu",
                        "gar": args.gar, "optimizer": "sgd lr=0.2 momentum=0.9 wd=5e-4 (fused in the GAR epilogue)",
                        "l2": "per-step working set 8 x 94 MB gradient rows = 753 MB > 126 MB L2 (no flush needed)",
+                       "worker_fusion": ("one batched forward/backward per GPU for its %d workers (per-worker BatchNorm statistics, weight "
+                                         "gradients and losses)" % (N_WORKERS // world)) if primary["worker_fusion"] else "off (one chain per worker)",
                        "d": primary["d"]},
             "per_gar": per_gar, "per_gar_e2e": per_gar_e2e,
             "e2e": {"value": round(primary["e2e_images_per_s"], 2), "unit": "images/s",

@@ -355,44 +355,62 @@ def binary_cross_entropy(prob, target):
 # ------------------------------------------------------------ fused channels-last BatchNorm (+ add) (+ ReLU) ---
 
 class _FusedBnFn(torch.autograd.Function):
+    """groups > 1: the batch holds `groups` equal statistics groups (co-located workers' batches) — per-group
+    mean / variance / running buffers ([groups, C]) and per-group parameter gradients, which go to `sink(dgamma, dbeta)`
+    (both [groups, C]) when a sink is given; autograd always sees their sum over the groups."""
+
     @staticmethod
-    def forward(ctx, x, gamma, beta, residual, running_mean, running_var, eps, momentum, relu):
+    def forward(ctx, x, gamma, beta, residual, running_mean, running_var, eps, momentum, relu, groups=1, sink=None):
         n, c, h, w = x.shape
-        rows = n * h * w
+        rows = n // groups * h * w
         y = torch.empty_like(x)                      # keeps the channels-last strides of x
-        mean, invstd = torch.empty(c, device=x.device), torch.empty(c, device=x.device)
+        mean, invstd = torch.empty(groups, c, device=x.device), torch.empty(groups, c, device=x.device)
         with torch.cuda.device(x.device):
-            _lib.check(_lib.require().gb_bn_nhwc_forward(_ptr(x), _ptr(residual), _ptr(gamma), _ptr(beta), _ptr(y), _ptr(mean), _ptr(invstd),
-                                                         _ptr(running_mean), _ptr(running_var), rows, c, float(eps), float(momentum),
-                                                         int(relu), _lib.stream_ptr(x.device)))
+            _lib.check(_lib.require().gb_bn_nhwc_forward_grouped(_ptr(x), _ptr(residual), _ptr(gamma), _ptr(beta), _ptr(y), _ptr(mean), _ptr(invstd),
+                                                                 _ptr(running_mean), _ptr(running_var), groups, rows, c, float(eps), float(momentum),
+                                                                 int(relu), _lib.stream_ptr(x.device)))
         _lib.count()
         ctx.save_for_backward(x, gamma, mean, invstd, y if relu else None)
-        ctx.cfg = (rows, c, relu, residual is not None)
+        ctx.cfg = (groups, rows, c, relu, residual is not None, sink)
         return y
 
     @staticmethod
     def backward(ctx, dy):
         x, gamma, mean, invstd, y = ctx.saved_tensors
-        rows, c, relu, has_res = ctx.cfg
+        groups, rows, c, relu, has_res, sink = ctx.cfg
         if not dy.is_contiguous(memory_format=torch.channels_last):
             dy = dy.contiguous(memory_format=torch.channels_last)
         dx = torch.empty_like(x)
         dres = torch.empty_like(x) if has_res else None
-        dgamma, dbeta = torch.empty(c, device=x.device), torch.empty(c, device=x.device)
+        dgamma, dbeta = torch.empty(groups, c, device=x.device), torch.empty(groups, c, device=x.device)
         with torch.cuda.device(x.device):
-            _lib.check(_lib.require().gb_bn_nhwc_backward(_ptr(x), _ptr(y), _ptr(dy), _ptr(gamma), _ptr(mean), _ptr(invstd), _ptr(dx), _ptr(dres),
-                                                          _ptr(dgamma), _ptr(dbeta), rows, c, int(relu), _lib.stream_ptr(x.device)))
+            _lib.check(_lib.require().gb_bn_nhwc_backward_grouped(_ptr(x), _ptr(y), _ptr(dy), _ptr(gamma), _ptr(mean), _ptr(invstd), _ptr(dx),
+                                                                  _ptr(dres), _ptr(dgamma), _ptr(dbeta), groups, rows, c, int(relu),
+                                                                  _lib.stream_ptr(x.device)))
         _lib.count()
-        return dx, dgamma, dbeta, dres, None, None, None, None, None
+        if sink is not None:
+            sink(dgamma, dbeta)
+            return dx, None, None, dres, None, None, None, None, None, None, None
+        if groups == 1:
+            return dx, dgamma[0], dbeta[0], dres, None, None, None, None, None, None, None
+        return dx, dgamma.sum(0), dbeta.sum(0), dres, None, None, None, None, None, None, None
+
+
+def fused_bn_usable(x, bn, residual=None):
+    """True when `fused_batch_norm` can take the hand-written kernel for this call."""
+    return (bn.training and x.is_cuda and x.dtype == torch.float32 and x.dim() == 4 and bn.affine and bn.momentum is not None
+            and x.shape[1] % 4 == 0 and x.is_contiguous(memory_format=torch.channels_last) and _lib.available()
+            and (residual is None or (residual.shape == x.shape and residual.is_contiguous(memory_format=torch.channels_last))))
 
 
 def fused_batch_norm(x, bn, residual=None, relu=True):
     """`[relu](bn(x) [+ residual])` for a `BatchNorm2d` module `bn` in ONE kernel (training mode,
-    channels-last fp32 CUDA activations); anything else takes the equivalent torch ops."""
-    usable = (bn.training and x.is_cuda and x.dtype == torch.float32 and x.dim() == 4 and bn.affine and bn.momentum is not None
-              and x.shape[1] % 4 == 0 and x.is_contiguous(memory_format=torch.channels_last) and _lib.available()
-              and (residual is None or (residual.shape == x.shape and residual.is_contiguous(memory_format=torch.channels_last))))
-    if not usable:
+    channels-last fp32 CUDA activations); anything else takes the equivalent torch ops. A layer owned by a worker
+    group (`parallel.grouped`) is normalised per worker."""
+    group = getattr(bn, "_gb_group", None)
+    if group is not None:
+        return group(bn, x, residual, relu)
+    if not fused_bn_usable(x, bn, residual):
         y = torch.nn.functional.batch_norm(x, bn.running_mean, bn.running_var, bn.weight, bn.bias, bn.training or bn.running_mean is None,
                                            bn.momentum if bn.momentum is not None else 0.1, bn.eps)
         if residual is not None:
@@ -400,3 +418,50 @@ def fused_batch_norm(x, bn, residual=None, relu=True):
         return torch.relu(y) if relu else y
     return _FusedBnFn.apply(x, bn.weight, bn.bias, residual, bn.running_mean if bn.track_running_stats else None,
                             bn.running_var if bn.track_running_stats else None, bn.eps, bn.momentum, relu)
+
+
+def grouped_batch_norm(x, weight, bias, running_mean, running_var, groups, eps=1e-5, momentum=0.1, residual=None, relu=False, sink=None):
+    """Training-mode BatchNorm over `groups` equal slices of the batch, each with its own statistics
+    (running_mean / running_var: [groups, C] or None). ONE kernel on channels-last CUDA activations; elsewhere the
+    same arithmetic in torch. `sink(dgamma, dbeta)` receives the per-group parameter gradients ([groups, C])."""
+    n, c = x.shape[0], x.shape[1]
+    if n % groups:
+        raise ValueError("batch %d is not divisible into %d groups" % (n, groups))
+    if (x.is_cuda and x.dtype == torch.float32 and x.dim() == 4 and c % 4 == 0 and x.is_contiguous(memory_format=torch.channels_last)
+            and _lib.available() and (residual is None or (residual.shape == x.shape and residual.is_contiguous(memory_format=torch.channels_last)))):
+        return _FusedBnFn.apply(x, weight, bias, residual, running_mean, running_var, eps, momentum, relu, groups, sink)
+    xg = x.reshape(groups, n // groups, *x.shape[1:])
+    dims = [1] + list(range(3, xg.dim()))
+    mean = xg.mean(dims, keepdim=True)
+    var = xg.var(dims, unbiased=False, keepdim=True)
+    if running_mean is not None:
+        with torch.no_grad():
+            count = xg.numel() // (groups * c)
+            running_mean.mul_(1 - momentum).add_(momentum * mean.reshape(groups, c))
+            running_var.mul_(1 - momentum).add_(momentum * var.reshape(groups, c) * (count / max(count - 1, 1)))
+    shape = [groups, 1, c] + [1] * (xg.dim() - 3)
+    gam, bet = _per_group(weight, bias, groups, sink)
+    y = ((xg - mean) * torch.rsqrt(var + eps) * gam.reshape(shape) + bet.reshape(shape)).reshape(x.shape)
+    if residual is not None:
+        y = y + residual
+    return torch.relu(y) if relu else y
+
+
+class _PerGroupFn(torch.autograd.Function):
+    """Replicate (weight, bias) for every group; the per-group gradients go to the sink instead of being summed."""
+
+    @staticmethod
+    def forward(ctx, weight, bias, groups, sink):
+        ctx.sink = sink
+        return weight.unsqueeze(0).repeat(groups, *[1] * weight.dim()), bias.unsqueeze(0).repeat(groups, *[1] * bias.dim())
+
+    @staticmethod
+    def backward(ctx, dw, db):
+        ctx.sink(dw, db)
+        return None, None, None, None
+
+
+def _per_group(weight, bias, groups, sink):
+    if sink is None:
+        return weight.unsqueeze(0).expand(groups, *weight.shape), bias.unsqueeze(0).expand(groups, *bias.shape)
+    return _PerGroupFn.apply(weight, bias, groups, sink)

@@ -31,6 +31,7 @@ from ..garfieldpp import tools
 from ..garfieldpp.datasets import DatasetManager
 from ..ops import _lib, attacks, gar as gar_ops
 from ..ops.optim import FlatOptimizer
+from .grouped import GroupedWorkers
 
 __all__ = ["SSMWEngine"]
 
@@ -156,7 +157,7 @@ class SSMWEngine:
     def __init__(self, model, dataset, loss, num_workers, f, gar, batch, optimizer="sgd", opt_args=None, byzantine=None,
                  device=None, group=None, use_graphs=True, train_set=None, seed=1234, gar_kwargs=None, sharded=None,
                  channels_last=True, sync="nccl", flag_timeout=5.0, gather_grads=True, fast_bn=True,
-                 split_backward=None):
+                 split_backward=None, fuse_workers=None):
         self.rank = dist.get_rank(group) if dist.is_initialized() else 0
         self.world = dist.get_world_size(group) if dist.is_initialized() else 1
         self.group = group
@@ -220,6 +221,14 @@ class SSMWEngine:
                                              attack=self.byzantine.get(wid), channels_last=self.channels_last, gather=gather_grads,
                                              split_backward=split_backward))
 
+        # worker fusion: the co-located workers share ONE forward/backward pass (parallel/grouped.py) when every
+        # layer of the model is covered; otherwise each worker keeps its own chain and stream
+        self.fused = None
+        if fuse_workers is None:
+            fuse_workers = len(self.workers) >= 2 and gather_grads
+        if fuse_workers and self.workers and GroupedWorkers.unsupported_reason(module, loss_fn) is None:
+            self._fuse_workers(module, loss_fn)
+
         # server state (whole vector on rank 0, or this rank's coordinate slice when sharded)
         if self.sharded:
             per = (self.pitch // 64 + self.world - 1) // self.world * 64   # slice length, multiple of 64 floats
@@ -255,6 +264,26 @@ class SSMWEngine:
         self.use_graphs = use_graphs
         self.steps_done = 0
         self.h2d_bytes = 0
+
+    def _fuse_workers(self, module, loss_fn):
+        """Point every local worker's inputs, loss and BatchNorm running statistics at slices of the group's
+        buffers, so loading batches, evaluation and checkpoints work on the worker objects as before."""
+        G = len(self.workers)
+        replica = FlatModel(copy.deepcopy(module), self.device, flat=self.flat, channels_last=self.channels_last)
+        self.fused = GroupedWorkers(replica, [w.row for w in self.workers], loss_fn)
+        first = self.workers[0]
+        data = torch.zeros((G * first.data.shape[0],) + tuple(first.data.shape[1:]), device=self.device)
+        if self.channels_last and data.dim() == 4:
+            data = data.contiguous(memory_format=torch.channels_last)
+        target = torch.zeros((G * first.target.shape[0],) + tuple(first.target.shape[1:]), dtype=first.target.dtype, device=self.device)
+        self._group_data, self._group_target = data, target
+        self._group_losses = torch.zeros(G, device=self.device)
+        b, t = first.data.shape[0], first.target.shape[0]
+        for g, w in enumerate(self.workers):
+            w.data, w.target, w.loss = data[g * b:(g + 1) * b], target[g * t:(g + 1) * t], self._group_losses[g]
+            modules = dict(w.replica.module.named_modules())
+            for name, (mean, var) in self.fused.running_tables.items():
+                modules[name]._buffers["running_mean"], modules[name]._buffers["running_var"] = mean[g], var[g]
 
     # ------------------------------------------------------------------------------------------
     @staticmethod
@@ -330,6 +359,9 @@ class SSMWEngine:
         return losses
 
     def _run_workers(self):
+        if self.fused is not None:
+            self.fused.forward_backward(self._group_data, self._group_target, self._group_losses)
+            return
         main = torch.cuda.current_stream(self.device)
         for w in self.workers:
             w.stream.wait_stream(main)
@@ -347,8 +379,10 @@ class SSMWEngine:
         torch.cuda.current_stream(self.device).wait_stream(side)
         torch.cuda.synchronize(self.device)
         graph = torch.cuda.CUDAGraph()
+        before = _lib.launches[0]
         with torch.cuda.graph(graph):
             self._run_workers()
+        self._graph_launches = _lib.launches[0] - before   # this library's kernels inside the graph (counted per replay)
         self._graph = graph
 
     def compute_gradients(self):
@@ -358,6 +392,7 @@ class SSMWEngine:
             if self._graph is None:
                 self._capture()
             self._graph.replay()
+            _lib.count(self._graph_launches)
         else:
             self._run_workers()
         for w in self.workers:

@@ -1,0 +1,294 @@
+"""Worker fusion: ONE forward/backward pass computes the gradients of all G workers hosted by a GPU.
+
+The reference runs every worker as its own process with its own pickled model copy (garfieldpp/worker.py:77-96);
+the first device engine here ran one CUDA-graphed chain per worker on its own stream. But co-located workers of one
+step all evaluate the SAME parameters, so everything except the weight gradients can be batched:
+
+* forward and data gradients run once over the concatenated batch [G·B, …] (same weights → one convolution / GEMM
+  instead of G small ones, weights read once);
+* BatchNorm keeps per-worker statistics: `ops.nn.grouped_batch_norm` normalises each of the G slices with its own
+  mean/variance/running buffers in one launch (thread-block clusters + DSMEM reduction, csrc/cuda/bn_nhwc.cu);
+* weight gradients stay per worker (that is what the aggregation rule consumes): 1×1 convolutions and Linear
+  layers become ONE batched GEMM [G, out, B·HW] × [G, B·HW, in]; k×k convolutions run G weight-gradient kernels on
+  side streams, off the data-gradient chain;
+* the loss is the sum of the G per-worker mean losses, so every sample's logit gradient is exactly its own
+  worker's; each worker's gradient lands in its own row of the gradient matrix through ONE multi-tensor scatter.
+
+The result is the same G gradients as G separate replicas (tests/test_grouped.py), not a large-batch gradient.
+"""
+
+from __future__ import annotations
+
+import ctypes
+import types
+
+import torch
+import torch.nn.functional as F
+
+from ..ops import _lib
+from ..ops.nn import grouped_batch_norm
+
+__all__ = ["GroupedWorkers"]
+
+_aten = torch.ops.aten
+
+
+def _same_layout(a, b):
+    """Same shape and same element order in memory (strides of size-1 dimensions are irrelevant)."""
+    if a.shape != b.shape:
+        return False
+    return all(sa == sb for n, sa, sb in zip(a.shape, a.stride(), b.stride()) if n > 1)
+
+
+class _GradSink:
+    """Per-group gradients of every parameter, scattered into the G gradient rows after the backward pass."""
+
+    def __init__(self, params, slices, rows, view_of):
+        self.params, self.slices, self.rows, self.view_of = params, slices, rows, view_of
+        self.groups = len(rows)
+        self.pending = {}
+        base = rows[0]
+        self.row_offsets = [(r.data_ptr() - base.data_ptr()) // 4 for r in rows]
+        self.contiguous_rows = base.is_cuda and all(o >= 0 for o in self.row_offsets)
+
+    def put(self, index, grads):
+        """grads: a [G, *shape] tensor or a list of G tensors of the parameter's shape."""
+        self.pending[index] = grads
+
+    def flush(self):
+        srcs, offs, sizes = [], [], []
+        for index, (p, (off, n, shape)) in enumerate(zip(self.params, self.slices)):
+            grads = self.pending.get(index)
+            for g in range(self.groups):
+                row = self.rows[g]
+                if grads is None:
+                    row[off:off + n].zero_()
+                    continue
+                t = grads[g]
+                if t.shape != p.shape:
+                    t = t.reshape(p.shape)
+                if self.contiguous_rows and t.is_cuda and t.dtype == torch.float32 and _same_layout(t, p):
+                    srcs.append(t.data_ptr()); offs.append(self.row_offsets[g] + off); sizes.append(n)
+                else:
+                    self.view_of(row, off, n, shape).copy_(t)
+        if srcs:
+            k = len(srcs)
+            base = self.rows[0]
+            _lib.check(_lib.require().gb_multi_copy((ctypes.c_void_p * k)(*srcs), (ctypes.c_uint64 * k)(*offs), (ctypes.c_uint32 * k)(*sizes), k,
+                                                    base.data_ptr(), _lib.stream_ptr(base.device)))
+            _lib.count((k + 111) // 112)
+        self.pending = {}
+
+
+class _GroupedConv(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, w, b, owner, conv, widx, bidx):
+        ctx.save_for_backward(x, w)
+        ctx.cfg = (owner, conv, widx, bidx)
+        return F.conv2d(x, w, b, conv.stride, conv.padding, conv.dilation, conv.groups)
+
+    @staticmethod
+    def backward(ctx, gy):
+        x, w = ctx.saved_tensors
+        owner, conv, widx, bidx = ctx.cfg
+        G = owner.groups
+        B = x.shape[0] // G
+        stride, padding, dilation = list(conv.stride), list(conv.padding), list(conv.dilation)
+        pointwise = (conv.kernel_size == (1, 1) and conv.groups == 1 and conv.padding == (0, 0) and x.is_cuda
+                     and x.is_contiguous(memory_format=torch.channels_last))
+        if pointwise:
+            # per-worker weight gradients of a 1×1 convolution = one batched GEMM over the NHWC views
+            if not gy.is_contiguous(memory_format=torch.channels_last):
+                gy = gy.contiguous(memory_format=torch.channels_last)
+            xs = x if conv.stride == (1, 1) else x[:, :, ::conv.stride[0], ::conv.stride[1]].contiguous(memory_format=torch.channels_last)
+            xm = xs.permute(0, 2, 3, 1).reshape(G, -1, xs.shape[1])
+            gm = gy.permute(0, 2, 3, 1).reshape(G, -1, gy.shape[1])
+            with owner.tf32_matmul():
+                owner.sink.put(widx, torch.bmm(gm.transpose(1, 2), xm).unsqueeze(-1).unsqueeze(-1))
+        else:
+            sides = owner.side_streams
+            cur = torch.cuda.current_stream(x.device) if sides else None
+            if sides:
+                for s in sides:
+                    s.wait_stream(cur)
+                for s in sides:
+                    gy.record_stream(s); x.record_stream(s)
+            grads = []
+            for g in range(G):
+                xs, gs = x[g * B:(g + 1) * B], gy[g * B:(g + 1) * B]
+                if sides:
+                    with torch.cuda.stream(sides[g % len(sides)]):
+                        grads.append(_aten.convolution_backward(gs, xs, w, None, stride, padding, dilation, False, [0, 0], conv.groups,
+                                                                [False, True, False])[1])
+                else:
+                    grads.append(_aten.convolution_backward(gs, xs, w, None, stride, padding, dilation, False, [0, 0], conv.groups,
+                                                            [False, True, False])[1])
+            owner.sink.put(widx, grads)
+        if bidx is not None:
+            owner.sink.put(bidx, gy.reshape(G, B, *gy.shape[1:]).sum((1, 3, 4)))
+        gx = None
+        if ctx.needs_input_grad[0]:
+            gx = _aten.convolution_backward(gy, x, w, None, stride, padding, dilation, False, [0, 0], conv.groups, [True, False, False])[0]
+        return gx, None, None, None, None, None, None
+
+
+class _GroupedLinear(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, w, b, owner, widx, bidx):
+        ctx.save_for_backward(x, w)
+        ctx.cfg = (owner, widx, bidx)
+        return F.linear(x, w, b)
+
+    @staticmethod
+    def backward(ctx, gy):
+        x, w = ctx.saved_tensors
+        owner, widx, bidx = ctx.cfg
+        G = owner.groups
+        xm = x.reshape(G, -1, x.shape[-1])
+        gm = gy.reshape(G, -1, gy.shape[-1])
+        owner.sink.put(widx, torch.bmm(gm.transpose(1, 2), xm))
+        if bidx is not None:
+            owner.sink.put(bidx, gm.sum(1))
+        gx = gy @ w if ctx.needs_input_grad[0] else None
+        return gx, None, None, None, None, None
+
+
+class _Tf32:
+    def __init__(self, enable):
+        self.enable = enable
+
+    def __enter__(self):
+        self.prev = torch.backends.cuda.matmul.allow_tf32
+        if self.enable:
+            torch.backends.cuda.matmul.allow_tf32 = True
+
+    def __exit__(self, *exc):
+        torch.backends.cuda.matmul.allow_tf32 = self.prev
+
+
+class GroupedWorkers:
+    """Gradients of G co-located workers from one pass over `replica` (a FlatModel aliasing the shared parameters).
+
+    rows[g] receives worker g's flat gradient; `data`/`target` are the concatenated [G·B, …] inputs; `losses` ([G])
+    receives the per-worker mean losses. BatchNorm running statistics are kept per worker in `[G, C]` tables
+    (`running_tables[name]`), so every worker's replica can alias its own row."""
+
+    _BATCHNORM = (torch.nn.BatchNorm1d, torch.nn.BatchNorm2d)
+
+    def __init__(self, replica, rows, loss_fn, side_streams=4):
+        self.replica, self.module, self.rows = replica, replica.module, list(rows)
+        self.groups = len(self.rows)
+        self.loss_kind = self._loss_kind(loss_fn)
+        reason = self.unsupported_reason(self.module, loss_fn)
+        if reason:
+            raise ValueError("worker fusion does not cover this model: " + reason)
+        params = list(self.module.parameters())
+        index = {id(p): i for i, p in enumerate(params)}
+        self.sink = _GradSink(params, replica.slices, self.rows, replica._view)
+        device = params[0].device
+        self.side_streams = [torch.cuda.Stream(device=device) for _ in range(side_streams)] if device.type == "cuda" and side_streams else []
+        self.running_tables = {}
+        for name, m in self.module.named_modules():
+            if isinstance(m, torch.nn.Conv2d):
+                m.forward = types.MethodType(self._conv_forward(index[id(m.weight)], None if m.bias is None else index[id(m.bias)]), m)
+            elif isinstance(m, torch.nn.Linear):
+                m.forward = types.MethodType(self._linear_forward(index[id(m.weight)], None if m.bias is None else index[id(m.bias)]), m)
+            elif isinstance(m, self._BATCHNORM):
+                tables = None
+                if m.track_running_stats:
+                    tables = (m.running_mean.detach().unsqueeze(0).repeat(self.groups, 1).contiguous(),
+                              m.running_var.detach().unsqueeze(0).repeat(self.groups, 1).contiguous())
+                    self.running_tables[name] = tables
+                m._gb_group = _BnGroup(self, index[id(m.weight)], index[id(m.bias)], tables)
+                m.forward = types.MethodType(lambda bn, x: bn._gb_group(bn, x, None, False), m)
+
+    # -- what the fusion covers ---------------------------------------------------------------------------------
+    @staticmethod
+    def _loss_kind(loss_fn):
+        for cls, kind in ((torch.nn.CrossEntropyLoss, "ce"), (torch.nn.NLLLoss, "nll"), (torch.nn.BCELoss, "bce")):
+            if isinstance(loss_fn, cls):
+                return kind if getattr(loss_fn, "reduction", "mean") == "mean" and getattr(loss_fn, "weight", None) is None else None
+        return None
+
+    @classmethod
+    def unsupported_reason(cls, module, loss_fn):
+        """None when every parameter of `module` belongs to a layer the fusion knows how to differentiate per worker."""
+        if cls._loss_kind(loss_fn) is None:
+            return "loss %s" % type(loss_fn).__name__
+        covered = set()
+        for m in module.modules():
+            own = list(m.parameters(recurse=False))
+            if not own:
+                continue
+            if isinstance(m, torch.nn.Conv2d) and m.padding_mode == "zeros" and not isinstance(m.padding, str):
+                pass
+            elif isinstance(m, torch.nn.Linear):
+                pass
+            elif isinstance(m, cls._BATCHNORM) and m.affine and m.momentum is not None:
+                pass
+            else:
+                return "layer %s" % type(m).__name__
+            covered.update(id(p) for p in own)
+        if any(id(p) not in covered for p in module.parameters()):
+            return "parameters outside Conv2d / Linear / BatchNorm layers"
+        if len({id(p) for p in module.parameters()}) != len(list(module.parameters())):
+            return "shared parameters"
+        return None
+
+    # -- patched layer forwards -----------------------------------------------------------------------------------
+    def _conv_forward(self, widx, bidx):
+        owner = self
+
+        def forward(conv, x):
+            return _GroupedConv.apply(x, conv.weight, conv.bias, owner, conv, widx, bidx)
+        return forward
+
+    def _linear_forward(self, widx, bidx):
+        owner = self
+
+        def forward(lin, x):
+            if x.dim() != 2:
+                raise ValueError("worker fusion expects 2-D inputs to Linear layers")
+            return _GroupedLinear.apply(x, lin.weight, lin.bias, owner, widx, bidx)
+        return forward
+
+    def tf32_matmul(self):
+        return _Tf32(torch.backends.cudnn.allow_tf32)   # weight-gradient GEMMs at the precision of the convolutions they replace
+
+    # -- one step ------------------------------------------------------------------------------------------------
+    def forward_backward(self, data, target, losses):
+        G = self.groups
+        self.module.train()
+        out = self.module(data)
+        if self.loss_kind == "ce":
+            per_sample = F.cross_entropy(out, target, reduction="none")
+        elif self.loss_kind == "nll":
+            per_sample = F.nll_loss(out, target, reduction="none")
+        else:
+            per_sample = F.binary_cross_entropy(out, target, reduction="none")
+        per_worker = per_sample.reshape(G, -1).mean(1)
+        per_worker.sum().backward()
+        losses.copy_(per_worker.detach())
+        if self.side_streams:
+            cur = torch.cuda.current_stream(data.device)
+            for s in self.side_streams:
+                cur.wait_stream(s)
+        self.sink.flush()
+
+
+class _BnGroup:
+    """Grouped BatchNorm call for one layer (also reached from the fused ResNet block forwards)."""
+
+    def __init__(self, owner, widx, bidx, tables):
+        self.owner, self.widx, self.bidx, self.tables = owner, widx, bidx, tables
+
+    def __call__(self, bn, x, residual, relu):
+        if not bn.training:
+            y = F.batch_norm(x, bn.running_mean, bn.running_var, bn.weight, bn.bias, False, 0.0, bn.eps)
+            if residual is not None:
+                y = y + residual
+            return torch.relu(y) if relu else y
+        sink = self.owner.sink
+        rm, rv = self.tables if self.tables is not None else (None, None)
+        return grouped_batch_norm(x, bn.weight, bn.bias, rm, rv, self.owner.groups, bn.eps, bn.momentum, residual, relu,
+                                  lambda dg, db: (sink.put(self.widx, dg), sink.put(self.bidx, db)))

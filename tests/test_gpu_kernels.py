@@ -360,16 +360,20 @@ def test_engine_gradient_gather_matches_bound_grads():
     cuda_lib()
     finals = {}
     for tag, kw in (("bound", dict(gather_grads=False, fast_bn=False, use_graphs=False, split_backward=False)),
-                    ("gather", dict(gather_grads=True, fast_bn=True, use_graphs=False)),
-                    ("graph", dict(gather_grads=True, fast_bn=True, use_graphs=True)),
-                    ("nchw", dict(gather_grads=True, fast_bn=True, use_graphs=False, channels_last=False))):
+                    ("gather", dict(gather_grads=True, fast_bn=True, use_graphs=False, fuse_workers=False)),
+                    ("graph", dict(gather_grads=True, fast_bn=True, use_graphs=True, fuse_workers=False)),
+                    ("nchw", dict(gather_grads=True, fast_bn=True, use_graphs=False, channels_last=False, fuse_workers=False)),
+                    ("fused", dict(use_graphs=False, fuse_workers=True)),
+                    ("fused_graph", dict(use_graphs=True, fuse_workers=True)),
+                    ("fused_nchw", dict(use_graphs=False, fuse_workers=True, channels_last=False))):
         eng = SSMWEngine("cnn", "synthetic-cifar10", "cross-entropy", 7, 1, "median", 8, "sgd", dict(lr=0.02, momentum=0.9),
                          byzantine={6: "reverse"}, seed=3, **kw)
         for m in eng.master.module.modules():   # dropout would make the runs incomparable
             if isinstance(m, (torch.nn.Dropout, torch.nn.Dropout2d)):
                 m.p = 0.0
-        for w in eng.workers:
-            for m in w.replica.module.modules():
+        assert (eng.fused is not None) == tag.startswith("fused")
+        for module in [w.replica.module for w in eng.workers] + ([eng.fused.module] if eng.fused is not None else []):
+            for m in module.modules():
                 if isinstance(m, (torch.nn.Dropout, torch.nn.Dropout2d)):
                     m.p = 0.0
         for i in range(3):
@@ -379,11 +383,11 @@ def test_engine_gradient_gather_matches_bound_grads():
         bn = [b.clone() for b in eng.workers[0].replica.module.buffers() if b.dtype == torch.float32]
         finals[tag + "_bn"] = torch.cat([b.reshape(-1) for b in bn])
         eng.close()
-    for tag in ("gather", "graph", "nchw"):
+    for tag in ("gather", "graph", "nchw", "fused", "fused_graph", "fused_nchw"):
         diff = (finals[tag] - finals["bound"]).abs()
         assert diff.max().item() < 2e-3 and (diff > 2e-4).float().mean().item() < 1e-4, "%s vs bound: max %g" % (tag, diff.max().item())
-        if tag != "graph":  # graph capture replays its warm-up iterations, which also move the BN running statistics
-            torch.testing.assert_close(finals[tag + "_bn"], finals["bound_bn"], rtol=1e-3, atol=1e-4)
+        if "graph" not in tag:  # graph capture replays its warm-up iterations, which also move the BN running statistics
+            torch.testing.assert_close(finals[tag + "_bn"], finals["bound_bn"], rtol=2e-3, atol=5e-4)   # TF32 convolutions, different batch shapes
 
 
 def test_avgpool_dropout_bce_kernels():

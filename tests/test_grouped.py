@@ -1,0 +1,168 @@
+"""Worker fusion (parallel/grouped.py): one pass over the concatenated batches must give every worker exactly the
+gradient its own replica would compute (per-worker BatchNorm statistics, per-worker weight gradients, per-worker loss)."""
+import copy
+
+import pytest
+import torch
+
+from garfield_b200.parallel.arena import FlatModel
+from garfield_b200.parallel.grouped import GroupedWorkers
+
+
+class _Block(torch.nn.Module):
+    def __init__(self, cin, cout, stride):
+        super().__init__()
+        self.conv1 = torch.nn.Conv2d(cin, cout, 1, bias=False)
+        self.bn1 = torch.nn.BatchNorm2d(cout)
+        self.conv2 = torch.nn.Conv2d(cout, cout, 3, stride=stride, padding=1, bias=True)
+        self.bn2 = torch.nn.BatchNorm2d(cout)
+        self.down = torch.nn.Conv2d(cin, cout, 1, stride=stride, bias=False)
+
+    def forward(self, x):
+        out = torch.relu(self.bn1(self.conv1(x)))
+        out = self.bn2(self.conv2(out))
+        return torch.relu(out + self.down(x))
+
+
+class _Net(torch.nn.Module):
+    def __init__(self, classes=5):
+        super().__init__()
+        self.stem = torch.nn.Conv2d(3, 8, 3, padding=1)
+        self.b1 = _Block(8, 16, 1)
+        self.b2 = _Block(16, 32, 2)
+        self.pool = torch.nn.AdaptiveAvgPool2d(1)
+        self.fc = torch.nn.Linear(32, classes)
+
+    def forward(self, x):
+        x = self.b2(self.b1(torch.relu(self.stem(x))))
+        return self.fc(torch.flatten(self.pool(x), 1))
+
+
+def _reference(module, xs, ys, loss_fn):
+    grads, losses, stats = [], [], []
+    for x, y in zip(xs, ys):
+        m = copy.deepcopy(module)
+        m.train()
+        loss = loss_fn(m(x), y)
+        loss.backward()
+        grads.append(torch.cat([p.grad.reshape(-1) for p in m.parameters()]))
+        losses.append(loss.detach())
+        stats.append({k: v.clone() for k, v in m.named_buffers() if "running" in k})
+    return grads, losses, stats
+
+
+def _run_grouped(module, xs, ys, loss_fn, device, channels_last):
+    G = len(xs)
+    flat_model = FlatModel(copy.deepcopy(module), device, channels_last=channels_last)
+    d = flat_model.numel
+    matrix = torch.zeros(G, d, device=device)
+    group = GroupedWorkers(flat_model, [matrix[g] for g in range(G)], loss_fn, side_streams=2)
+    data = torch.cat(xs).to(device)
+    if channels_last:
+        data = data.contiguous(memory_format=torch.channels_last)
+    losses = torch.zeros(G, device=device)
+    for _ in range(2):  # twice: the sink must not keep state between steps
+        for name, (rm, rv) in group.running_tables.items():
+            ref = dict(module.named_modules())[name]
+            rm.copy_(ref.running_mean.expand_as(rm)); rv.copy_(ref.running_var.expand_as(rv))
+        group.forward_backward(data, torch.cat(ys).to(device), losses)
+    return flat_model, matrix, losses, group
+
+
+def _logical(flat_model, row):
+    """Row of the gradient matrix → the reference's flat order (undo the OHWI storage of 4-D parameters)."""
+    return torch.cat([flat_model._view(row, off, n, shape).reshape(-1) for off, n, shape in flat_model.slices])
+
+
+def test_grouped_workers_match_separate_replicas_cpu():
+    torch.manual_seed(0)
+    module = _Net()
+    G, B = 3, 4
+    xs = [torch.randn(B, 3, 8, 8) for _ in range(G)]
+    ys = [torch.randint(0, 5, (B,)) for _ in range(G)]
+    loss_fn = torch.nn.CrossEntropyLoss()
+    grads, losses, stats = _reference(module, xs, ys, loss_fn)
+    flat_model, matrix, glosses, group = _run_grouped(module, xs, ys, loss_fn, torch.device("cpu"), channels_last=False)
+    for g in range(G):
+        assert torch.allclose(_logical(flat_model, matrix[g]), grads[g], rtol=1e-4, atol=1e-5), g
+        assert torch.allclose(glosses[g], losses[g], rtol=1e-5)
+        for name, (rm, rv) in group.running_tables.items():
+            assert torch.allclose(rm[g], stats[g][name + ".running_mean"], rtol=1e-4, atol=1e-6)
+            assert torch.allclose(rv[g], stats[g][name + ".running_var"], rtol=1e-4, atol=1e-6)
+
+
+def test_grouped_workers_channels_last_storage_cpu():
+    torch.manual_seed(1)
+    module = _Net()
+    xs = [torch.randn(2, 3, 8, 8) for _ in range(2)]
+    ys = [torch.randint(0, 5, (2,)) for _ in range(2)]
+    loss_fn = torch.nn.CrossEntropyLoss()
+    grads, _, _ = _reference(module, xs, ys, loss_fn)
+    flat_model, matrix, _, _ = _run_grouped(module, xs, ys, loss_fn, torch.device("cpu"), channels_last=True)
+    for g in range(2):
+        assert torch.allclose(_logical(flat_model, matrix[g]), grads[g], rtol=1e-4, atol=1e-5)
+
+
+def test_unsupported_models_are_reported():
+    loss_fn = torch.nn.CrossEntropyLoss()
+    assert GroupedWorkers.unsupported_reason(_Net(), loss_fn) is None
+    odd = torch.nn.Sequential(torch.nn.Conv2d(3, 4, 1), torch.nn.GroupNorm(2, 4))
+    assert "GroupNorm" in GroupedWorkers.unsupported_reason(odd, loss_fn)
+    assert "loss" in GroupedWorkers.unsupported_reason(_Net(), torch.nn.MSELoss())
+
+
+@pytest.mark.gpu
+def test_grouped_workers_match_separate_replicas_gpu():
+    torch.manual_seed(0)
+    dev = torch.device("cuda")
+    prev = torch.backends.cudnn.allow_tf32
+    torch.backends.cudnn.allow_tf32 = False     # exact comparison; the bench runs with the default (TF32) on both paths
+    try:
+        module = _Net().to(dev)
+        G, B = 4, 6
+        xs = [torch.randn(B, 3, 16, 16, device=dev) for _ in range(G)]
+        ys = [torch.randint(0, 5, (B,), device=dev) for _ in range(G)]
+        loss_fn = torch.nn.CrossEntropyLoss()
+        grads, losses, stats = _reference(module, xs, ys, loss_fn)
+        flat_model, matrix, glosses, group = _run_grouped(module, xs, ys, loss_fn, dev, channels_last=True)
+        torch.cuda.synchronize()
+        for g in range(G):
+            got, want = _logical(flat_model, matrix[g]), grads[g]
+            assert (got - want).norm() <= 2e-4 * want.norm(), (g, float((got - want).norm() / want.norm()))
+            assert torch.allclose(glosses[g], losses[g], rtol=1e-4)
+            for name, (rm, rv) in group.running_tables.items():
+                assert torch.allclose(rm[g], stats[g][name + ".running_mean"], rtol=1e-3, atol=1e-5)
+                assert torch.allclose(rv[g], stats[g][name + ".running_var"], rtol=1e-3, atol=1e-5)
+    finally:
+        torch.backends.cudnn.allow_tf32 = prev
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("groups,batch,channels,hw", [(1, 25, 64, 16), (3, 4, 64, 20), (8, 25, 256, 8), (2, 40, 8, 32), (1, 3, 2048, 1),
+                                                      (4, 2, 12, 3), (1, 200, 64, 16)])
+def test_grouped_batchnorm_kernel_matches_torch(groups, batch, channels, hw):
+    """Cluster-split / register-resident / re-read variants of the fused NHWC BatchNorm against the per-group torch formula."""
+    from garfield_b200.ops import nn as gnn
+    torch.manual_seed(groups * 1000 + channels)
+    dev = torch.device("cuda")
+    n = groups * batch
+    x = (torch.randn(n, channels, hw, hw, device=dev) * 2 + 3).contiguous(memory_format=torch.channels_last)
+    res = torch.randn_like(x).contiguous(memory_format=torch.channels_last)
+    gamma, beta = torch.rand(channels, device=dev) + 0.5, torch.randn(channels, device=dev)
+    gy = torch.randn_like(x)
+    for relu, use_res in ((True, True), (False, False), (True, False)):
+        outs = []
+        for device in (dev, torch.device("cpu")):
+            xi = x.to(device).detach().requires_grad_(True)
+            ri = res.to(device).detach().requires_grad_(True) if use_res else None
+            g, b = gamma.to(device).clone().requires_grad_(True), beta.to(device).clone().requires_grad_(True)
+            rm, rv = torch.zeros(groups, channels, device=device), torch.ones(groups, channels, device=device)
+            got = {}
+            y = gnn.grouped_batch_norm(xi, g, b, rm, rv, groups, 1e-5, 0.1, ri, relu, sink=lambda dg, db: got.update(dg=dg, db=db))
+            y.backward(gy.to(device))
+            outs.append((y.detach().cpu(), xi.grad.cpu(), None if ri is None else ri.grad.cpu(), got["dg"].reshape(groups, channels).cpu(),
+                         got["db"].reshape(groups, channels).cpu(), rm.cpu(), rv.cpu()))
+        for a, b in zip(*outs):
+            if a is not None:   # a ReLU output within rounding of zero may flip its mask: tolerate isolated elements
+                bad = (a - b).abs() > 2e-3 + 2e-3 * b.abs()
+                assert int(bad.sum()) <= max(3, 2e-6 * bad.numel()), (int(bad.sum()), float((a - b).abs().max()))   # (and the sums they feed)
