@@ -37,24 +37,27 @@ __device__ __forceinline__ void st4(float* p, float4 v) { *reinterpret_cast<floa
 __device__ __forceinline__ float4 add4(float4 a, float4 b) { return make_float4(a.x + b.x, a.y + b.y, a.z + b.z, a.w + b.w); }
 __device__ __forceinline__ float4 zero4() { return make_float4(0.f, 0.f, 0.f, 0.f); }
 
-// Sum a float4 over all row lanes of the CTA; result valid in every thread of that quad.
+// Sum two float4 accumulators over all row lanes of the CTA (one barrier pair for both); results valid in every
+// thread of that quad.
 template <int QUADS>
-__device__ __forceinline__ float4 reduce_rows(float4 v, float4 (*scratch)[QUADS]) {
+__device__ __forceinline__ void reduce_rows(float4& a, float4& b, float4 (*scratch)[2][QUADS]) {
 #pragma unroll
     for (int o = QUADS; o < 32; o <<= 1) {
-        v.x += __shfl_xor_sync(0xffffffffu, v.x, o);
-        v.y += __shfl_xor_sync(0xffffffffu, v.y, o);
-        v.z += __shfl_xor_sync(0xffffffffu, v.z, o);
-        v.w += __shfl_xor_sync(0xffffffffu, v.w, o);
+        a.x += __shfl_xor_sync(0xffffffffu, a.x, o); a.y += __shfl_xor_sync(0xffffffffu, a.y, o);
+        a.z += __shfl_xor_sync(0xffffffffu, a.z, o); a.w += __shfl_xor_sync(0xffffffffu, a.w, o);
+        b.x += __shfl_xor_sync(0xffffffffu, b.x, o); b.y += __shfl_xor_sync(0xffffffffu, b.y, o);
+        b.z += __shfl_xor_sync(0xffffffffu, b.z, o); b.w += __shfl_xor_sync(0xffffffffu, b.w, o);
     }
     int const warp = threadIdx.x >> 5, lane = threadIdx.x & 31, quad = lane % QUADS;
+    if (lane < QUADS) { scratch[warp][0][quad] = a; scratch[warp][1][quad] = b; }
     __syncthreads();
-    if (lane < QUADS) scratch[warp][quad] = v;
-    __syncthreads();
-    float4 total = zero4();
+    float4 ta = zero4(), tb = zero4();
 #pragma unroll
-    for (int w = 0; w < kBnThreads / 32; ++w) total = add4(total, scratch[w][quad]);  // fixed order
-    return total;
+    for (int w = 0; w < kBnThreads / 32; ++w) {  // fixed order
+        ta = add4(ta, scratch[w][0][quad]);
+        tb = add4(tb, scratch[w][1][quad]);
+    }
+    a = ta; b = tb;
 }
 
 // Combine the two per-CTA partial sums over the row splits of the cluster (rank order → every CTA gets the same bits).
@@ -101,7 +104,7 @@ __global__ void __launch_bounds__(kBnThreads) bn_nhwc_fwd_kernel(int rows, int C
                                                                  const float* __restrict__ beta, float eps, float momentum, int relu,
                                                                  float* __restrict__ y, float* __restrict__ save_mean, float* __restrict__ save_invstd,
                                                                  float* __restrict__ running_mean, float* __restrict__ running_var) {
-    __shared__ float4 scratch[kBnThreads / 32][QUADS];
+    __shared__ float4 scratch[kBnThreads / 32][2][QUADS];
     __shared__ float4 part[2][QUADS];
     constexpr int kLanes = kBnThreads / QUADS;                          // row lanes per CTA
     BnGeom const t = bn_geometry<QUADS>(rows, C, splits);
@@ -130,7 +133,7 @@ __global__ void __launch_bounds__(kBnThreads) bn_nhwc_fwd_kernel(int rows, int C
                 q.x = fmaf(a, a, q.x); q.y = fmaf(b, b, q.y); q.z = fmaf(c, c, q.z); q.w = fmaf(d, d, q.w);
             }
         } else {
-#pragma unroll 4
+#pragma unroll 8
             for (int r = t.r0 + t.rlane; r < t.r1; r += kLanes) {
                 float4 const v = ld4(x + static_cast<long long>(r) * C + t.c0);
                 float const a = v.x - K.x, b = v.y - K.y, c = v.z - K.z, d = v.w - K.w;
@@ -139,8 +142,7 @@ __global__ void __launch_bounds__(kBnThreads) bn_nhwc_fwd_kernel(int rows, int C
             }
         }
     }
-    s = reduce_rows<QUADS>(s, scratch);
-    q = reduce_rows<QUADS>(q, scratch);
+    reduce_rows<QUADS>(s, q, scratch);
     reduce_cluster<QUADS>(s, q, part, splits, t.quad);
     if (!t.live) return;
     float const inv_rows = 1.0f / static_cast<float>(rows);
@@ -166,7 +168,7 @@ __global__ void __launch_bounds__(kBnThreads) bn_nhwc_fwd_kernel(int rows, int C
             if (r < t.r1) emit(r, keep[i]);
         }
     } else {
-#pragma unroll 4
+#pragma unroll 8
         for (int r = t.r0 + t.rlane; r < t.r1; r += kLanes) emit(r, ld4(x + static_cast<long long>(r) * C + t.c0));
     }
     if (t.rlane == 0 && blockIdx.x == 0) {
@@ -197,7 +199,7 @@ __global__ void __launch_bounds__(kBnThreads) bn_nhwc_bwd_kernel(int rows, int C
                                                                  const float* __restrict__ save_mean, const float* __restrict__ save_invstd, int relu,
                                                                  float* __restrict__ dx, float* __restrict__ d_residual, float* __restrict__ dgamma,
                                                                  float* __restrict__ dbeta) {
-    __shared__ float4 scratch[kBnThreads / 32][QUADS];
+    __shared__ float4 scratch[kBnThreads / 32][2][QUADS];
     __shared__ float4 part[2][QUADS];
     constexpr int kLanes = kBnThreads / QUADS;
     BnGeom const t = bn_geometry<QUADS>(rows, C, splits);
@@ -244,8 +246,7 @@ __global__ void __launch_bounds__(kBnThreads) bn_nhwc_bwd_kernel(int rows, int C
             }
         }
     }
-    s1 = reduce_rows<QUADS>(s1, scratch);
-    s2 = reduce_rows<QUADS>(s2, scratch);
+    reduce_rows<QUADS>(s1, s2, scratch);
     reduce_cluster<QUADS>(s1, s2, part, splits, t.quad);
     if (!t.live) return;
     float const inv_rows = 1.0f / static_cast<float>(rows);
@@ -286,19 +287,21 @@ struct BnPlan {
     dim3 grid;
 };
 
-// Channel quads per CTA: as many as keep >= 64 CTAs from channels × groups alone (128-byte rows for wide layers, more
-// CTAs for narrow ones); then split the rows over a cluster until ≈2 CTAs per SM exist or a CTA has < 1 row per lane.
+// One wave of fat CTAs: take the widest channel slab (128-byte rows) that still yields >= one CTA per SM from
+// channels x groups alone, going down to 32-byte rows (one sector) before giving up; only when even that leaves SMs
+// idle split the rows over a cluster (whose DSMEM exchange costs two cluster barriers), until every SM has a CTA or a
+// CTA would have less than one row per lane.
 inline BnPlan plan(int groups, int rows, int C) {
     BnPlan p;
     int const quads_total = C / 4;
-    p.quads = 1;
-    for (int q = 8; q > 1; q >>= 1)
-        if (static_cast<long long>(quads_total / q) * groups >= 64) { p.quads = q; break; }
+    int const sms = device_sm_count();
+    p.quads = quads_total >= 2 ? 2 : 1;
+    for (int q = 8; q > 2; q >>= 1)
+        if (static_cast<long long>((quads_total + q - 1) / q) * groups >= sms && quads_total % q == 0) { p.quads = q; break; }
     int const slabs = (quads_total + p.quads - 1) / p.quads;
     int const lanes = kBnThreads / p.quads;
     p.splits = 1;
-    while (p.splits < kMaxSplits && static_cast<long long>(slabs) * groups * p.splits < 2LL * device_sm_count() && rows / (p.splits * 2) >= lanes)
-        p.splits *= 2;
+    while (p.splits < kMaxSplits && static_cast<long long>(slabs) * groups * p.splits < sms && rows / (p.splits * 2) >= lanes) p.splits *= 2;
     int const chunk = (rows + p.splits - 1) / p.splits;
     p.keep = (chunk + lanes - 1) / lanes <= kKeep;
     p.grid = dim3(p.splits, slabs, groups);

@@ -50,6 +50,19 @@ class _GradSink:
         base = rows[0]
         self.row_offsets = [(r.data_ptr() - base.data_ptr()) // 4 for r in rows]
         self.contiguous_rows = base.is_cuda and all(o >= 0 for o in self.row_offsets)
+        pitch = self.row_offsets[1] if self.groups > 1 else base.numel()
+        self.pitch = pitch if self.contiguous_rows and all(o == g * pitch for g, o in enumerate(self.row_offsets)) else None
+
+    DONE = object()   # marker: the gradient was written straight into the rows
+
+    def direct(self, index, rows, cols):
+        """[G, rows, cols] strided view of parameter `index` inside the G gradient rows (row-major matrix layout), so a
+        batched GEMM can write the per-worker gradients in place; None when the rows are not uniformly pitched."""
+        if self.pitch is None:
+            return None
+        off, n, _ = self.slices[index]
+        base = self.rows[0]
+        return torch.as_strided(base, (self.groups, rows, cols), (self.pitch, cols, 1), base.storage_offset() + off)
 
     def put(self, index, grads):
         """grads: a [G, *shape] tensor or a list of G tensors of the parameter's shape."""
@@ -59,6 +72,8 @@ class _GradSink:
         srcs, offs, sizes = [], [], []
         for index, (p, (off, n, shape)) in enumerate(zip(self.params, self.slices)):
             grads = self.pending.get(index)
+            if grads is self.DONE:
+                continue
             for g in range(self.groups):
                 row = self.rows[g]
                 if grads is None:
@@ -96,15 +111,35 @@ class _GroupedConv(torch.autograd.Function):
         stride, padding, dilation = list(conv.stride), list(conv.padding), list(conv.dilation)
         pointwise = (conv.kernel_size == (1, 1) and conv.groups == 1 and conv.padding == (0, 0) and x.is_cuda
                      and x.is_contiguous(memory_format=torch.channels_last))
+        gx = None
         if pointwise:
-            # per-worker weight gradients of a 1×1 convolution = one batched GEMM over the NHWC views
+            # per-worker weight gradients of a 1×1 convolution = one batched GEMM over the NHWC views, written straight
+            # into the gradient rows, on a side stream (off the data-gradient chain)
             if not gy.is_contiguous(memory_format=torch.channels_last):
                 gy = gy.contiguous(memory_format=torch.channels_last)
-            xs = x if conv.stride == (1, 1) else x[:, :, ::conv.stride[0], ::conv.stride[1]].contiguous(memory_format=torch.channels_last)
-            xm = xs.permute(0, 2, 3, 1).reshape(G, -1, xs.shape[1])
-            gm = gy.permute(0, 2, 3, 1).reshape(G, -1, gy.shape[1])
+            strided = conv.stride != (1, 1)
+            xs = x[:, :, ::conv.stride[0], ::conv.stride[1]].contiguous(memory_format=torch.channels_last) if strided else x
+            cin, cout = xs.shape[1], gy.shape[1]
+            xm = xs.permute(0, 2, 3, 1).reshape(G, -1, cin)
+            gm = gy.permute(0, 2, 3, 1).reshape(G, -1, cout)
+            side = owner.next_side()
             with owner.tf32_matmul():
-                owner.sink.put(widx, torch.bmm(gm.transpose(1, 2), xm).unsqueeze(-1).unsqueeze(-1))
+                if side is not None:
+                    side.wait_stream(torch.cuda.current_stream(x.device))
+                    xs.record_stream(side); gy.record_stream(side)
+                with torch.cuda.stream(side) if side is not None else _NoStream():
+                    out = owner.sink.direct(widx, cout, cin)
+                    if out is not None:
+                        torch.bmm(gm.transpose(1, 2), xm, out=out)
+                        owner.sink.put(widx, owner.sink.DONE)
+                    else:
+                        owner.sink.put(widx, torch.bmm(gm.transpose(1, 2), xm).unsqueeze(-1).unsqueeze(-1))
+                if strided and ctx.needs_input_grad[0]:
+                    # data gradient of a strided 1×1 convolution: one GEMM scattered onto the sampled pixels (the library's
+                    # strided-dgrad kernels take 50-150 µs on these shapes)
+                    dxs = gm.reshape(-1, cout) @ w.reshape(cout, cin)
+                    gx = torch.zeros_like(x)
+                    gx[:, :, ::conv.stride[0], ::conv.stride[1]] = dxs.view(xs.shape[0], xs.shape[2], xs.shape[3], cin).permute(0, 3, 1, 2)
         else:
             sides = owner.side_streams
             cur = torch.cuda.current_stream(x.device) if sides else None
@@ -126,8 +161,7 @@ class _GroupedConv(torch.autograd.Function):
             owner.sink.put(widx, grads)
         if bidx is not None:
             owner.sink.put(bidx, gy.reshape(G, B, *gy.shape[1:]).sum((1, 3, 4)))
-        gx = None
-        if ctx.needs_input_grad[0]:
+        if gx is None and ctx.needs_input_grad[0]:
             gx = _aten.convolution_backward(gy, x, w, None, stride, padding, dilation, False, [0, 0], conv.groups, [True, False, False])[0]
         return gx, None, None, None, None, None, None
 
@@ -146,11 +180,24 @@ class _GroupedLinear(torch.autograd.Function):
         G = owner.groups
         xm = x.reshape(G, -1, x.shape[-1])
         gm = gy.reshape(G, -1, gy.shape[-1])
-        owner.sink.put(widx, torch.bmm(gm.transpose(1, 2), xm))
+        out = owner.sink.direct(widx, gm.shape[-1], xm.shape[-1])
+        if out is not None:
+            torch.bmm(gm.transpose(1, 2), xm, out=out)
+            owner.sink.put(widx, owner.sink.DONE)
+        else:
+            owner.sink.put(widx, torch.bmm(gm.transpose(1, 2), xm))
         if bidx is not None:
             owner.sink.put(bidx, gm.sum(1))
         gx = gy @ w if ctx.needs_input_grad[0] else None
         return gx, None, None, None, None, None
+
+
+class _NoStream:
+    def __enter__(self):
+        return None
+
+    def __exit__(self, *exc):
+        return False
 
 
 class _Tf32:
@@ -251,6 +298,12 @@ class GroupedWorkers:
                 raise ValueError("worker fusion expects 2-D inputs to Linear layers")
             return _GroupedLinear.apply(x, lin.weight, lin.bias, owner, widx, bidx)
         return forward
+
+    def next_side(self):
+        if not self.side_streams:
+            return None
+        self._side_rr = (getattr(self, "_side_rr", 0) + 1) % len(self.side_streams)
+        return self.side_streams[self._side_rr]
 
     def tf32_matmul(self):
         return _Tf32(torch.backends.cudnn.allow_tf32)   # weight-gradient GEMMs at the precision of the convolutions they replace
