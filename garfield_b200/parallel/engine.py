@@ -260,6 +260,7 @@ class SSMWEngine:
             servers = range(self.world) if self.sharded else [0]
             self._param_flags = [word(r, 1) for r in servers]
         self._graph = None
+        self._whole_step = None          # None: try the whole-iteration graph on one GPU; False: it failed to capture
         self._copy_stream = None
         self.use_graphs = use_graphs
         self.steps_done = 0
@@ -476,6 +477,8 @@ class SSMWEngine:
             if self.workers:
                 return torch.stack([w.loss for w in self.workers]).mean()
             return torch.zeros((), device=self.device)
+        if self._whole_step_capturable():
+            return self._step_whole()
         self.compute_gradients()
         self._barrier()                      # all gradient rows are complete
         if self.is_server:
@@ -485,6 +488,48 @@ class SSMWEngine:
         if self.workers:
             return torch.stack([w.loss for w in self.workers]).mean()
         return torch.zeros((), device=self.device)
+
+    # -- single-GPU fast path: the WHOLE iteration (gradient pass, attacks, GAR + fused SGD, loss) is one CUDA graph ----
+    def _whole_step_capturable(self):
+        return (self.world == 1 and self.use_graphs and self._whole_step is not False and self.workers and self.optimizer is not None
+                and self.optimizer.name == "sgd" and all(w.attack in (None, "reverse", "lie", "empire") for w in self.workers))
+
+    def _step_body(self):
+        self._run_workers()
+        for w in self.workers:
+            if w.attack is not None:
+                self._attack(w)
+        self.aggregate_and_update()
+        self._step_loss.copy_(self._group_losses.mean() if self.fused is not None else torch.stack([w.loss for w in self.workers]).mean())
+
+    def _step_whole(self):
+        opt = self.optimizer
+        if not hasattr(self, "_step_loss"):
+            self._step_loss = torch.zeros((), device=self.device)
+            self._eager_steps, self._step_graph, self._step_key = 0, None, None
+        key = tuple(sorted((k, v) for k, v in opt.hyper.items() if isinstance(v, (int, float, bool))))
+        if self._eager_steps < 2 or opt.steps == 0:      # warm-up: cuDNN autotuning, allocator, momentum-buffer initialisation
+            self._step_body()
+            self._eager_steps += 1
+        else:
+            if self._step_graph is None or key != self._step_key:   # hyper-parameters live in kernel arguments: re-capture on change
+                try:
+                    graph = torch.cuda.CUDAGraph()
+                    before, steps_before = _lib.launches[0], opt.steps
+                    with torch.cuda.graph(graph):
+                        self._step_body()
+                    opt.steps = steps_before
+                    self._step_launches = _lib.launches[0] - before
+                    self._step_graph, self._step_key = graph, key
+                except Exception:
+                    self._whole_step = False            # something in the rule is not capturable: keep the two-phase path
+                    torch.cuda.synchronize(self.device)
+                    return self.step(self.steps_done, load=False)
+            self._step_graph.replay()
+            opt.note_fused_step()
+            _lib.count(self._step_launches)
+        self.steps_done += 1
+        return self._step_loss
 
     # -- evaluation and checkpoints -----------------------------------------------------------------------
     def accuracy(self, batches):

@@ -162,7 +162,16 @@ class _GroupedConv(torch.autograd.Function):
         if bidx is not None:
             owner.sink.put(bidx, gy.reshape(G, B, *gy.shape[1:]).sum((1, 3, 4)))
         if gx is None and ctx.needs_input_grad[0]:
-            gx = _aten.convolution_backward(gy, x, w, None, stride, padding, dilation, False, [0, 0], conv.groups, [True, False, False])[0]
+            if (x.is_cuda and max(conv.stride) > 1 and conv.dilation == (1, 1) and conv.groups == 1
+                    and all(2 * p == k - 1 for p, k in zip(conv.padding, conv.kernel_size))):
+                # strided k×k data gradient = stride-1 data gradient of the zero-upsampled output gradient ("same"
+                # padding keeps the sizes equal); the library's strided-dgrad kernels are 5-10x slower on these shapes
+                up = torch.empty((gy.shape[0], gy.shape[1], x.shape[2], x.shape[3]), device=gy.device, dtype=gy.dtype,
+                                 memory_format=torch.channels_last if x.is_contiguous(memory_format=torch.channels_last) else torch.contiguous_format).zero_()
+                up[:, :, ::conv.stride[0], ::conv.stride[1]] = gy
+                gx = _aten.convolution_backward(up, x, w, None, [1, 1], padding, dilation, False, [0, 0], 1, [True, False, False])[0]
+            else:
+                gx = _aten.convolution_backward(gy, x, w, None, stride, padding, dilation, False, [0, 0], conv.groups, [True, False, False])[0]
         return gx, None, None, None, None, None, None
 
 
