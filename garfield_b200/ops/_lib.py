@@ -53,6 +53,7 @@ def _declare(h):
     h.gb_bce_loss.argtypes = [vp, vp, vp, vp, i64, vp]
     h.gb_bn_nhwc_forward.argtypes = [vp] * 9 + [i32, i32, f32, f32, i32, vp]
     h.gb_bn_nhwc_backward.argtypes = [vp] * 10 + [i32, i32, i32, vp]
+    h.gb_im2col_nhwc.argtypes = [vp, vp] + [i32] * 10 + [vp]
     h.gb_bn_nhwc_forward_grouped.argtypes = [vp] * 9 + [i32, i32, i32, f32, f32, i32, vp]
     h.gb_bn_nhwc_backward_grouped.argtypes = [vp] * 10 + [i32, i32, i32, i32, vp]
     h.gb_sgd_step.argtypes = [vp, vp, vp, i64, f32, f32, f32, f32, i32, i32, pp, i32, vp]

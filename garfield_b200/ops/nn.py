@@ -465,3 +465,18 @@ def _per_group(weight, bias, groups, sink):
     if sink is None:
         return weight.unsqueeze(0).expand(groups, *weight.shape), bias.unsqueeze(0).expand(groups, *bias.shape)
     return _PerGroupFn.apply(weight, bias, groups, sink)
+
+
+def im2col_nhwc(x, kernel_size, stride, padding):
+    """Patch matrix [N·Ho·Wo, KH·KW·C] in (kh, kw, c) order of a channels-last CUDA activation (C % 4 == 0)."""
+    n, c, h, w = x.shape
+    (kh, kw), (sh, sw), (ph, pw) = kernel_size, stride, padding
+    ho, wo = (h + 2 * ph - kh) // sh + 1, (w + 2 * pw - kw) // sw + 1
+    if not (x.is_cuda and x.dtype == torch.float32 and c % 4 == 0 and x.is_contiguous(memory_format=torch.channels_last)):
+        cols = torch.nn.functional.unfold(x, (kh, kw), 1, (ph, pw), (sh, sw))                 # [N, C·KH·KW, L], (c, kh, kw) order
+        return cols.view(n, c, kh * kw, ho * wo).permute(0, 3, 2, 1).reshape(n * ho * wo, kh * kw * c)
+    cols = torch.empty(n * ho * wo, kh * kw * c, device=x.device)
+    with torch.cuda.device(x.device):
+        _lib.check(_lib.require().gb_im2col_nhwc(_ptr(x), _ptr(cols), n, h, w, c, kh, kw, sh, sw, ph, pw, _lib.stream_ptr(x.device)))
+    _lib.count()
+    return cols

@@ -26,7 +26,7 @@ import torch
 import torch.nn.functional as F
 
 from ..ops import _lib
-from ..ops.nn import grouped_batch_norm
+from ..ops.nn import grouped_batch_norm, im2col_nhwc
 
 __all__ = ["GroupedWorkers"]
 
@@ -140,6 +140,22 @@ class _GroupedConv(torch.autograd.Function):
                     dxs = gm.reshape(-1, cout) @ w.reshape(cout, cin)
                     gx = torch.zeros_like(x)
                     gx[:, :, ::conv.stride[0], ::conv.stride[1]] = dxs.view(xs.shape[0], xs.shape[2], xs.shape[3], cin).permute(0, 3, 1, 2)
+        elif (x.is_cuda and owner.replica.channels_last and conv.groups == 1 and conv.dilation == (1, 1) and x.shape[1] % 4 == 0
+              and x.is_contiguous(memory_format=torch.channels_last) and owner.sink.direct(widx, 1, 1) is not None):
+            # k×k convolution: gather the patches once (own im2col kernel, (kh, kw, c) order), then ONE batched GEMM
+            # dW[g] = dY[g]ᵀ · cols[g] writes all workers' gradients in OHWI order straight into their rows
+            if not gy.is_contiguous(memory_format=torch.channels_last):
+                gy = gy.contiguous(memory_format=torch.channels_last)
+            cout, k = gy.shape[1], conv.kernel_size[0] * conv.kernel_size[1] * x.shape[1]
+            side = owner.next_side()
+            if side is not None:
+                side.wait_stream(torch.cuda.current_stream(x.device))
+                x.record_stream(side); gy.record_stream(side)
+            with owner.tf32_matmul(), (torch.cuda.stream(side) if side is not None else _NoStream()):
+                cols = im2col_nhwc(x, conv.kernel_size, conv.stride, conv.padding).view(G, -1, k)
+                gm = gy.permute(0, 2, 3, 1).reshape(G, -1, cout)
+                torch.bmm(gm.transpose(1, 2), cols, out=owner.sink.direct(widx, cout, k))
+            owner.sink.put(widx, owner.sink.DONE)
         else:
             sides = owner.side_streams
             cur = torch.cuda.current_stream(x.device) if sides else None

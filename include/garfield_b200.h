@@ -182,6 +182,10 @@ GB_API int gb_bn_nhwc_forward_grouped(float const* x, float const* residual, flo
 GB_API int gb_bn_nhwc_backward_grouped(float const* x, float const* y, float const* dy, float const* gamma, float const* save_mean,
                                        float const* save_invstd, float* dx, float* d_residual, float* dgamma, float* dbeta, int groups, int rows,
                                        int C, int relu, void* stream);
+/* cols[(n,ho,wo), (kh,kw,c)] = x[n, ho*s-p+kh, wo*s-p+kw, c] for channels-last x [N,H,W,C] (C % 4 == 0): the patch matrix whose
+ * batched GEMM with dY gives per-worker k x k weight gradients directly in OHWI order (worker fusion). No reference counterpart. */
+GB_API int gb_im2col_nhwc(float const* x, float* cols, int N, int H, int W, int C, int KH, int KW, int stride_h, int stride_w, int pad_h,
+                          int pad_w, void* stream);
 GB_API int gb_global_avgpool_forward(float const* x, float* y, int64_t planes, int hw, void* stream);
 GB_API int gb_global_avgpool_backward(float const* dy, float* dx, int64_t planes, int hw, void* stream);
 /* Inverted dropout with a regenerable Philox mask (apply to dy with the same seed for the backward pass). */

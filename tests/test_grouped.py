@@ -166,3 +166,13 @@ def test_grouped_batchnorm_kernel_matches_torch(groups, batch, channels, hw):
             if a is not None:   # a ReLU output within rounding of zero may flip its mask: tolerate isolated elements
                 bad = (a - b).abs() > 2e-3 + 2e-3 * b.abs()
                 assert int(bad.sum()) <= max(3, 2e-6 * bad.numel()), (int(bad.sum()), float((a - b).abs().max()))   # (and the sums they feed)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("shape,k,stride,pad", [((6, 8, 9, 7), 3, 1, 1), ((4, 64, 8, 8), 3, 2, 1), ((3, 12, 5, 5), 5, 1, 2), ((2, 4, 4, 4), 1, 2, 0)])
+def test_im2col_kernel_matches_unfold(shape, k, stride, pad):
+    from garfield_b200.ops import nn as gnn
+    x = torch.randn(*shape, device="cuda").contiguous(memory_format=torch.channels_last)
+    got = gnn.im2col_nhwc(x, (k, k), (stride, stride), (pad, pad))
+    want = gnn.im2col_nhwc(x.cpu().contiguous(), (k, k), (stride, stride), (pad, pad))
+    assert torch.equal(got.cpu(), want)
