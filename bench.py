@@ -49,6 +49,7 @@ def parse_args(argv=None):
     ap.add_argument("--no-graphs", action="store_true")
     ap.add_argument("--fuse-workers", default="auto", choices=["auto", "on", "off"],
                     help="one batched forward/backward for the workers hosted by a GPU (auto: when a rank hosts >= 2 workers)")
+    ap.add_argument("--fusion-chains", type=int, default=1, help="split a rank's fused workers into this many concurrent passes")
     ap.add_argument("--sync", default="nccl", choices=["nccl", "flags"], help="inter-rank synchronisation (N > 1)")
     return ap.parse_args(argv)
 
@@ -163,7 +164,7 @@ def run_gar(gar, args, rank, world, local, full):
     from garfield_b200.parallel.engine import SSMWEngine
     torch.backends.cudnn.benchmark = True
     engine = SSMWEngine(MODEL, DATASET, LOSS, N_WORKERS, F_BYZ, gar, BATCH, "sgd", OPT_ARGS, use_graphs=not args.no_graphs, sync=args.sync,
-                        fuse_workers={"auto": None, "on": True, "off": False}[args.fuse_workers])
+                        fuse_workers={"auto": None, "on": True, "off": False}[args.fuse_workers], fusion_chains=args.fusion_chains)
     it = 0
     for _ in range(max(args.warmup, 3)):
         engine.step(it).item()

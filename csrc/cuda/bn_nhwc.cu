@@ -117,6 +117,11 @@ __global__ void __launch_bounds__(kBnThreads) bn_nhwc_fwd_kernel(int rows, int C
         if (running_mean != nullptr) { running_mean += soff; running_var += soff; }
     }
     float4 const K = t.live ? ld4(x + t.c0) : zero4();                   // pivot: the group's first row (same in every split)
+    // issued now, consumed after the reduction: their latency hides behind the statistics pass
+    bool const writes_stats = t.live && t.rlane == 0 && blockIdx.x == 0;
+    float4 const g = t.live ? ld4(gamma + t.c0) : zero4(), b = t.live ? ld4(beta + t.c0) : zero4();
+    float4 rm = zero4(), rv = zero4();
+    if (writes_stats && running_mean != nullptr) { rm = ld4(running_mean + t.c0); rv = ld4(running_var + t.c0); }
     float4 s = zero4(), q = zero4();
     float4 keep[KEEP ? kKeep : 1];
     if (t.live) {
@@ -151,7 +156,6 @@ __global__ void __launch_bounds__(kBnThreads) bn_nhwc_fwd_kernel(int rows, int C
     float4 const var = make_float4(fmaxf(q.x * inv_rows - ds.x * ds.x, 0.f), fmaxf(q.y * inv_rows - ds.y * ds.y, 0.f),
                                    fmaxf(q.z * inv_rows - ds.z * ds.z, 0.f), fmaxf(q.w * inv_rows - ds.w * ds.w, 0.f));
     float4 const invstd = make_float4(rsqrtf(var.x + eps), rsqrtf(var.y + eps), rsqrtf(var.z + eps), rsqrtf(var.w + eps));
-    float4 const g = ld4(gamma + t.c0), b = ld4(beta + t.c0);
     float4 const scale = make_float4(g.x * invstd.x, g.y * invstd.y, g.z * invstd.z, g.w * invstd.w);
     float4 const shift = make_float4(b.x - mean.x * scale.x, b.y - mean.y * scale.y, b.z - mean.z * scale.z, b.w - mean.w * scale.w);
     auto emit = [&](int r, float4 v) {
@@ -171,12 +175,11 @@ __global__ void __launch_bounds__(kBnThreads) bn_nhwc_fwd_kernel(int rows, int C
 #pragma unroll 8
         for (int r = t.r0 + t.rlane; r < t.r1; r += kLanes) emit(r, ld4(x + static_cast<long long>(r) * C + t.c0));
     }
-    if (t.rlane == 0 && blockIdx.x == 0) {
+    if (writes_stats) {
         st4(save_mean + t.c0, mean);
         st4(save_invstd + t.c0, invstd);
         if (running_mean != nullptr) {
             float const unbias = rows > 1 ? static_cast<float>(rows) / static_cast<float>(rows - 1) : 1.0f;
-            float4 rm = ld4(running_mean + t.c0), rv = ld4(running_var + t.c0);
             float const k = 1.0f - momentum;
             rm = make_float4(k * rm.x + momentum * mean.x, k * rm.y + momentum * mean.y, k * rm.z + momentum * mean.z, k * rm.w + momentum * mean.w);
             rv = make_float4(k * rv.x + momentum * var.x * unbias, k * rv.y + momentum * var.y * unbias, k * rv.z + momentum * var.z * unbias,
@@ -290,7 +293,7 @@ struct BnPlan {
 // One wave of fat CTAs: take the widest channel slab (128-byte rows) that still yields >= one CTA per SM from
 // channels x groups alone, going down to 32-byte rows (one sector) before giving up; only when even that leaves SMs
 // idle split the rows over a cluster (whose DSMEM exchange costs two cluster barriers), until every SM has a CTA or a
-// CTA would have less than one row per lane.
+// CTA would have less than one row per lane (a split is only worth its barriers while half the SMs would otherwise idle).
 inline BnPlan plan(int groups, int rows, int C) {
     BnPlan p;
     int const quads_total = C / 4;
@@ -301,7 +304,7 @@ inline BnPlan plan(int groups, int rows, int C) {
     int const slabs = (quads_total + p.quads - 1) / p.quads;
     int const lanes = kBnThreads / p.quads;
     p.splits = 1;
-    while (p.splits < kMaxSplits && static_cast<long long>(slabs) * groups * p.splits < sms && rows / (p.splits * 2) >= lanes) p.splits *= 2;
+    while (p.splits < kMaxSplits && static_cast<long long>(slabs) * groups * p.splits * 2 <= sms && rows / (p.splits * 2) >= lanes) p.splits *= 2;
     int const chunk = (rows + p.splits - 1) / p.splits;
     p.keep = (chunk + lanes - 1) / lanes <= kKeep;
     p.grid = dim3(p.splits, slabs, groups);

@@ -157,7 +157,7 @@ class SSMWEngine:
     def __init__(self, model, dataset, loss, num_workers, f, gar, batch, optimizer="sgd", opt_args=None, byzantine=None,
                  device=None, group=None, use_graphs=True, train_set=None, seed=1234, gar_kwargs=None, sharded=None,
                  channels_last=True, sync="nccl", flag_timeout=5.0, gather_grads=True, fast_bn=True,
-                 split_backward=None, fuse_workers=None):
+                 split_backward=None, fuse_workers=None, fusion_chains=1):
         self.rank = dist.get_rank(group) if dist.is_initialized() else 0
         self.world = dist.get_world_size(group) if dist.is_initialized() else 1
         self.group = group
@@ -227,7 +227,7 @@ class SSMWEngine:
         if fuse_workers is None:
             fuse_workers = len(self.workers) >= 2 and gather_grads
         if fuse_workers and self.workers and GroupedWorkers.unsupported_reason(module, loss_fn) is None:
-            self._fuse_workers(module, loss_fn)
+            self._fuse_workers(module, loss_fn, max(1, min(int(fusion_chains), len(self.workers))))
 
         # server state (whole vector on rank 0, or this rank's coordinate slice when sharded)
         if self.sharded:
@@ -266,12 +266,11 @@ class SSMWEngine:
         self.steps_done = 0
         self.h2d_bytes = 0
 
-    def _fuse_workers(self, module, loss_fn):
+    def _fuse_workers(self, module, loss_fn, chains=1):
         """Point every local worker's inputs, loss and BatchNorm running statistics at slices of the group's
-        buffers, so loading batches, evaluation and checkpoints work on the worker objects as before."""
+        buffers, so loading batches, evaluation and checkpoints work on the worker objects as before.
+        `chains` > 1 splits the workers into that many fused passes running concurrently on their own streams."""
         G = len(self.workers)
-        replica = FlatModel(copy.deepcopy(module), self.device, flat=self.flat, channels_last=self.channels_last)
-        self.fused = GroupedWorkers(replica, [w.row for w in self.workers], loss_fn)
         first = self.workers[0]
         data = torch.zeros((G * first.data.shape[0],) + tuple(first.data.shape[1:]), device=self.device)
         if self.channels_last and data.dim() == 4:
@@ -280,11 +279,19 @@ class SSMWEngine:
         self._group_data, self._group_target = data, target
         self._group_losses = torch.zeros(G, device=self.device)
         b, t = first.data.shape[0], first.target.shape[0]
-        for g, w in enumerate(self.workers):
-            w.data, w.target, w.loss = data[g * b:(g + 1) * b], target[g * t:(g + 1) * t], self._group_losses[g]
-            modules = dict(w.replica.module.named_modules())
-            for name, (mean, var) in self.fused.running_tables.items():
-                modules[name]._buffers["running_mean"], modules[name]._buffers["running_var"] = mean[g], var[g]
+        bounds = [G * c // chains for c in range(chains + 1)]
+        self._chains = []
+        for lo, hi in zip(bounds[:-1], bounds[1:]):
+            replica = FlatModel(copy.deepcopy(module), self.device, flat=self.flat, channels_last=self.channels_last)
+            group = GroupedWorkers(replica, [w.row for w in self.workers[lo:hi]], loss_fn)
+            stream = torch.cuda.Stream(device=self.device) if chains > 1 else None
+            self._chains.append((group, data[lo * b:hi * b], target[lo * t:hi * t], self._group_losses[lo:hi], stream))
+            for g, w in enumerate(self.workers[lo:hi]):
+                w.data, w.target, w.loss = data[(lo + g) * b:(lo + g + 1) * b], target[(lo + g) * t:(lo + g + 1) * t], self._group_losses[lo + g]
+                modules = dict(w.replica.module.named_modules())
+                for name, (mean, var) in group.running_tables.items():
+                    modules[name]._buffers["running_mean"], modules[name]._buffers["running_var"] = mean[g], var[g]
+        self.fused = self._chains[0][0]
 
     # ------------------------------------------------------------------------------------------
     @staticmethod
@@ -361,7 +368,17 @@ class SSMWEngine:
 
     def _run_workers(self):
         if self.fused is not None:
-            self.fused.forward_backward(self._group_data, self._group_target, self._group_losses)
+            if len(self._chains) == 1:
+                group, data, target, losses, _ = self._chains[0]
+                group.forward_backward(data, target, losses)
+                return
+            main = torch.cuda.current_stream(self.device)
+            for group, data, target, losses, stream in self._chains:
+                stream.wait_stream(main)
+                with torch.cuda.stream(stream):
+                    group.forward_backward(data, target, losses)
+            for chain in self._chains:
+                main.wait_stream(chain[4])
             return
         main = torch.cuda.current_stream(self.device)
         for w in self.workers:
