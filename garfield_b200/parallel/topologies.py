@@ -26,6 +26,7 @@ import torch
 import torch.distributed as dist
 
 from .arena import FlatModel
+from .grouped import GroupedWorkers
 from .peer import PeerArena
 from ..garfieldpp import tools
 from ..garfieldpp.datasets import DatasetManager
@@ -193,16 +194,30 @@ class MSMWEngine(_Base):
     computes its gradient on that model; every server aggregates all workers' gradients with the
     gradient GAR and steps; then every server replaces its model by the model GAR of all servers'
     models (double-buffered). Byzantine servers publish an attacked model instead of their own.
+
+    Worker fusion (default when the model is covered, `parallel/grouped.py`): every worker of a rank sees the same
+    published models, so the rank takes their median ONCE into a shared channels-last model and computes all its
+    workers' gradients in one CUDA-graphed pass (per-worker BatchNorm statistics, weight gradients and losses).
     """
 
     def __init__(self, model, dataset, loss, num_workers, num_ps, fw, fps, gar, batch, mar="median", optimizer="sgd", opt_args=None,
-                 byzantine_workers=None, byzantine_servers=None, device=None, group=None, seed=1234):
+                 byzantine_workers=None, byzantine_servers=None, device=None, group=None, seed=1234, fuse_workers=None,
+                 use_graphs=True):
         self._init_dist(group, device)
         self.n, self.num_ps, self.fw, self.fps = num_workers, num_ps, fw, fps
         self.gar_name, self.mar_name = gar, mar
         self.byz_w, self.byz_s = dict(byzantine_workers or {}), dict(byzantine_servers or {})
         torch.manual_seed(seed)
         module = tools.select_model(model, self.device, dataset)
+        loss_fn = tools.select_loss(loss)
+        self.fuse = (GroupedWorkers.unsupported_reason(module, loss_fn) is None) if fuse_workers is None else bool(fuse_workers)
+        self.channels_last = self.fuse          # every arena of this engine then stores 4-D parameters in OHWI order
+        if self.fuse:
+            from ..models.fused_resnet import fuse_resnet_blocks
+            from .engine import _skip_bn_counters
+            _skip_bn_counters(module)
+            fuse_resnet_blocks(module)
+            module = module.to(memory_format=torch.channels_last)
         self.d = sum(p.numel() for p in module.parameters())
         self.pitch = (self.d + 63) // 64 * 64
         self.local_workers = [w for w in range(self.n) if w % self.world == self.rank]
@@ -212,25 +227,68 @@ class MSMWEngine(_Base):
         self.grads = PeerArena(w_slots * self.pitch, self.device, group)
         self.wmodels = PeerArena(max(1, w_slots) * self.pitch, self.device, group)      # workers' private models (local use only)
         self.smodels = PeerArena(s_slots * 3 * self.pitch, self.device, group)          # per server: 2 model buffers + 1 published copy
-        init = FlatModel(module, self.device)
+        init = FlatModel(module, self.device, channels_last=self.channels_last)
+        self.layout = init                       # reference-order <-> arena-order conversions (`to_reference_order`)
         if self.world > 1:
             dist.broadcast(init.flat, src=0, group=group)
-        loss_fn = tools.select_loss(loss)
         self.cur = 0
         self.workers, self.servers = [], []
         for j, w in enumerate(self.local_workers):
-            mine = self.wmodels.local[j * self.pitch:j * self.pitch + self.d]
+            mine = self.wmodels.local[(0 if self.fuse else j) * self.pitch:(0 if self.fuse else j) * self.pitch + self.d]
             mine.copy_(init.flat)
-            replica = FlatModel(copy.deepcopy(module), self.device, flat=mine)
+            replica = FlatModel(copy.deepcopy(module), self.device, flat=mine, channels_last=self.channels_last)
             batches = DatasetManager(dataset, batch, self.n, self.n + num_ps, w + num_ps).get_train_set()
+            if self.fuse:
+                batches = [(self._host(x), y.pin_memory()) for x, y in batches]
             self.workers.append(dict(id=w, slot=j, replica=replica, batches=batches, loss_fn=loss_fn, attack=self.byz_w.get(w),
                                      loss=torch.zeros((), device=self.device)))
+        self.fused, self._graph, self._eager_passes, self.use_graphs = None, None, 0, use_graphs
+        if self.fuse and self.workers:
+            G = len(self.workers)
+            shared = FlatModel(copy.deepcopy(module), self.device, flat=self.wmodels.local[:self.d], channels_last=True)
+            self.fused = GroupedWorkers(shared, [self._grad(self.rank, wrk["slot"]) for wrk in self.workers], loss_fn)
+            x0, y0 = self.workers[0]["batches"][0]
+            self._gdata = torch.zeros((G * x0.shape[0],) + tuple(x0.shape[1:]), device=self.device)
+            if self._gdata.dim() == 4:
+                self._gdata = self._gdata.contiguous(memory_format=torch.channels_last)
+            self._gtarget = torch.zeros((G * y0.shape[0],) + tuple(y0.shape[1:]), dtype=y0.dtype, device=self.device)
+            self._glosses = torch.zeros(G, device=self.device)
+            for g, wrk in enumerate(self.workers):
+                wrk["loss"] = self._glosses[g]
+                modules = dict(wrk["replica"].module.named_modules())
+                for name, (mean, var) in self.fused.running_tables.items():
+                    modules[name]._buffers["running_mean"], modules[name]._buffers["running_var"] = mean[g], var[g]
         for j, s in enumerate(self.local_servers):
             for which in range(3):
                 self._smodel(self.rank, j, which).copy_(init.flat)
             opt = FlatOptimizer(self._smodel(self.rank, j, 0), optimizer, **(opt_args or {}))
             self.servers.append(dict(id=s, slot=j, opt=opt, attack=self.byz_s.get(s)))
         self._barrier()
+
+    @staticmethod
+    def _host(x):
+        x = x.contiguous(memory_format=torch.channels_last) if x.dim() == 4 else x.contiguous()
+        return x.pin_memory()
+
+    def _fused_pass(self, iter_num, published):
+        """Median of the published models once per rank, then all local workers' gradients in one pass."""
+        shared = self.wmodels.local[:self.d]
+        gar_ops.coordwise(published, "median_lower", out=shared) if self.num_ps > 1 else shared.copy_(published[0])
+        bx, by = self._gdata.shape[0] // len(self.workers), self._gtarget.shape[0] // len(self.workers)
+        for g, wrk in enumerate(self.workers):
+            data, target = wrk["batches"][iter_num % len(wrk["batches"])]
+            self._gdata[g * bx:(g + 1) * bx].copy_(data, non_blocking=True)
+            self._gtarget[g * by:(g + 1) * by].copy_(target, non_blocking=True)
+        if not self.use_graphs or self._eager_passes < 2:
+            self.fused.forward_backward(self._gdata, self._gtarget, self._glosses)
+            self._eager_passes += 1
+            return
+        if self._graph is None:
+            graph = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(graph):
+                self.fused.forward_backward(self._gdata, self._gtarget, self._glosses)
+            self._graph = graph
+        self._graph.replay()
 
     def _smodel(self, rank, slot, which):
         base = (slot * 3 + which) * self.pitch
@@ -256,7 +314,9 @@ class MSMWEngine(_Base):
         self._barrier()
         published = self._published()
         # 1. workers: model := median of all servers' published models (fused pull), then gradient
-        for wrk in self.workers:
+        if self.fused is not None:
+            self._fused_pass(iter_num, published)
+        for wrk in ([] if self.fused is not None else self.workers):
             mine = self.wmodels.local[wrk["slot"] * self.pitch:wrk["slot"] * self.pitch + self.d]
             gar_ops.coordwise(published, "median_lower", out=mine) if self.num_ps > 1 else mine.copy_(published[0])
             row = self._grad(self.rank, wrk["slot"])

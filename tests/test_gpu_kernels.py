@@ -236,6 +236,31 @@ def test_device_topology_engines_single_gpu():
     dec.close()
 
 
+def test_msmw_worker_fusion_matches_per_worker_path():
+    """ByzSGD engine: one fused pass for a rank's workers (shared median model, channels-last arenas, CUDA graph)
+    gives the same server models as the worker-by-worker path."""
+    import os
+    os.environ.setdefault("GARFIELD_SYNTHETIC_SIZE", "1500")
+    from garfield_b200.parallel.topologies import MSMWEngine
+    cuda_lib()
+    finals = {}
+    for fuse in (False, True):
+        eng = MSMWEngine("cnn", "synthetic-cifar10", "cross-entropy", 5, 3, 1, 1, "krum", 8, mar="median", opt_args=dict(lr=0.02, momentum=0.9),
+                         byzantine_workers={4: "reverse"}, byzantine_servers={2: "reverse"}, fuse_workers=fuse, seed=5)
+        assert (eng.fused is not None) == fuse
+        for module in [w["replica"].module for w in eng.workers] + ([eng.fused.module] if fuse else []):
+            for m in module.modules():
+                if isinstance(m, (torch.nn.Dropout, torch.nn.Dropout2d)):
+                    m.p = 0.0
+        losses = [eng.step(i).item() for i in range(4)]
+        assert all(l == l for l in losses)
+        torch.cuda.synchronize()
+        finals[fuse] = eng.layout.to_reference_order(eng.server_model(0)).clone()
+        eng.close()
+    diff = (finals[True] - finals[False]).abs()
+    assert diff.max().item() < 2e-3 and (diff > 2e-4).float().mean().item() < 1e-4, diff.max().item()
+
+
 @pytest.mark.parametrize("m,n,k", [(128, 128, 64), (25, 10, 84), (200, 120, 400), (77, 300, 1000), (512, 1024, 4096), (1000, 4096, 25088 // 8)])
 @pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
 def test_tcgen05_gemm_nt(m, n, k, dtype):
