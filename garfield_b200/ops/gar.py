@@ -152,52 +152,53 @@ def weighted(gradients, W, theta=1, **kw):
     return coordwise(gradients, "linear", W=W, theta=theta, **kw)
 
 
-def krum(gradients, f, m, neighbors, squared, update=None, want_out=True):
+def krum(gradients, f, m, neighbors, squared, update=None, want_out=True, out=None):
     ws = select(gradients, "krum", f=f, m=m, neighbors=neighbors, squared=squared)
-    return coordwise(gradients, "linear", W=ws["W"], theta=1, update=update, want_out=want_out)
+    return coordwise(gradients, "linear", W=ws["W"], theta=1, update=update, want_out=want_out, out=out)
 
 
-def bulyan(gradients, f, m=None, native=False, update=None, want_out=True):
+def bulyan(gradients, f, m=None, native=False, update=None, want_out=True, out=None):
     n = len(gradients)
     m = n - f - 2 if m is None else m
     theta = n - 2 * f - 2
     ws = select(gradients, "bulyan_native" if native else "bulyan_python", f=f, m=m, squared=native)
     return coordwise(gradients, "averaged_median", beta=theta - 2 * f, upper=native, W=ws["W"], theta=theta,
-                     update=update, want_out=want_out)
+                     update=update, want_out=want_out, out=out)
 
 
-def mda(gradients, f, squared=False, update=None, want_out=True):
+def mda(gradients, f, squared=False, update=None, want_out=True, out=None):
     ws = select(gradients, "mda", f=f, squared=squared)
-    return coordwise(gradients, "linear", W=ws["W"], theta=1, update=update, want_out=want_out)
+    return coordwise(gradients, "linear", W=ws["W"], theta=1, update=update, want_out=want_out, out=out)
 
 
-def aksel(gradients, c, update=None, want_out=True):
+def aksel(gradients, c, update=None, want_out=True, out=None):
     med = coordwise(gradients, "median_lower")
     ws = select(list(gradients) + [med], "closest", m=c, squared=True)
     # W has n+1 columns (last = the median row, weight 0): reuse it on the extended row list
-    return coordwise(list(gradients) + [med], "linear", W=ws["W"], theta=1, update=update, want_out=want_out)
+    return coordwise(list(gradients) + [med], "linear", W=ws["W"], theta=1, update=update, want_out=want_out, out=out)
 
 
 _uniform = {}
 
 
-def average(gradients, update=None, want_out=True):
+def average(gradients, update=None, want_out=True, out=None):
     n = len(gradients)
     device = gradients[0].device
     key = (device, n)
     if key not in _uniform:
         _uniform[key] = torch.full((1, n), 1.0 / n, dtype=torch.float32, device=device)
-    return coordwise(gradients, "linear", W=_uniform[key], theta=1, update=update, want_out=want_out)
+    return coordwise(gradients, "linear", W=_uniform[key], theta=1, update=update, want_out=want_out, out=out)
 
 
-def aggregate(name, gradients, f, m=None, update=None, want_out=True, **kw):
+def aggregate(name, gradients, f, m=None, update=None, want_out=True, out=None, **kw):
     """Run the registry rule `name` on device rows with an optional fused SGD epilogue.
 
     Same semantics as `aggregators.gars[name](gradients=..., f=...)` on CUDA tensors; the fused
     form additionally applies the optimizer step and publishes the parameters in the same pass.
+    `out`: write the aggregate into this d-length tensor (it must not alias an input row).
     """
     n = len(gradients)
-    common = dict(update=update, want_out=want_out)
+    common = dict(update=update, want_out=want_out, out=out)
     if name == "average":
         return average(gradients, **common)
     if name == "median":
@@ -245,7 +246,7 @@ _DISTANCE_RULES = {
 }
 
 
-def aggregate_sharded(name, slice_rows, f, allreduce, m=None, update=None, want_out=True, **kw):
+def aggregate_sharded(name, slice_rows, f, allreduce, m=None, update=None, want_out=True, out=None, **kw):
     """Coordinate-sharded form of `aggregate`: `slice_rows` are this rank's coordinate slice of the
     n gradients; `allreduce(tensor)` sums a small device tensor over the ranks in place.
 
@@ -253,7 +254,7 @@ def aggregate_sharded(name, slice_rows, f, allreduce, m=None, update=None, want_
     distances of the slice, all-reduce the n×n matrix, run the (replicated) selection and apply the
     resulting weights to the slice — the robust analogue of a reduce-scatter."""
     n = len(slice_rows)
-    common = dict(update=update, want_out=want_out)
+    common = dict(update=update, want_out=want_out, out=out)
     if name == "aksel":
         med = coordwise(slice_rows, "median_lower")
         rows = list(slice_rows) + [med]

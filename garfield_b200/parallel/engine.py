@@ -213,6 +213,8 @@ class SSMWEngine:
                 batches = train_set(wid)
             else:
                 batches = DatasetManager(dataset, batch, self.n, self.n + 1, wid + 1).get_train_set()
+            # static device buffers / CUDA graphs need one batch shape: a shorter tail batch of the partition is skipped
+            batches = [b for b in batches if b[0].shape[0] == batches[0][0].shape[0]]
             if self.channels_last and batches[0][0].dim() == 4:  # host batches in NHWC so the H2D copy is a plain memcpy
                 batches = [(self._pin(x.contiguous(memory_format=torch.channels_last)), y) for x, y in batches]
             self.train_sets[wid] = batches

@@ -78,12 +78,24 @@ class DecentralizedEngine(_Base):
     """
 
     def __init__(self, model, dataset, loss, num_nodes, f, gar, batch, optimizer="sgd", opt_args=None, byzantine=None,
-                 non_iid=False, device=None, group=None, seed=1234):
+                 non_iid=False, device=None, group=None, seed=1234, fuse_workers=None, use_graphs=True):
         self._init_dist(group, device)
         self.n, self.f, self.gar_name, self.non_iid = num_nodes, f, gar, non_iid
         self.byzantine = dict(byzantine or {})
         torch.manual_seed(seed)
         module = tools.select_model(model, self.device, dataset)
+        loss_fn = tools.select_loss(loss)
+        # Worker fusion: the contract step leaves every node with the SAME model (each node runs the same deterministic
+        # kernel over the same row table), so a rank computes the gradients of all its nodes in one pass on a copy of
+        # its first node's live model (per-node BatchNorm statistics, weight gradients and losses).
+        self.fuse = (GroupedWorkers.unsupported_reason(module, loss_fn) is None) if fuse_workers is None else bool(fuse_workers)
+        self.channels_last = self.fuse
+        if self.fuse:
+            from ..models.fused_resnet import fuse_resnet_blocks
+            from .engine import _skip_bn_counters
+            _skip_bn_counters(module)
+            fuse_resnet_blocks(module)
+            module = module.to(memory_format=torch.channels_last)
         self.d = sum(p.numel() for p in module.parameters())
         self.pitch = (self.d + 63) // 64 * 64
         self.local_ids = [k for k in range(self.n) if k % self.world == self.rank]
@@ -93,22 +105,60 @@ class DecentralizedEngine(_Base):
         self.params = PeerArena(slots * 2 * self.pitch, self.device, group)
         self.grads = PeerArena(slots * self.pitch, self.device, group)
         self.aggrs = PeerArena(slots * 2 * self.pitch, self.device, group)
-        init = FlatModel(module, self.device)
+        init = FlatModel(module, self.device, channels_last=self.channels_last)
+        self.layout = init
         if self.world > 1:
             dist.broadcast(init.flat, src=0, group=group)
         self.cur = 0            # which parameter buffer is live
-        loss_fn = tools.select_loss(loss)
         self.nodes = []
         for j, k in enumerate(self.local_ids):
             live = self._param(self.rank, j, 0)
             live.copy_(init.flat)
             self._param(self.rank, j, 1).copy_(init.flat)
-            replica = FlatModel(copy.deepcopy(module), self.device, flat=live)
+            replica = FlatModel(copy.deepcopy(module), self.device, flat=live, channels_last=self.channels_last)
             batches = DatasetManager(dataset, batch, self.n, self.n, k).get_train_set()
+            if self.fuse:   # static buffers: skip a shorter tail batch
+                batches = [(MSMWEngine._host(x), y.pin_memory()) for x, y in batches if x.shape[0] == batches[0][0].shape[0]]
             opt = FlatOptimizer(live, optimizer, **(opt_args or {}))
             self.nodes.append(dict(id=k, slot=j, replica=replica, batches=batches, opt=opt, loss_fn=loss_fn,
                                    attack=self.byzantine.get(k), loss=torch.zeros((), device=self.device)))
+        self.fused, self._graph, self._eager_passes, self.use_graphs = None, None, 0, use_graphs
+        if self.fuse and self.nodes:
+            G = len(self.nodes)
+            self._wmodel = torch.empty(self.d, device=self.device)          # static copy of the rank's live model for the graphed pass
+            self._wmodel.copy_(init.flat)
+            shared = FlatModel(copy.deepcopy(module), self.device, flat=self._wmodel, channels_last=True)
+            self.fused = GroupedWorkers(shared, [self._grad(self.rank, node["slot"]) for node in self.nodes], loss_fn)
+            x0, y0 = self.nodes[0]["batches"][0]
+            self._gdata = torch.zeros((G * x0.shape[0],) + tuple(x0.shape[1:]), device=self.device)
+            if self._gdata.dim() == 4:
+                self._gdata = self._gdata.contiguous(memory_format=torch.channels_last)
+            self._gtarget = torch.zeros((G * y0.shape[0],) + tuple(y0.shape[1:]), dtype=y0.dtype, device=self.device)
+            self._glosses = torch.zeros(G, device=self.device)
+            for g, node in enumerate(self.nodes):
+                node["loss"] = self._glosses[g]
+                modules = dict(node["replica"].module.named_modules())
+                for name, (mean, var) in self.fused.running_tables.items():
+                    modules[name]._buffers["running_mean"], modules[name]._buffers["running_var"] = mean[g], var[g]
         self.steps_done = 0
+
+    def _fused_pass(self, iter_num):
+        self._wmodel.copy_(self._param(self.rank, self.nodes[0]["slot"], self.cur))
+        bx, by = self._gdata.shape[0] // len(self.nodes), self._gtarget.shape[0] // len(self.nodes)
+        for g, node in enumerate(self.nodes):
+            data, target = node["batches"][iter_num % len(node["batches"])]
+            self._gdata[g * bx:(g + 1) * bx].copy_(data, non_blocking=True)
+            self._gtarget[g * by:(g + 1) * by].copy_(target, non_blocking=True)
+        if not self.use_graphs or self._eager_passes < 2:
+            self.fused.forward_backward(self._gdata, self._gtarget, self._glosses)
+            self._eager_passes += 1
+            return
+        if self._graph is None:
+            graph = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(graph):
+                self.fused.forward_backward(self._gdata, self._gtarget, self._glosses)
+            self._graph = graph
+        self._graph.replay()
 
     # arena views -----------------------------------------------------------------------------
     def _param(self, rank, slot, which):
@@ -133,7 +183,9 @@ class DecentralizedEngine(_Base):
     def step(self, iter_num):
         n, f = self.n, self.f
         # 1. local gradients (on each node's own live model)
-        for node in self.nodes:
+        if self.fused is not None:
+            self._fused_pass(iter_num)
+        for node in ([] if self.fused is not None else self.nodes):
             row = self._grad(self.rank, node["slot"])
             replica = node["replica"]
             row.zero_()
@@ -153,29 +205,34 @@ class DecentralizedEngine(_Base):
         rounds = int(math.ceil(math.log2(iter_num + 1))) if (self.non_iid and iter_num > 0) else 0
         rows = self._all(self._grad)
         which = 0
+        fused_sgd = rounds == 0 and all(node["opt"].name == "sgd" for node in self.nodes)
         for node in self.nodes:
-            out = self._aggr(self.rank, node["slot"], which)
-            out.copy_(gar_ops.aggregate(self.gar_name, rows, f))
+            if fused_sgd:    # no agreement rounds: the SGD step rides in the epilogue of the aggregation pass
+                gar_ops.aggregate(self.gar_name, rows, f, update=node["opt"].sgd_fusion(), want_out=False)
+                node["opt"].note_fused_step()
+            else:
+                gar_ops.aggregate(self.gar_name, rows, f, out=self._aggr(self.rank, node["slot"], which))
         # 3. agreement rounds on the aggregated gradients (double-buffered)
         for _ in range(rounds):
             self._barrier()
             peers = self._all(self._aggr, which)
             for node in self.nodes:
-                self._aggr(self.rank, node["slot"], 1 - which).copy_(gar_ops.aggregate(self.gar_name, peers, f))
+                gar_ops.aggregate(self.gar_name, peers, f, out=self._aggr(self.rank, node["slot"], 1 - which))
             which = 1 - which
         # 4. optimizer step on each node's live model
-        for node in self.nodes:
+        for node in ([] if fused_sgd else self.nodes):
             node["opt"].step(self._aggr(self.rank, node["slot"], which))
         self._barrier()
         # 5. contract: model := GAR(all nodes' live models), written into the other buffer
         models = self._all(self._param, self.cur)
         for node in self.nodes:
-            self._param(self.rank, node["slot"], 1 - self.cur).copy_(gar_ops.aggregate(self.gar_name, models, f))
+            gar_ops.aggregate(self.gar_name, models, f, out=self._param(self.rank, node["slot"], 1 - self.cur))
         self._barrier()
         self.cur = 1 - self.cur
         for node in self.nodes:  # re-alias replicas and optimizers onto the now-live buffer
             live = self._param(self.rank, node["slot"], self.cur)
-            node["replica"] = FlatModel(node["replica"].module, self.device, flat=live)
+            if self.fused is None:
+                node["replica"] = FlatModel(node["replica"].module, self.device, flat=live)
             node["opt"].rebind(live)
         self.steps_done += 1
         return torch.stack([node["loss"] for node in self.nodes]).mean() if self.nodes else torch.zeros((), device=self.device)
@@ -238,8 +295,8 @@ class MSMWEngine(_Base):
             mine.copy_(init.flat)
             replica = FlatModel(copy.deepcopy(module), self.device, flat=mine, channels_last=self.channels_last)
             batches = DatasetManager(dataset, batch, self.n, self.n + num_ps, w + num_ps).get_train_set()
-            if self.fuse:
-                batches = [(self._host(x), y.pin_memory()) for x, y in batches]
+            if self.fuse:   # static buffers: skip a shorter tail batch
+                batches = [(self._host(x), y.pin_memory()) for x, y in batches if x.shape[0] == batches[0][0].shape[0]]
             self.workers.append(dict(id=w, slot=j, replica=replica, batches=batches, loss_fn=loss_fn, attack=self.byz_w.get(w),
                                      loss=torch.zeros((), device=self.device)))
         self.fused, self._graph, self._eager_passes, self.use_graphs = None, None, 0, use_graphs
@@ -354,7 +411,7 @@ class MSMWEngine(_Base):
                 if self.mar_name in ("vanilla", "crash"):
                     nxt.copy_(torch.stack(published).mean(0) if self.mar_name == "vanilla" else published[0])
                 else:
-                    nxt.copy_(gar_ops.aggregate(self.mar_name, published, self.fps))
+                    gar_ops.aggregate(self.mar_name, published, self.fps, out=nxt)
             self._barrier()
             self.cur = 1 - self.cur
             for srv in self.servers:

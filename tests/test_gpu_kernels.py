@@ -261,6 +261,30 @@ def test_msmw_worker_fusion_matches_per_worker_path():
     assert diff.max().item() < 2e-3 and (diff > 2e-4).float().mean().item() < 1e-4, diff.max().item()
 
 
+def test_decentralized_worker_fusion_matches_per_node_path():
+    import os
+    os.environ.setdefault("GARFIELD_SYNTHETIC_SIZE", "1500")
+    from garfield_b200.parallel.topologies import DecentralizedEngine
+    cuda_lib()
+    finals = {}
+    for fuse in (False, True):
+        eng = DecentralizedEngine("cnn", "synthetic-cifar10", "cross-entropy", 6, 1, "median", 8, opt_args=dict(lr=0.02, momentum=0.9),
+                                  byzantine={5: "reverse"}, non_iid=True, fuse_workers=fuse, seed=7)
+        assert (eng.fused is not None) == fuse
+        for module in [node["replica"].module for node in eng.nodes] + ([eng.fused.module] if fuse else []):
+            for m in module.modules():
+                if isinstance(m, (torch.nn.Dropout, torch.nn.Dropout2d)):
+                    m.p = 0.0
+        losses = [eng.step(i).item() for i in range(4)]
+        assert all(l == l for l in losses)
+        torch.cuda.synchronize()
+        finals[fuse] = eng.layout.to_reference_order(eng.model_of(0)).clone()
+        torch.testing.assert_close(eng.model_of(0), eng.model_of(1))
+        eng.close()
+    diff = (finals[True] - finals[False]).abs()
+    assert diff.max().item() < 2e-3 and (diff > 2e-4).float().mean().item() < 1e-3, diff.max().item()
+
+
 @pytest.mark.parametrize("m,n,k", [(128, 128, 64), (25, 10, 84), (200, 120, 400), (77, 300, 1000), (512, 1024, 4096), (1000, 4096, 25088 // 8)])
 @pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
 def test_tcgen05_gemm_nt(m, n, k, dtype):
