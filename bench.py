@@ -48,7 +48,7 @@ def parse_args(argv=None):
     ap.add_argument("--also", default="median,bulyan", help="other rules reported under per_gar ('' to skip)")
     ap.add_argument("--no-graphs", action="store_true")
     ap.add_argument("--fuse-workers", default="auto", choices=["auto", "on", "off"],
-                    help="one batched forward/backward for the workers hosted by a GPU (auto: when a rank hosts >= 2 workers)")
+                    help="one batched forward/backward for the workers hosted by a GPU (auto: whenever the model is covered)")
     ap.add_argument("--fusion-chains", type=int, default=1, help="split a rank's fused workers into this many concurrent passes")
     ap.add_argument("--sync", default="nccl", choices=["nccl", "flags"], help="inter-rank synchronisation (N > 1)")
     return ap.parse_args(argv)

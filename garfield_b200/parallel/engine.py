@@ -226,8 +226,8 @@ class SSMWEngine:
         # worker fusion: the co-located workers share ONE forward/backward pass (parallel/grouped.py) when every
         # layer of the model is covered; otherwise each worker keeps its own chain and stream
         self.fused = None
-        if fuse_workers is None:
-            fuse_workers = len(self.workers) >= 2 and gather_grads
+        if fuse_workers is None:     # also pays for a single hosted worker (in-place weight-gradient GEMMs, no gather copy)
+            fuse_workers = len(self.workers) >= 1 and gather_grads
         if fuse_workers and self.workers and GroupedWorkers.unsupported_reason(module, loss_fn) is None:
             self._fuse_workers(module, loss_fn, max(1, min(int(fusion_chains), len(self.workers))))
 
