@@ -23,6 +23,7 @@
 #include <string>
 #include <vector>
 
+#include "strided_view.hpp"
 #include "combinations.hpp"
 #include "garfield_b200.h"
 #include "threadpool.hpp"
@@ -207,7 +208,6 @@ int bulyan(T const* const* in, int n, std::int64_t d, int f, int m, T* out) {
     std::size_t const blocks = (static_cast<std::size_t>(d) + kBlock - 1) / kBlock;
     gb::parallel_for(0, blocks, [&](std::size_t lo, std::size_t hi) {
         std::vector<T> tile(static_cast<std::size_t>(theta) * kBlock);
-        std::vector<T> column(theta);
         for (std::size_t b = lo; b < hi; ++b) {
             std::size_t const x0 = b * kBlock;
             std::size_t const len = std::min<std::size_t>(static_cast<std::size_t>(d), x0 + kBlock) - x0;
@@ -221,15 +221,17 @@ int bulyan(T const* const* in, int n, std::int64_t d, int f, int m, T* out) {
                     for (std::size_t x = 0; x < len; ++x) row[x] += g[x] * w;
                 }
             }
+            // order statistics run in place along the (strided) θ axis of the tile — no per-coordinate gather
+            gb::StridedView<T> const rounds(tile.data(), {static_cast<std::size_t>(theta), kBlock});
             for (std::size_t x = 0; x < len; ++x) {
-                for (int k = 0; k < theta; ++k) column[k] = tile[static_cast<std::size_t>(k) * kBlock + x];
+                auto const column = rounds.at(1, x).line(0);
                 std::nth_element(column.begin(), column.begin() + theta / 2, column.end());
-                T const med = column[theta / 2];
+                T const med = column.begin()[theta / 2];
                 std::nth_element(column.begin(), column.begin() + (beta - 1), column.end(), [&](T a, T c) {
                     return std::fabs(a - med) < std::fabs(c - med);
                 });
                 T sum = 0;
-                for (int k = 0; k < beta; ++k) sum += column[k];
+                for (int k = 0; k < beta; ++k) sum += column.begin()[k];
                 out[x0 + x] = sum / static_cast<T>(beta);
             }
         }
@@ -376,3 +378,34 @@ GB_API int gb_cpu_parallel_for_probe(int64_t total, int64_t grain, int32_t* hits
 }
 
 }  // extern "C"
+
+
+// k-th smallest along `axis` of a row-major array (in place, like std::nth_element), one result per line:
+// exercises gb::StridedView / StrideIterator (role of the reference's include/array.hpp) through the C ABI.
+extern "C" GB_API int gb_cpu_axis_nth_f32(float* data, int rank, int64_t const* shape, int axis, int64_t k, float* out) {
+    if (rank < 1 || rank > gb::StridedView<float>::kMaxRank || axis < 0 || axis >= rank) return fail("axis_nth: rank must be 1..4 and axis inside it");
+    std::size_t dims[4] = {1, 1, 1, 1};
+    std::size_t lines = 1;
+    for (int a = 0; a < rank; ++a) {
+        if (shape[a] < 1) return fail("axis_nth: empty dimension");
+        dims[a] = static_cast<std::size_t>(shape[a]);
+        if (a != axis) lines *= dims[a];
+    }
+    if (k < 0 || k >= shape[axis]) return fail("axis_nth: k outside the axis");
+    gb::StridedView<float> const view(data, rank, dims);
+    gb::parallel_for(0, lines, [&](std::size_t lo, std::size_t hi) {
+        for (std::size_t line = lo; line < hi; ++line) {
+            gb::StridedView<float> v = view;     // fix every other axis, last to first, so earlier positions stay valid
+            std::size_t rest = line;
+            for (int a = rank - 1; a >= 0; --a) {
+                if (a == axis) continue;
+                v = v.at(a, rest % dims[a]);
+                rest /= dims[a];
+            }
+            auto const range = v.line(0);        // the only axis left is `axis`
+            std::nth_element(range.begin(), range.begin() + k, range.end());
+            out[line] = range.begin()[k];
+        }
+    });
+    return 0;
+}

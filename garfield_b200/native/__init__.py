@@ -67,6 +67,7 @@ def _declare(h):
     h.gb_combinations_seek.argtypes = [ctypes.c_uint, ctypes.c_uint, ctypes.c_uint64, ctypes.POINTER(ctypes.c_int)]
     h.gb_combinations_next.argtypes = [ctypes.c_uint, ctypes.c_uint, ctypes.POINTER(ctypes.c_int)]
     h.gb_cpu_parallel_for_probe.argtypes = [i64, i64, vp]
+    h.gb_cpu_axis_nth_f32.argtypes = [vp, i32, ctypes.POINTER(ctypes.c_int64), i32, i64, vp]
     h.gb_mreg_create.restype = vp
     h.gb_mreg_create.argtypes = [i32, i64, i32]
     h.gb_mreg_close.argtypes = [vp]

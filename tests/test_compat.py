@@ -111,3 +111,59 @@ def test_tf_style_pull_deployment_in_threads():
     assert len(ps.servicer.model_history) == 4 and np.isfinite(ps.flat()).all()
     for node in results.values():
         node.stop()
+
+
+def test_legacy_train_message_exchange_in_process_and_grpc():
+    """Garfield_legacy/all.proto: every declared RPC answers; hashes and signatures verify; pulls block until published."""
+    import threading
+    import numpy as np
+    from garfield_b200.compat import legacy_exchange as lx
+    node = lx.TrainMessageExchangeServicer(index=3, secret=b"node-3", timeout=5.0)
+    model = np.arange(10, dtype=np.float32)
+    grad = np.linspace(-1, 1, 10).astype(np.float32)
+    threading.Timer(0.05, lambda: node.publish_model(2, model, inputs=np.ones((2, 3), np.float32), labels=np.array([1, 0]), correct=[0, 2])).start()
+    threading.Timer(0.05, lambda: node.publish_gradient(2, grad, lipschitz=0.25)).start()
+    server = lx.serve_legacy(node, 0)
+    try:
+        for client in (lx.LegacyClient(node), lx.LegacyClient("127.0.0.1:%d" % server.bound_port)):
+            index, pub = client.get_public_key()
+            assert index == 3 and len(pub) == 32
+            it, got = client.get_model(2)
+            assert it == 2 and np.array_equal(got, model)
+            assert np.array_equal(client.get_unified_model()[1], model)
+            full = client.get_complete_model(1)
+            assert full["iter"] == 2 and full["correct"] == [0, 2] and full["msg_hash"] == lx.model_hash(model)
+            assert lx.Signer.verify(pub, full["msg_hash"], full["signature"])
+            assert not lx.Signer.verify(pub, lx.model_hash(model + 1), full["signature"])
+            _, digest, sig = client.get_only_hash(2)
+            assert digest == lx.model_hash(model) and lx.Signer.verify(pub, digest, sig)
+            it, g, lip = client.get_gradients(2)
+            assert it == 2 and np.array_equal(g, grad) and abs(lip - 0.25) < 1e-7
+            assert client.get_grad_hash(2) == (3, lx.model_hash(grad))
+            node.record_peer_hash(2, 5, b"\\x01" * 32)
+            hashes = client.get_grad_hashes(2)
+            assert hashes[3] == lx.model_hash(grad) and 5 in hashes
+            client.close()
+    finally:
+        server.stop(0)
+
+
+def test_legacy_lipschitz_filter_and_update_model():
+    import numpy as np
+    import torch
+    from garfield_b200.compat import legacy_exchange as lx
+    flt = lx.LipschitzFilter(num_ps=4, num_byzps=1)
+    rng = np.random.default_rng(0)
+    for _ in range(120):
+        ok, bound = flt.observe(abs(rng.normal()) + 0.1)
+        assert bound > 0
+    assert len(flt.history) <= 100
+    assert flt.observe(1e9)[0] is False and flt.observe(0.0)[0] is True
+    x0, x1 = np.zeros(4), np.array([3.0, 4.0, 0.0, 0.0])
+    g0, g1 = np.zeros(4), np.array([0.0, 0.0, 6.0, 8.0])
+    assert abs(lx.LipschitzFilter.coefficient(g1, g0, x1, x0) - 2.0) < 1e-12
+    assert lx.drift_bound(0.1, 2.0, 10, 8, 2, 5) == 0.1 * 2.0 * ((32 * 6) / 8.0 + 8)
+    assert lx.drift_bound(0.1, 2.0, 10, 8, 0, 5) == float("inf")
+    m, g = np.ones(5, np.float32), np.full(5, 2.0, np.float32)
+    assert np.allclose(lx.update_model(m, g), 0.8)
+    assert torch.allclose(lx.update_model(torch.ones(5), torch.full((5,), 2.0)), torch.full((5,), 0.8))

@@ -95,6 +95,24 @@ def test_parallel_for_covers_range_exactly_once(total, grain):
     assert bool((hits == 1).all())
 
 
+@pytest.mark.parametrize("shape,axis", [((7,), 0), ((5, 9), 0), ((5, 9), 1), ((4, 6, 3), 1), ((3, 4, 5, 6), 2), ((3, 4, 5, 6), 0)])
+def test_strided_view_axis_nth_matches_sort(shape, axis):
+    """std::nth_element over the strided iterator (csrc/cpu/strided_view.hpp) along any axis, in place."""
+    import ctypes
+    torch.manual_seed(sum(shape) + axis)
+    data = torch.randn(*shape)
+    k = shape[axis] // 2
+    want = data.sort(dim=axis).values.select(axis, k).reshape(-1)
+    work = data.clone()
+    out = torch.empty(want.numel())
+    dims = (ctypes.c_int64 * len(shape))(*shape)
+    assert native.lib().gb_cpu_axis_nth_f32(work.data_ptr(), len(shape), dims, axis, k, out.data_ptr()) == 0
+    assert torch.equal(out, want)
+    assert torch.equal(work.sort(dim=axis).values, data.sort(dim=axis).values)   # a permutation along the axis only
+    assert torch.equal(work.select(axis, k).reshape(-1), want)                   # k-th element in place
+    assert native.lib().gb_cpu_axis_nth_f32(work.data_ptr(), len(shape), dims, len(shape), k, out.data_ptr()) != 0
+
+
 def test_multiregister_latest_value_and_close():
     reg = MultiRegister(3, 16)
     out = torch.zeros(4)
