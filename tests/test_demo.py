@@ -41,3 +41,19 @@ def test_demo_http_roundtrip():
             assert err.code == 400
     finally:
         server.shutdown()
+
+
+def test_playground_scripts_run(tmp_path):
+    """rsrcs/playgrounds counterparts: the random-attack Aggregathor variant and the centralized tutorial loop."""
+    import os
+    import subprocess
+    import sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    env = dict(os.environ, GARFIELD_SYNTHETIC_SIZE="400", CUDA_VISIBLE_DEVICES="")
+    out = subprocess.run([sys.executable, os.path.join(root, "applications/playgrounds/centralized/cifar10.py"), "--dataset", "synthetic-cifar10",
+                          "--epochs", "1", "--batch", "50", "--max_steps", "3"], env=env, capture_output=True, text=True, timeout=240)
+    assert out.returncode == 0 and "test accuracy" in out.stdout, out.stderr[-800:]
+    out = subprocess.run([sys.executable, os.path.join(root, "applications/playgrounds/trainer.py"), "--dataset", "synthetic-mnist", "--model", "convnet",
+                          "--num_workers", "7", "--fw", "1", "--gar", "krum", "--num_iter", "4", "--acc_freq", "2", "--batch", "16"],
+                         env=env, capture_output=True, text=True, timeout=240)
+    assert out.returncode == 0, out.stderr[-800:]
