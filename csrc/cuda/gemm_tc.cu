@@ -4,6 +4,9 @@
 // epilogue with fused bias / ReLU. Warp-specialised: warp 0 = TMA producer, warp 1 = MMA issuer
 // (one elected thread), warps 2-5 = epilogue (one TMEM lane quadrant each).
 //
+// The launched kernel is the persistent, double-buffered form further down (`gemm_tc_persistent_kernel`); the
+// one-tile-per-CTA kernel is kept as the readable reference of the pipeline.
+//
 // This is the framework's own GEMM for nn.Linear forward / dgrad / wgrad (the reference relies on
 // cuBLAS through ATen: garfieldpp/models/nets.py:47-57, 68-77). Both operands are
 // K-major ("NT"), which is nn.Linear's natural layout: y = x[M,K] · W[N,K]ᵀ.
@@ -127,6 +130,146 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
     if (warp == 1) ptx::tmem_dealloc<BN>(tmem);
 }
 
+// Persistent form: one CTA per SM walks the tile list; TMEM holds TWO accumulators (2·BN columns) so the epilogue of
+// tile j (tcgen05.ld → bias/ReLU → global stores) overlaps the TMA + MMA main loop of tile j+1. The smem ring runs on
+// across tile boundaries. Consecutive CTAs take tiles that share the same B tile (column-major rasterisation), so a
+// wave reads each B tile once from L2.
+struct GemmSharedP {
+    uint64_t full[kGemmStages];
+    uint64_t empty[kGemmStages];
+    uint64_t acc_full[2];
+    uint64_t acc_empty[2];
+    uint32_t tmem_base;
+};
+
+template <int BN, bool TF32>
+__global__ void __launch_bounds__(kGemmThreads, 1)
+gemm_tc_persistent_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b, float* __restrict__ C,
+                          const float* __restrict__ bias, int M, int N, int K, long long ldc, int relu, int tiles_m, int tiles_n) {
+    extern __shared__ __align__(1024) unsigned char smem_raw[];
+    __shared__ GemmSharedP sh;
+    constexpr uint32_t kABytes = kBM * kRowBytes, kBBytes = BN * kRowBytes, kStageBytes = kABytes + kBBytes;
+    constexpr int kElemsPerStage = TF32 ? 32 : 64;
+    int const warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    int const k_steps = (K + kElemsPerStage - 1) / kElemsPerStage;
+    int const total = tiles_m * tiles_n;
+
+    if (threadIdx.x == 0) {
+        for (int s = 0; s < kGemmStages; ++s) {
+            ptx::mbar_init(&sh.full[s], 1);
+            ptx::mbar_init(&sh.empty[s], 1);
+        }
+        for (int b = 0; b < 2; ++b) {
+            ptx::mbar_init(&sh.acc_full[b], 1);
+            ptx::mbar_init(&sh.acc_empty[b], 4);     // one arrival per epilogue warp
+        }
+        ptx::fence_mbar_init();
+        ptx::prefetch_tensormap(&map_a);
+        ptx::prefetch_tensormap(&map_b);
+    }
+    if (warp == 1) ptx::tmem_alloc<2 * BN>(&sh.tmem_base);
+    ptx::tc_fence_before();
+    __syncthreads();
+    ptx::tc_fence_after();
+    uint32_t const tmem = sh.tmem_base;
+
+    if (warp == 0) {
+        if (ptx::elect_one()) {
+            int it = 0;
+            for (int t = blockIdx.x; t < total; t += gridDim.x) {
+                int const tile_m = t % tiles_m, tile_n = t / tiles_m;
+                for (int kk = 0; kk < k_steps; ++kk, ++it) {
+                    int const s = it % kGemmStages;
+                    uint32_t const phase = static_cast<uint32_t>((it / kGemmStages) & 1);
+                    ptx::mbar_wait(&sh.empty[s], phase ^ 1u);
+                    ptx::mbar_arrive_expect_tx(&sh.full[s], kStageBytes);
+                    unsigned char* dst = smem_raw + static_cast<size_t>(s) * kStageBytes;
+                    ptx::tma_load_2d(dst, &map_a, kk * kElemsPerStage, tile_m * kBM, &sh.full[s]);
+                    ptx::tma_load_2d(dst + kABytes, &map_b, kk * kElemsPerStage, tile_n * BN, &sh.full[s]);
+                }
+            }
+        }
+    } else if (warp == 1) {
+        if (ptx::elect_one()) {
+            uint32_t const idesc = TF32 ? ptx::make_idesc(2u, 2u, kBM, BN) : ptx::make_idesc(1u, 1u, kBM, BN);
+            int it = 0, j = 0;
+            for (int t = blockIdx.x; t < total; t += gridDim.x, ++j) {
+                int const buf = j & 1;
+                ptx::mbar_wait(&sh.acc_empty[buf], static_cast<uint32_t>(((j >> 1) & 1) ^ 1));   // epilogue drained this accumulator
+                ptx::tc_fence_after();
+                uint32_t const acc = tmem + static_cast<uint32_t>(buf * BN);
+                for (int kk = 0; kk < k_steps; ++kk, ++it) {
+                    int const s = it % kGemmStages;
+                    uint32_t const phase = static_cast<uint32_t>((it / kGemmStages) & 1);
+                    ptx::mbar_wait(&sh.full[s], phase);
+                    ptx::tc_fence_after();
+                    uint32_t const a_base = ptx::smem_u32(smem_raw + static_cast<size_t>(s) * kStageBytes);
+                    uint32_t const b_base = a_base + kABytes;
+#pragma unroll
+                    for (int k = 0; k < 4; ++k) {
+                        uint64_t const adesc = ptx::make_smem_desc(a_base + k * 32u, 16u, 1024u, 2u);
+                        uint64_t const bdesc = ptx::make_smem_desc(b_base + k * 32u, 16u, 1024u, 2u);
+                        if (TF32) ptx::mma_tf32_ss(acc, adesc, bdesc, idesc, (kk > 0 || k > 0) ? 1u : 0u);
+                        else ptx::mma_f16_ss(acc, adesc, bdesc, idesc, (kk > 0 || k > 0) ? 1u : 0u);
+                    }
+                    ptx::mma_commit(&sh.empty[s]);
+                }
+                ptx::mma_commit(&sh.acc_full[buf]);
+            }
+        }
+    } else {
+        int const quad = warp & 3;
+        int j = 0;
+        for (int t = blockIdx.x; t < total; t += gridDim.x, ++j) {
+            int const tile_m = t % tiles_m, tile_n = t / tiles_m;
+            int const buf = j & 1;
+            int const row = tile_m * kBM + quad * 32 + lane;
+            ptx::mbar_wait(&sh.acc_full[buf], static_cast<uint32_t>((j >> 1) & 1));
+            ptx::tc_fence_after();
+            uint32_t const acc = tmem + static_cast<uint32_t>(buf * BN) + (static_cast<uint32_t>(quad * 32) << 16);
+#pragma unroll 1
+            for (int c0 = 0; c0 < BN; c0 += 32) {
+                uint32_t v[32];
+                ptx::tmem_ld_32x32b_x16(acc + static_cast<uint32_t>(c0), reinterpret_cast<uint32_t(&)[16]>(v[0]));
+                ptx::tmem_ld_32x32b_x16(acc + static_cast<uint32_t>(c0 + 16), reinterpret_cast<uint32_t(&)[16]>(v[16]));
+                ptx::tmem_ld_wait();
+                int const col0 = tile_n * BN + c0;
+                if (row < M && col0 < N) {
+                    float* out = C + static_cast<long long>(row) * ldc + col0;
+                    if (col0 + 32 <= N && (reinterpret_cast<uintptr_t>(out) & 15u) == 0) {
+#pragma unroll
+                        for (int q = 0; q < 8; ++q) {
+                            float4 o = make_float4(__uint_as_float(v[4 * q]), __uint_as_float(v[4 * q + 1]), __uint_as_float(v[4 * q + 2]),
+                                                   __uint_as_float(v[4 * q + 3]));
+                            if (bias != nullptr) {
+                                o.x += bias[col0 + 4 * q]; o.y += bias[col0 + 4 * q + 1]; o.z += bias[col0 + 4 * q + 2]; o.w += bias[col0 + 4 * q + 3];
+                            }
+                            if (relu) { o.x = fmaxf(o.x, 0.f); o.y = fmaxf(o.y, 0.f); o.z = fmaxf(o.z, 0.f); o.w = fmaxf(o.w, 0.f); }
+                            *reinterpret_cast<float4*>(out + 4 * q) = o;
+                        }
+                    } else {
+#pragma unroll
+                        for (int jj = 0; jj < 32; ++jj) {
+                            if (col0 + jj < N) {
+                                float x = __uint_as_float(v[jj]);
+                                if (bias != nullptr) x += bias[col0 + jj];
+                                if (relu) x = fmaxf(x, 0.0f);
+                                out[jj] = x;
+                            }
+                        }
+                    }
+                }
+            }
+            ptx::tc_fence_before();
+            __syncwarp();
+            if (lane == 0) ptx::mbar_arrive(&sh.acc_empty[buf]);
+        }
+    }
+    ptx::tc_fence_before();
+    __syncthreads();
+    if (warp == 1) ptx::tmem_dealloc<2 * BN>(tmem);
+}
+
 using EncodeFn = CUresult (*)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
                               const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
                               CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
@@ -160,12 +303,14 @@ bool make_map(CUtensorMap* map, const void* base, long long rows, long long k, l
 template <int BN, bool TF32>
 cudaError_t launch_gemm(CUtensorMap const& ma, CUtensorMap const& mb, float* C, const float* bias, int M, int N, int K, long long ldc,
                         int relu, cudaStream_t stream) {
-    auto kern = gemm_tc_kernel<BN, TF32>;
+    auto kern = gemm_tc_persistent_kernel<BN, TF32>;
     size_t const smem = static_cast<size_t>(kGemmStages) * (kBM + BN) * kRowBytes;
     cudaError_t err = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem));
     if (err != cudaSuccess) return err;
-    dim3 grid((N + BN - 1) / BN, (M + kBM - 1) / kBM);
-    kern<<<grid, kGemmThreads, smem, stream>>>(ma, mb, C, bias, M, N, K, ldc, relu);
+    int const tiles_n = (N + BN - 1) / BN, tiles_m = (M + kBM - 1) / kBM;
+    long long const total = static_cast<long long>(tiles_m) * tiles_n;
+    int const grid = static_cast<int>(total < device_sm_count() ? total : device_sm_count());
+    kern<<<grid, kGemmThreads, smem, stream>>>(ma, mb, C, bias, M, N, K, ldc, relu, tiles_m, tiles_n);
     return cudaGetLastError();
 }
 
