@@ -20,17 +20,24 @@ The result is the same G gradients as G separate replicas (tests/test_grouped.py
 from __future__ import annotations
 
 import ctypes
+import os
 import types
 
 import torch
 import torch.nn.functional as F
 
 from ..ops import _lib
-from ..ops.nn import grouped_batch_norm, im2col_nhwc
+from ..ops.nn import gemm_nt, grouped_batch_norm, im2col_nhwc
 
 __all__ = ["GroupedWorkers"]
 
 _aten = torch.ops.aten
+
+# 1×1 convolutions forward on our tcgen05 GEMM instead of the library convolution. Opt-in: at the flagship's shapes
+# (M = 200·HW ≤ 12 800, K ≤ 2048, one tile per CTA, so the row-strided TMEM epilogue is exposed) it measured 2.58 ms
+# per gradient pass against 2.35 ms with the library kernels (profiles/README.md §3); it needs a coalesced
+# (smem-staged) epilogue and 64-wide tiles before it can be the default.
+POINTWISE_GEMM = [os.environ.get("GARFIELD_POINTWISE_GEMM", "0") != "0"]
 
 
 def _same_layout(a, b):
@@ -100,6 +107,14 @@ class _GroupedConv(torch.autograd.Function):
     def forward(ctx, x, w, b, owner, conv, widx, bidx):
         ctx.save_for_backward(x, w)
         ctx.cfg = (owner, conv, widx, bidx)
+        if (POINTWISE_GEMM[0] and conv.kernel_size == (1, 1) and conv.stride == (1, 1) and conv.padding == (0, 0) and conv.groups == 1
+                and x.is_cuda and x.dtype == torch.float32 and x.shape[1] % 4 == 0 and torch.backends.cudnn.allow_tf32
+                and x.is_contiguous(memory_format=torch.channels_last) and _lib.available()):
+            # a stride-1 1×1 convolution over NHWC activations IS the GEMM y[M, Cout] = x[M, Cin] · W[Cout, Cin]ᵀ:
+            # run it on our persistent tcgen05 kernel (TF32, like the library convolution it replaces)
+            n, cin, h, wd = x.shape
+            ym = gemm_nt(x.permute(0, 2, 3, 1).reshape(-1, cin), w.reshape(w.shape[0], cin), bias=b)
+            return ym.view(n, h, wd, w.shape[0]).permute(0, 3, 1, 2)
         return F.conv2d(x, w, b, conv.stride, conv.padding, conv.dilation, conv.groups)
 
     @staticmethod

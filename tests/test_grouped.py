@@ -112,11 +112,23 @@ def test_unsupported_models_are_reported():
 
 
 @pytest.mark.gpu
-def test_grouped_workers_match_separate_replicas_gpu():
+@pytest.mark.parametrize("pointwise_gemm", [False, True])
+def test_grouped_workers_match_separate_replicas_gpu(pointwise_gemm):
+    """pointwise_gemm: 1×1 convolutions forward on the tcgen05 GEMM (TF32 operands → looser tolerance)."""
+    from garfield_b200.parallel import grouped
+    previous = grouped.POINTWISE_GEMM[0]
+    grouped.POINTWISE_GEMM[0] = pointwise_gemm
+    try:
+        _check_grouped_gpu(8e-2 if pointwise_gemm else 2e-4, pointwise_gemm)   # TF32 everywhere vs exact fp32
+    finally:
+        grouped.POINTWISE_GEMM[0] = previous
+
+
+def _check_grouped_gpu(tolerance, allow_tf32):
     torch.manual_seed(0)
     dev = torch.device("cuda")
     prev = torch.backends.cudnn.allow_tf32
-    torch.backends.cudnn.allow_tf32 = False     # exact comparison; the bench runs with the default (TF32) on both paths
+    torch.backends.cudnn.allow_tf32 = allow_tf32     # exact comparison unless the TF32 GEMM path is under test
     try:
         module = _Net().to(dev)
         G, B = 4, 6
@@ -128,11 +140,12 @@ def test_grouped_workers_match_separate_replicas_gpu():
         torch.cuda.synchronize()
         for g in range(G):
             got, want = _logical(flat_model, matrix[g]), grads[g]
-            assert (got - want).norm() <= 2e-4 * want.norm(), (g, float((got - want).norm() / want.norm()))
-            assert torch.allclose(glosses[g], losses[g], rtol=1e-4)
+            assert (got - want).norm() <= tolerance * want.norm(), (g, float((got - want).norm() / want.norm()))
+            loose = allow_tf32
+            assert torch.allclose(glosses[g], losses[g], rtol=2e-2 if loose else 1e-4)
             for name, (rm, rv) in group.running_tables.items():
-                assert torch.allclose(rm[g], stats[g][name + ".running_mean"], rtol=1e-3, atol=1e-5)
-                assert torch.allclose(rv[g], stats[g][name + ".running_var"], rtol=1e-3, atol=1e-5)
+                assert torch.allclose(rm[g], stats[g][name + ".running_mean"], rtol=2e-2 if loose else 1e-3, atol=1e-3 if loose else 1e-5)
+                assert torch.allclose(rv[g], stats[g][name + ".running_var"], rtol=2e-2 if loose else 1e-3, atol=1e-3 if loose else 1e-5)
     finally:
         torch.backends.cudnn.allow_tf32 = prev
 
