@@ -2,10 +2,8 @@
 // cores: TMA 2-D tiled loads (128-byte swizzle) → 4-stage mbarrier ring → tcgen05.mma
 // (kind::tf32 for fp32 operands, kind::f16 for bf16 operands) accumulating in TMEM → tcgen05.ld
 // epilogue with fused bias / ReLU. Warp-specialised: warp 0 = TMA producer, warp 1 = MMA issuer
-// (one elected thread), warps 2-5 = epilogue (one TMEM lane quadrant each).
-//
-// The launched kernel is the persistent, double-buffered form further down (`gemm_tc_persistent_kernel`); the
-// one-tile-per-CTA kernel is kept as the readable reference of the pipeline.
+// (one elected thread), warps 2-5 = epilogue (one TMEM lane quadrant each). Persistent CTAs, two TMEM
+// accumulators: the epilogue of one tile overlaps the main loop of the next.
 //
 // This is the framework's own GEMM for nn.Linear forward / dgrad / wgrad (the reference relies on
 // cuBLAS through ATen: garfieldpp/models/nets.py:47-57, 68-77). Both operands are
@@ -31,104 +29,6 @@ constexpr int kGemmThreads = 32 * 6;
 constexpr int kGemmStages = 4;
 constexpr int kBM = 128;
 constexpr int kRowBytes = 128;  // bytes of K per stage and per smem row (one swizzle atom wide)
-
-struct GemmShared {
-    uint64_t full[kGemmStages];
-    uint64_t empty[kGemmStages];
-    uint64_t accum_done;
-    uint32_t tmem_base;
-};
-
-template <int BN, bool TF32>
-__global__ void __launch_bounds__(kGemmThreads, 1)
-gemm_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b, float* __restrict__ C,
-               const float* __restrict__ bias, int M, int N, int K, long long ldc, int relu) {
-    extern __shared__ __align__(1024) unsigned char smem_raw[];
-    __shared__ GemmShared sh;
-    constexpr uint32_t kABytes = kBM * kRowBytes, kBBytes = BN * kRowBytes, kStageBytes = kABytes + kBBytes;
-    constexpr int kElemsPerStage = TF32 ? 32 : 64;  // K elements per stage
-    int const warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    int const tile_n = blockIdx.x, tile_m = blockIdx.y;
-    int const k_steps = (K + kElemsPerStage - 1) / kElemsPerStage;
-
-    if (threadIdx.x == 0) {
-        for (int s = 0; s < kGemmStages; ++s) {
-            ptx::mbar_init(&sh.full[s], 1);
-            ptx::mbar_init(&sh.empty[s], 1);
-        }
-        ptx::mbar_init(&sh.accum_done, 1);
-        ptx::fence_mbar_init();
-        ptx::prefetch_tensormap(&map_a);
-        ptx::prefetch_tensormap(&map_b);
-    }
-    if (warp == 1) ptx::tmem_alloc<BN>(&sh.tmem_base);
-    ptx::tc_fence_before();
-    __syncthreads();
-    ptx::tc_fence_after();
-    uint32_t const tmem = sh.tmem_base;
-
-    if (warp == 0) {
-        if (ptx::elect_one()) {
-            for (int it = 0; it < k_steps; ++it) {
-                int const s = it % kGemmStages;
-                uint32_t const phase = static_cast<uint32_t>((it / kGemmStages) & 1);
-                ptx::mbar_wait(&sh.empty[s], phase ^ 1u);
-                ptx::mbar_arrive_expect_tx(&sh.full[s], kStageBytes);
-                unsigned char* dst = smem_raw + static_cast<size_t>(s) * kStageBytes;
-                ptx::tma_load_2d(dst, &map_a, it * kElemsPerStage, tile_m * kBM, &sh.full[s]);
-                ptx::tma_load_2d(dst + kABytes, &map_b, it * kElemsPerStage, tile_n * BN, &sh.full[s]);
-            }
-        }
-    } else if (warp == 1) {
-        if (ptx::elect_one()) {
-            uint32_t const idesc = TF32 ? ptx::make_idesc(2u, 2u, kBM, BN) : ptx::make_idesc(1u, 1u, kBM, BN);
-            for (int it = 0; it < k_steps; ++it) {
-                int const s = it % kGemmStages;
-                uint32_t const phase = static_cast<uint32_t>((it / kGemmStages) & 1);
-                ptx::mbar_wait(&sh.full[s], phase);
-                ptx::tc_fence_after();
-                uint32_t const a_base = ptx::smem_u32(smem_raw + static_cast<size_t>(s) * kStageBytes);
-                uint32_t const b_base = a_base + kABytes;
-#pragma unroll
-                for (int k = 0; k < 4; ++k) {  // 4 × 32 bytes of K inside the 128-byte swizzle atom
-                    uint64_t const adesc = ptx::make_smem_desc(a_base + k * 32u, 16u, 1024u, 2u);
-                    uint64_t const bdesc = ptx::make_smem_desc(b_base + k * 32u, 16u, 1024u, 2u);
-                    if (TF32) ptx::mma_tf32_ss(tmem, adesc, bdesc, idesc, (it > 0 || k > 0) ? 1u : 0u);
-                    else ptx::mma_f16_ss(tmem, adesc, bdesc, idesc, (it > 0 || k > 0) ? 1u : 0u);
-                }
-                ptx::mma_commit(&sh.empty[s]);
-            }
-            ptx::mma_commit(&sh.accum_done);
-        }
-    } else {
-        int const quad = warp & 3;
-        int const row = tile_m * kBM + quad * 32 + lane;
-        ptx::mbar_wait(&sh.accum_done, 0u);
-        ptx::tc_fence_after();
-#pragma unroll 1
-        for (int c0 = 0; c0 < BN; c0 += 16) {
-            uint32_t v[16];
-            ptx::tmem_ld_32x32b_x16(tmem + (static_cast<uint32_t>(quad * 32) << 16) + static_cast<uint32_t>(c0), v);
-            ptx::tmem_ld_wait();
-            int const col0 = tile_n * BN + c0;
-            if (row < M && col0 < N) {
-                float* out = C + static_cast<long long>(row) * ldc + col0;
-#pragma unroll
-                for (int j = 0; j < 16; ++j) {
-                    if (col0 + j < N) {
-                        float x = __uint_as_float(v[j]);
-                        if (bias != nullptr) x += bias[col0 + j];
-                        if (relu) x = fmaxf(x, 0.0f);
-                        out[j] = x;
-                    }
-                }
-            }
-        }
-    }
-    ptx::tc_fence_before();
-    __syncthreads();
-    if (warp == 1) ptx::tmem_dealloc<BN>(tmem);
-}
 
 // Persistent form: one CTA per SM walks the tile list; TMEM holds TWO accumulators (2·BN columns) so the epilogue of
 // tile j (tcgen05.ld → bias/ReLU → global stores) overlaps the TMA + MMA main loop of tile j+1. The smem ring runs on
