@@ -19,6 +19,7 @@
 #include <cooperative_groups.h>
 
 #include <cmath>
+#include <cstdlib>
 
 #include "garfield_b200.h"
 #include "launch.cuh"
@@ -108,6 +109,7 @@ __global__ void __launch_bounds__(kBnThreads) bn_nhwc_fwd_kernel(int rows, int C
     __shared__ float4 part[2][QUADS];
     constexpr int kLanes = kBnThreads / QUADS;                          // row lanes per CTA
     BnGeom const t = bn_geometry<QUADS>(rows, C, splits);
+    cudaGridDependencySynchronize();   // no-op unless launched with programmatic stream serialization
     {   // blockIdx.z = statistics group: a contiguous block of `rows` rows with its own mean/variance/running buffers
         long long const goff = static_cast<long long>(blockIdx.z) * rows * C;
         int const soff = blockIdx.z * C;
@@ -206,6 +208,7 @@ __global__ void __launch_bounds__(kBnThreads) bn_nhwc_bwd_kernel(int rows, int C
     __shared__ float4 part[2][QUADS];
     constexpr int kLanes = kBnThreads / QUADS;
     BnGeom const t = bn_geometry<QUADS>(rows, C, splits);
+    cudaGridDependencySynchronize();
     {
         long long const goff = static_cast<long long>(blockIdx.z) * rows * C;
         int const soff = blockIdx.z * C;
@@ -311,19 +314,33 @@ inline BnPlan plan(int groups, int rows, int C) {
     return p;
 }
 
+inline bool pdl_enabled() {
+    static int const on = [] { char const* v = std::getenv("GARFIELD_BN_PDL"); return v != nullptr && v[0] == '1' ? 1 : 0; }();
+    return on != 0;
+}
+
 template <typename Kernel, typename... Args>
 cudaError_t launch_bn(Kernel kernel, BnPlan const& p, cudaStream_t stream, Args... args) {
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = p.grid;
     cfg.blockDim = dim3(kBnThreads);
     cfg.stream = stream;
-    cudaLaunchAttribute attr[1];
-    attr[0].id = cudaLaunchAttributeClusterDimension;
-    attr[0].val.clusterDim.x = p.splits;
-    attr[0].val.clusterDim.y = 1;
-    attr[0].val.clusterDim.z = 1;
+    cudaLaunchAttribute attr[2];
+    int count = 0;
+    if (p.splits > 1) {
+        attr[count].id = cudaLaunchAttributeClusterDimension;
+        attr[count].val.clusterDim.x = p.splits;
+        attr[count].val.clusterDim.y = 1;
+        attr[count].val.clusterDim.z = 1;
+        ++count;
+    }
+    if (pdl_enabled()) {   // programmatic dependent launch: CTAs are scheduled while the producer drains; the kernel
+        attr[count].id = cudaLaunchAttributeProgrammaticStreamSerialization;   // waits in cudaGridDependencySynchronize()
+        attr[count].val.programmaticStreamSerializationAllowed = 1;
+        ++count;
+    }
     cfg.attrs = attr;
-    cfg.numAttrs = p.splits > 1 ? 1 : 0;
+    cfg.numAttrs = count;
     return cudaLaunchKernelEx(&cfg, kernel, args...);
 }
 
