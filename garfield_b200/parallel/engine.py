@@ -31,7 +31,7 @@ from ..garfieldpp import tools
 from ..garfieldpp.datasets import DatasetManager
 from ..ops import _lib, attacks, gar as gar_ops
 from ..ops.optim import FlatOptimizer
-from .grouped import GroupedWorkers
+from .grouped import GroupedWorkers, ScatterSink
 
 __all__ = ["SSMWEngine"]
 
@@ -157,7 +157,7 @@ class SSMWEngine:
     def __init__(self, model, dataset, loss, num_workers, f, gar, batch, optimizer="sgd", opt_args=None, byzantine=None,
                  device=None, group=None, use_graphs=True, train_set=None, seed=1234, gar_kwargs=None, sharded=None,
                  channels_last=True, sync="nccl", flag_timeout=5.0, gather_grads=True, fast_bn=True,
-                 split_backward=None, fuse_workers=None, fusion_chains=1):
+                 split_backward=None, fuse_workers=None, fusion_chains=1, scatter_grads=None):
         self.rank = dist.get_rank(group) if dist.is_initialized() else 0
         self.world = dist.get_world_size(group) if dist.is_initialized() else 1
         self.group = group
@@ -190,10 +190,20 @@ class SSMWEngine:
             # workers the GPU is already saturated by their streams and the extra ones only add contention
             split_backward = len(self.local_ids) <= 2
         self.max_local = (self.n + self.world - 1) // self.world
+        loss_fn = tools.select_loss(loss)
+        if fuse_workers is None:     # also pays for a single hosted worker (in-place weight-gradient GEMMs, no gather copy)
+            fuse_workers = gather_grads
+        fuse_workers = bool(fuse_workers) and GroupedWorkers.unsupported_reason(module, loss_fn) is None
+        # scatter: with the coordinate-sharded server, every worker's gradient is written slice by slice straight into
+        # the arena of the rank that aggregates that range (a reduce-scatter by construction, overlapped with the
+        # backward pass); the aggregation kernels then read local HBM only.
+        self.per = (self.pitch // 64 + self.world - 1) // self.world * 64      # coordinates per rank (multiple of 64 floats)
+        self.scatter = fuse_workers and self.sharded and (scatter_grads is None or bool(scatter_grads))
 
-        # peer-mapped arenas: parameters (one per rank) and gradient rows (max_local per rank)
+        # peer-mapped arenas: parameters (one per rank) and gradient rows (max_local full rows per rank, or — scatter —
+        # one slice-long row per worker of the whole job)
         self.param_arena = PeerArena(self.pitch, self.device, group)
-        self.grad_arena = PeerArena(self.max_local * self.pitch, self.device, group)
+        self.grad_arena = PeerArena(self.world * self.max_local * self.per if self.scatter else self.max_local * self.pitch, self.device, group)
         self.flat = self.param_arena.local[:self.d]
         self.master = FlatModel(module, self.device, flat=None, channels_last=self.channels_last)
         if self.world > 1:  # everyone starts from rank 0's initialisation
@@ -203,12 +213,11 @@ class SSMWEngine:
         self.flat.copy_(self.master.flat)
         self.master = FlatModel(module, self.device, flat=self.flat, channels_last=self.channels_last)  # re-alias onto the arena
 
-        loss_fn = tools.select_loss(loss)
         self.train_sets = {}
         self.workers = []
         for j, wid in enumerate(self.local_ids):
             replica = FlatModel(copy.deepcopy(module), self.device, flat=self.flat, channels_last=self.channels_last)
-            row = self.grad_arena.local[j * self.pitch:j * self.pitch + self.d]
+            row = None if self.scatter else self.grad_arena.local[j * self.pitch:j * self.pitch + self.d]
             if train_set is not None:
                 batches = train_set(wid)
             else:
@@ -226,16 +235,12 @@ class SSMWEngine:
         # worker fusion: the co-located workers share ONE forward/backward pass (parallel/grouped.py) when every
         # layer of the model is covered; otherwise each worker keeps its own chain and stream
         self.fused = None
-        if fuse_workers is None:     # also pays for a single hosted worker (in-place weight-gradient GEMMs, no gather copy)
-            fuse_workers = len(self.workers) >= 1 and gather_grads
-        if fuse_workers and self.workers and GroupedWorkers.unsupported_reason(module, loss_fn) is None:
-            self._fuse_workers(module, loss_fn, max(1, min(int(fusion_chains), len(self.workers))))
+        if fuse_workers and self.workers:
+            self._fuse_workers(module, loss_fn, 1 if self.scatter else max(1, min(int(fusion_chains), len(self.workers))))
 
         # server state (whole vector on rank 0, or this rank's coordinate slice when sharded)
         if self.sharded:
-            per = (self.pitch // 64 + self.world - 1) // self.world * 64   # slice length, multiple of 64 floats
-            self.lo = min(self.d, self.rank * per)
-            self.hi = min(self.d, self.lo + per)
+            self.lo, self.hi = self._bounds(self.rank)
         else:
             self.lo, self.hi = 0, self.d
         self.optimizer, self.rows = None, None
@@ -244,7 +249,11 @@ class SSMWEngine:
             self.rows = []
             for wid in range(self.n):
                 owner, j = wid % self.world, wid // self.world
-                self.rows.append(self.grad_arena.peer(owner)[j * self.pitch + self.lo:j * self.pitch + self.hi])
+                if self.scatter:    # this rank's slice of every worker's gradient is in its own arena
+                    at = (owner * self.max_local + j) * self.per
+                    self.rows.append(self.grad_arena.local[at:at + self.hi - self.lo])
+                else:
+                    self.rows.append(self.grad_arena.peer(owner)[j * self.pitch + self.lo:j * self.pitch + self.hi])
             self.mirrors = [self.param_arena.peer(r)[self.lo:self.hi] for r in range(self.world) if r != self.rank]
         self._flag = torch.zeros(1, device=self.device)
         # sync="flags": ranks synchronise through peer-mapped epoch flags polled by a tiny kernel with a
@@ -268,6 +277,10 @@ class SSMWEngine:
         self.steps_done = 0
         self.h2d_bytes = 0
 
+    def _bounds(self, rank):
+        lo = min(self.d, rank * self.per)
+        return lo, min(self.d, lo + self.per)
+
     def _fuse_workers(self, module, loss_fn, chains=1):
         """Point every local worker's inputs, loss and BatchNorm running statistics at slices of the group's
         buffers, so loading batches, evaluation and checkpoints work on the worker objects as before.
@@ -285,7 +298,13 @@ class SSMWEngine:
         self._chains = []
         for lo, hi in zip(bounds[:-1], bounds[1:]):
             replica = FlatModel(copy.deepcopy(module), self.device, flat=self.flat, channels_last=self.channels_last)
-            group = GroupedWorkers(replica, [w.row for w in self.workers[lo:hi]], loss_fn)
+            sink = None
+            if self.scatter:
+                arenas = [self.grad_arena.peer(r) for r in range(self.world)]
+                bounds = [self._bounds(r) for r in range(self.world)]
+                first, per = self.rank * self.max_local, self.per
+                sink = lambda params, slices, view_of: ScatterSink(params, slices, view_of, G, arenas, first, per, bounds)
+            group = GroupedWorkers(replica, [w.row for w in self.workers[lo:hi]], loss_fn, sink=sink)
             stream = torch.cuda.Stream(device=self.device) if chains > 1 else None
             self._chains.append((group, data[lo * b:hi * b], target[lo * t:hi * t], self._group_losses[lo:hi], stream))
             for g, w in enumerate(self.workers[lo:hi]):
@@ -415,9 +434,26 @@ class SSMWEngine:
             _lib.count(self._graph_launches)
         else:
             self._run_workers()
-        for w in self.workers:
+        for w in ([] if self.scatter else self.workers):
             if w.attack is not None:
                 self._attack(w)
+
+    def _attack_slices(self):
+        """Scatter mode: every attack is coordinate-wise, so the rank that owns a coordinate range applies it to its
+        slice of the Byzantine workers' rows (colluding attacks see the honest workers' slices)."""
+        honest = [row for wid, row in enumerate(self.rows) if wid not in self.byzantine]
+        for wid, kind in self.byzantine.items():
+            row = self.rows[wid]
+            if kind == "random":
+                row.copy_(attacks.random_like(row))
+            elif kind == "reverse":
+                row.copy_(attacks.reverse(row))
+            elif kind == "drop":
+                row.copy_(attacks.drop(row))
+            elif kind in ("lie", "empire"):
+                row.copy_(attacks.lie(honest or [row]) if kind == "lie" else attacks.empire(honest or [row]))
+            else:
+                raise ValueError("unknown attack %r" % (kind,))
 
     def _attack(self, w):
         if w.attack == "random":
@@ -439,6 +475,8 @@ class SSMWEngine:
         """Server side: fused gather + GAR + optimizer step + parameter publication, on the whole
         vector (rank 0) or on this rank's coordinate slice (sharded)."""
         opt = self.optimizer
+        if self.scatter and self.byzantine and self.rows:
+            self._attack_slices()
         if self.sharded:
             if opt is None:  # empty slice: still take part in the distance all-reduce
                 raise RuntimeError("empty coordinate slice: use fewer ranks than d / 64")

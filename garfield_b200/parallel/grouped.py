@@ -29,7 +29,7 @@ import torch.nn.functional as F
 from ..ops import _lib
 from ..ops.nn import gemm_nt, grouped_batch_norm, im2col_nhwc
 
-__all__ = ["GroupedWorkers"]
+__all__ = ["GroupedWorkers", "ScatterSink"]
 
 _aten = torch.ops.aten
 
@@ -98,6 +98,78 @@ class _GradSink:
             base = self.rows[0]
             _lib.check(_lib.require().gb_multi_copy((ctypes.c_void_p * k)(*srcs), (ctypes.c_uint64 * k)(*offs), (ctypes.c_uint32 * k)(*sizes), k,
                                                     base.data_ptr(), _lib.stream_ptr(base.device)))
+            _lib.count((k + 111) // 112)
+        self.pending = {}
+
+
+class ScatterSink:
+    """Gradient sink for the coordinate-sharded server: the gradient of worker g (arena row `first_row + g`) is written
+    slice by slice straight into the arena of the rank that AGGREGATES that coordinate range — a reduce-scatter by
+    construction. `arenas[r]` is rank r's peer-mapped arena ([rows, per] floats, row pitch `per`), `bounds[r]` the
+    coordinate range [lo, hi) rank r owns. Parameters lying inside one range are written in place by the producing
+    batched GEMM (its epilogue stores go over NVLink while the backward pass continues); parameters straddling a
+    boundary, BatchNorm parameters and biases are scattered by one multi-tensor copy per destination rank."""
+
+    DONE = _GradSink.DONE
+
+    def __init__(self, params, slices, view_of, groups, arenas, first_row, per, bounds):
+        self.params, self.slices, self.view_of, self.groups = params, slices, view_of, groups
+        self.arenas, self.first_row, self.per, self.bounds = arenas, first_row, per, bounds
+        self.pending = {}
+        self._pieces = [self._owners(off, n) for off, n, _ in slices]
+
+    def _owners(self, off, n):
+        pieces = []
+        for r, (lo, hi) in enumerate(self.bounds):
+            a, b = max(off, lo), min(off + n, hi)
+            if a < b:
+                pieces.append((r, a, b))
+        return pieces
+
+    def put(self, index, grads):
+        self.pending[index] = grads
+
+    def direct(self, index, rows, cols):
+        pieces = self._pieces[index]
+        if len(pieces) != 1:
+            return None
+        r, a, _ = pieces[0]
+        base = self.arenas[r]
+        return torch.as_strided(base, (self.groups, rows, cols), (self.per, cols, 1),
+                                base.storage_offset() + self.first_row * self.per + (a - self.bounds[r][0]))
+
+    def flush(self):
+        table = {}
+        keep = []          # staging copies must outlive the launches below
+        for index, (p, (off, n, shape)) in enumerate(zip(self.params, self.slices)):
+            grads = self.pending.get(index)
+            if grads is self.DONE:
+                continue
+            for g in range(self.groups):
+                src = None
+                if grads is not None:
+                    t = grads[g]
+                    if t.shape != p.shape:
+                        t = t.reshape(p.shape)
+                    if not (t.dtype == torch.float32 and _same_layout(t, p) and t.is_cuda):
+                        staged = torch.empty(n, device=p.device)           # the parameter's storage order
+                        self.view_of(staged, 0, n, shape).copy_(t)
+                        t = staged
+                    keep.append(t)
+                    src = t.data_ptr()
+                for r, a, b in self._pieces[index]:
+                    dst_off = (self.first_row + g) * self.per + (a - self.bounds[r][0])
+                    if src is None:
+                        self.arenas[r][dst_off:dst_off + (b - a)].zero_()
+                    else:
+                        entry = table.setdefault(r, ([], [], []))
+                        entry[0].append(src + 4 * (a - off)); entry[1].append(dst_off); entry[2].append(b - a)
+        lib = _lib.require()
+        for r, (srcs, offs, sizes) in table.items():
+            k = len(srcs)
+            base = self.arenas[r]
+            _lib.check(lib.gb_multi_copy((ctypes.c_void_p * k)(*srcs), (ctypes.c_uint64 * k)(*offs), (ctypes.c_uint32 * k)(*sizes), k,
+                                         base.data_ptr(), _lib.stream_ptr(base.device)))
             _lib.count((k + 111) // 112)
         self.pending = {}
 
@@ -262,7 +334,9 @@ class GroupedWorkers:
 
     _BATCHNORM = (torch.nn.BatchNorm1d, torch.nn.BatchNorm2d)
 
-    def __init__(self, replica, rows, loss_fn, side_streams=4):
+    def __init__(self, replica, rows, loss_fn, side_streams=4, sink=None):
+        """`sink`: a factory `(params, slices, view_of) -> sink` replacing the default rows-of-one-arena destination
+        (e.g. `ScatterSink` for the coordinate-sharded server); `rows` is then only used for its length."""
         self.replica, self.module, self.rows = replica, replica.module, list(rows)
         self.groups = len(self.rows)
         self.loss_kind = self._loss_kind(loss_fn)
@@ -271,7 +345,7 @@ class GroupedWorkers:
             raise ValueError("worker fusion does not cover this model: " + reason)
         params = list(self.module.parameters())
         index = {id(p): i for i, p in enumerate(params)}
-        self.sink = _GradSink(params, replica.slices, self.rows, replica._view)
+        self.sink = sink(params, replica.slices, replica._view) if sink is not None else _GradSink(params, replica.slices, self.rows, replica._view)
         device = params[0].device
         self.side_streams = [torch.cuda.Stream(device=device) for _ in range(side_streams)] if device.type == "cuda" and side_streams else []
         self.running_tables = {}
