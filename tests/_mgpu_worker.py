@@ -61,6 +61,33 @@ def main():
     torch.testing.assert_close(finals[0], finals[1], rtol=1e-4, atol=1e-6)   # cuDNN wgrad is not bitwise reproducible
     if rank == 0:
         print("ok flags", flush=True)
+    # scatter mode (every gradient slice written straight into its aggregating rank's arena, owner-side attacks, CUDA graph)
+    # against the pull-over-NVLink sharded server, on a model with BatchNorm and k×k / 1×1 / Linear weight-gradient paths
+    finals = []
+    for scatter in (False, True):
+        eng = SSMWEngine("cnn", "synthetic-cifar10", "cross-entropy", 8, 1, "krum", 8, "sgd", dict(lr=0.02, momentum=0.9),
+                         byzantine={7: "reverse"}, use_graphs=True, sharded=True, seed=17, scatter_grads=scatter)
+        assert eng.scatter == scatter and eng.fused is not None
+        for module in [w.replica.module for w in eng.workers] + [eng.fused.module]:
+            for m in module.modules():
+                if isinstance(m, (torch.nn.Dropout, torch.nn.Dropout2d)):
+                    m.p = 0.0
+        for i in range(4):
+            eng.step(i)
+        torch.cuda.synchronize()
+        finals.append(eng.master.to_reference_order(eng.flat).clone())
+        eng.close()
+    diff = (finals[0] - finals[1]).abs()
+    assert diff.max().item() < 2e-3 and (diff > 2e-4).float().mean().item() < 1e-3, "scatter != pull: max %g" % diff.max().item()
+    # colluding attacks are applied by the owner of each coordinate range (they see every honest worker's slice)
+    eng = SSMWEngine("cnn", "synthetic-cifar10", "cross-entropy", 8, 1, "median", 8, "sgd", dict(lr=0.02, momentum=0.9),
+                     byzantine={7: "lie"}, use_graphs=True, sharded=True, seed=17)
+    assert eng.scatter
+    losses = [eng.step(i).item() for i in range(3)]
+    assert all(l == l for l in losses) and torch.isfinite(eng.flat).all()
+    eng.close()
+    if rank == 0:
+        print("ok scatter", flush=True)
     dist.destroy_process_group()
 
 
