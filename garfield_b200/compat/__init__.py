@@ -5,3 +5,4 @@ itself is not required (and not installed here): models/optimizers come from the
 from .aggregator_tf import Aggregator_tf  # noqa: F401
 from .attacker import Attacker  # noqa: F401
 from .network import Network  # noqa: F401
+from .model import ModelManager  # noqa: F401

@@ -161,10 +161,12 @@ class ScatterSink:
                     dst_off = (self.first_row + g) * self.per + (a - self.bounds[r][0])
                     if src is None:
                         self.arenas[r][dst_off:dst_off + (b - a)].zero_()
+                    elif not self.arenas[r].is_cuda:      # host arenas (unit tests of the slicing logic)
+                        self.arenas[r][dst_off:dst_off + (b - a)].copy_(t.reshape(-1)[a - off:b - off])
                     else:
                         entry = table.setdefault(r, ([], [], []))
                         entry[0].append(src + 4 * (a - off)); entry[1].append(dst_off); entry[2].append(b - a)
-        lib = _lib.require()
+        lib = _lib.require() if table else None
         for r, (srcs, offs, sizes) in table.items():
             k = len(srcs)
             base = self.arenas[r]

@@ -167,3 +167,20 @@ def test_legacy_lipschitz_filter_and_update_model():
     m, g = np.ones(5, np.float32), np.full(5, 2.0, np.float32)
     assert np.allclose(lx.update_model(m, g), 0.8)
     assert torch.allclose(lx.update_model(torch.ones(5), torch.full((5,), 2.0)), torch.full((5,), 0.8))
+
+
+def test_tf_model_manager_names():
+    """tensorflow_impl/libs/model.py names resolve to torch modules producing [batch, classes] logits."""
+    import torch
+    from garfield_b200.compat import ModelManager
+    info = {"num_classes": 7, "image_shape": (3, 32, 32)}
+    for name in ("Small", "CNN", "Cifarnet", "MobileNetV2"):
+        net = ModelManager(name, info).model
+        net.eval()
+        with torch.no_grad():
+            assert net(torch.randn(2, 3, 32, 32)).shape == (2, 7), name
+    assert ModelManager("Small", {"num_classes": 10, "image_shape": (1, 28, 28)}).model(torch.randn(3, 1, 28, 28)).shape == (3, 10)
+    assert set(ModelManager.NAMES) == {"Small", "MobileNetV2", "Resnet50", "Resnet200", "VGG", "DenseNet", "Cifarnet", "Inception", "CNN"}
+    import pytest
+    with pytest.raises(AssertionError):
+        ModelManager("Transformer", info)

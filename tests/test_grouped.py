@@ -189,3 +189,33 @@ def test_im2col_kernel_matches_unfold(shape, k, stride, pad):
     got = gnn.im2col_nhwc(x, (k, k), (stride, stride), (pad, pad))
     want = gnn.im2col_nhwc(x.cpu().contiguous(), (k, k), (stride, stride), (pad, pad))
     assert torch.equal(got.cpu(), want)
+
+
+def test_scatter_sink_slices_every_gradient_to_its_owner_cpu():
+    """ScatterSink: worker g's gradient lands slice by slice in the arena of the rank owning each coordinate range
+    (in-place GEMM outputs for parameters inside one range, copies for the ones straddling a boundary)."""
+    from garfield_b200.parallel.grouped import ScatterSink
+    torch.manual_seed(3)
+    module = _Net()
+    G, B, world = 3, 4, 3
+    xs = [torch.randn(B, 3, 8, 8) for _ in range(G)]
+    ys = [torch.randint(0, 5, (B,)) for _ in range(G)]
+    loss_fn = torch.nn.CrossEntropyLoss()
+    grads, _, _ = _reference(module, xs, ys, loss_fn)
+    flat_model = FlatModel(copy.deepcopy(module), torch.device("cpu"))
+    d = flat_model.numel
+    per = ((d + 63) // 64 + world - 1) // world * 64
+    bounds = [(min(d, r * per), min(d, r * per + per)) for r in range(world)]
+    first_row, rows_total = 2, 2 + G + 1                      # this "rank" owns arena rows 2 .. 2+G-1
+    arenas = [torch.full((rows_total * per,), float("nan")) for _ in range(world)]
+    sink = lambda params, slices, view_of: ScatterSink(params, slices, view_of, G, arenas, first_row, per, bounds)
+    group = GroupedWorkers(flat_model, [None] * G, loss_fn, side_streams=0, sink=sink)
+    straddling = sum(1 for pieces in group.sink._pieces if len(pieces) > 1)
+    assert straddling >= 1 and any(len(pieces) == 1 for pieces in group.sink._pieces)
+    losses = torch.zeros(G)
+    group.forward_backward(torch.cat(xs), torch.cat(ys), losses)
+    for g in range(G):
+        got = torch.cat([arenas[r][(first_row + g) * per:(first_row + g) * per + (hi - lo)] for r, (lo, hi) in enumerate(bounds)])
+        assert torch.allclose(got, grads[g], rtol=1e-4, atol=1e-5), g
+    untouched = torch.cat([a[:first_row * per] for a in arenas] + [a[(first_row + G) * per:] for a in arenas])
+    assert torch.isnan(untouched).all()                      # other ranks' rows are never written
