@@ -28,6 +28,7 @@ namespace {
 constexpr int kGemmThreads = 32 * 6;
 constexpr int kGemmStages = 4;
 constexpr int kBM = 128;
+constexpr int kStagePitch = 36;  // floats per staged epilogue row (32 + 4: 16-byte aligned, bank-conflict-free)
 constexpr int kRowBytes = 128;  // bytes of K per stage and per smem row (one swizzle atom wide)
 
 // Persistent form: one CTA per SM walks the tile list; TMEM holds TWO accumulators (2·BN columns) so the epilogue of
@@ -48,6 +49,7 @@ gemm_tc_persistent_kernel(const __grid_constant__ CUtensorMap map_a, const __gri
                           const float* __restrict__ bias, int M, int N, int K, long long ldc, int relu, int tiles_m, int tiles_n) {
     extern __shared__ __align__(1024) unsigned char smem_raw[];
     __shared__ GemmSharedP sh;
+    __shared__ __align__(16) float epi_stage[4][32 * kStagePitch];   // per epilogue warp: 32 rows × 32 columns (+ padding)
     constexpr uint32_t kABytes = kBM * kRowBytes, kBBytes = BN * kRowBytes, kStageBytes = kABytes + kBBytes;
     constexpr int kElemsPerStage = TF32 ? 32 : 64;
     int const warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -123,10 +125,12 @@ gemm_tc_persistent_kernel(const __grid_constant__ CUtensorMap map_a, const __gri
         for (int t = blockIdx.x; t < total; t += gridDim.x, ++j) {
             int const tile_m = t % tiles_m, tile_n = t / tiles_m;
             int const buf = j & 1;
-            int const row = tile_m * kBM + quad * 32 + lane;
             ptx::mbar_wait(&sh.acc_full[buf], static_cast<uint32_t>((j >> 1) & 1));
             ptx::tc_fence_after();
             uint32_t const acc = tmem + static_cast<uint32_t>(buf * BN) + (static_cast<uint32_t>(quad * 32) << 16);
+            int const row0 = tile_m * kBM + quad * 32;                       // first row of this warp's TMEM lane quadrant
+            float* const stage = &epi_stage[quad][0];
+            bool const vec_ok = (reinterpret_cast<uintptr_t>(C) & 15u) == 0 && (ldc & 3) == 0;
 #pragma unroll 1
             for (int c0 = 0; c0 < BN; c0 += 32) {
                 uint32_t v[32];
@@ -134,31 +138,40 @@ gemm_tc_persistent_kernel(const __grid_constant__ CUtensorMap map_a, const __gri
                 ptx::tmem_ld_32x32b_x16(acc + static_cast<uint32_t>(c0 + 16), reinterpret_cast<uint32_t(&)[16]>(v[16]));
                 ptx::tmem_ld_wait();
                 int const col0 = tile_n * BN + c0;
-                if (row < M && col0 < N) {
-                    float* out = C + static_cast<long long>(row) * ldc + col0;
-                    if (col0 + 32 <= N && (reinterpret_cast<uintptr_t>(out) & 15u) == 0) {
+                if (col0 >= N || row0 >= M) continue;                         // warp-uniform
+                // thread = one row × 32 columns in registers → stage through shared memory (pitch 36 floats: conflict-free
+                // 16-byte accesses both ways) so that global stores are 128-byte row segments instead of 32 scattered 16-byte pieces
 #pragma unroll
-                        for (int q = 0; q < 8; ++q) {
-                            float4 o = make_float4(__uint_as_float(v[4 * q]), __uint_as_float(v[4 * q + 1]), __uint_as_float(v[4 * q + 2]),
-                                                   __uint_as_float(v[4 * q + 3]));
-                            if (bias != nullptr) {
-                                o.x += bias[col0 + 4 * q]; o.y += bias[col0 + 4 * q + 1]; o.z += bias[col0 + 4 * q + 2]; o.w += bias[col0 + 4 * q + 3];
-                            }
-                            if (relu) { o.x = fmaxf(o.x, 0.f); o.y = fmaxf(o.y, 0.f); o.z = fmaxf(o.z, 0.f); o.w = fmaxf(o.w, 0.f); }
-                            *reinterpret_cast<float4*>(out + 4 * q) = o;
-                        }
-                    } else {
+                for (int q = 0; q < 8; ++q) {
+                    float4 o = make_float4(__uint_as_float(v[4 * q]), __uint_as_float(v[4 * q + 1]), __uint_as_float(v[4 * q + 2]),
+                                           __uint_as_float(v[4 * q + 3]));
+                    if (bias != nullptr) {
+                        int const c = col0 + 4 * q;
+                        o.x += c < N ? bias[c] : 0.f; o.y += c + 1 < N ? bias[c + 1] : 0.f;
+                        o.z += c + 2 < N ? bias[c + 2] : 0.f; o.w += c + 3 < N ? bias[c + 3] : 0.f;
+                    }
+                    if (relu) { o.x = fmaxf(o.x, 0.f); o.y = fmaxf(o.y, 0.f); o.z = fmaxf(o.z, 0.f); o.w = fmaxf(o.w, 0.f); }
+                    *reinterpret_cast<float4*>(stage + lane * kStagePitch + 4 * q) = o;
+                }
+                __syncwarp();
 #pragma unroll
-                        for (int jj = 0; jj < 32; ++jj) {
-                            if (col0 + jj < N) {
-                                float x = __uint_as_float(v[jj]);
-                                if (bias != nullptr) x += bias[col0 + jj];
-                                if (relu) x = fmaxf(x, 0.0f);
-                                out[jj] = x;
-                            }
+                for (int i = 0; i < 8; ++i) {
+                    int const r = i * 4 + (lane >> 3), c = (lane & 7) * 4;
+                    float4 const o = *reinterpret_cast<float4 const*>(stage + r * kStagePitch + c);
+                    int const grow = row0 + r, gcol = col0 + c;
+                    if (grow < M && gcol < N) {
+                        float* out = C + static_cast<long long>(grow) * ldc + gcol;
+                        if (vec_ok && gcol + 3 < N) {
+                            *reinterpret_cast<float4*>(out) = o;
+                        } else {
+                            out[0] = o.x;
+                            if (gcol + 1 < N) out[1] = o.y;
+                            if (gcol + 2 < N) out[2] = o.z;
+                            if (gcol + 3 < N) out[3] = o.w;
                         }
                     }
                 }
+                __syncwarp();
             }
             ptx::tc_fence_before();
             __syncwarp();

@@ -34,9 +34,9 @@ __all__ = ["GroupedWorkers", "ScatterSink"]
 _aten = torch.ops.aten
 
 # 1×1 convolutions forward on our tcgen05 GEMM instead of the library convolution. Opt-in: at the flagship's shapes
-# (M = 200·HW ≤ 12 800, K ≤ 2048, one tile per CTA, so the row-strided TMEM epilogue is exposed) it measured 2.58 ms
-# per gradient pass against 2.35 ms with the library kernels (profiles/README.md §3); it needs a coalesced
-# (smem-staged) epilogue and 64-wide tiles before it can be the default.
+# (M = 200·HW ≤ 12 800, K ≤ 2048: one tile per CTA, so set-up and epilogue are exposed) it measured 2.53 ms per
+# gradient pass against 2.34 ms with the library kernels (profiles/README.md §3); it needs a small-tile variant
+# before it can be the default.
 POINTWISE_GEMM = [os.environ.get("GARFIELD_POINTWISE_GEMM", "0") != "0"]
 
 
