@@ -56,10 +56,10 @@ GB_API void gb_combinations_seek(unsigned n, unsigned k, uint64_t pos, int* idx)
 GB_API int gb_combinations_next(unsigned n, unsigned k, int* idx);   /* 1 = advanced, 0 = was last */
 
 /* Thread-pool coverage probe for tests. ref: include/threadpool.hpp:202-222 */
+GB_API int gb_cpu_parallel_for_probe(int64_t total, int64_t grain, int32_t* hits);
 /* k-th smallest along `axis` of a row-major [shape] array, in place (std::nth_element over csrc/cpu/strided_view.hpp's
  * strided iterator), one value per line -> out. ref: include/array.hpp (N-D strided view + iterator, bulyan.cpp:167-171). */
 GB_API int gb_cpu_axis_nth_f32(float* data, int rank, int64_t const* shape, int axis, int64_t k, float* out);
-GB_API int gb_cpu_parallel_for_probe(int64_t total, int64_t grain, int32_t* hits);
 
 /* Multi-replica register. ref: include/multiregister.hpp:232-552.
  * write/read return 0 ok, 1 closed, 2 timed out; timeout_ns < 0 waits forever. */
