@@ -20,7 +20,7 @@ import torch
 from . import _lib
 from ._lib import FusedUpdate
 
-__all__ = ["available", "pairwise_sqdist", "select", "coordwise", "krum", "bulyan", "mda", "aksel",
+__all__ = ["available", "pairwise_sqdist", "select", "coordwise", "krum", "bulyan", "mda", "aksel", "distance_rules",
            "average", "weighted", "SgdFusion", "MAX_ROWS"]
 
 MAX_ROWS = 64
@@ -39,8 +39,10 @@ class _Workspace:
     _cache = {}
 
     @classmethod
-    def get(cls, device, n):
-        key = (device.index if device.index is not None else torch.cuda.current_device(), n)
+    def get(cls, device, n, tag=0):
+        """`tag` separates workspaces that are in flight at the same time (e.g. distances of one coordinate range
+        computed on a side stream while another call runs)."""
+        key = (device.index if device.index is not None else torch.cuda.current_device(), n, tag)
         ws = cls._cache.get(key)
         if ws is None:
             lib = _lib.require()
@@ -114,7 +116,7 @@ def coordwise(gradients, rule, f=0, beta=0, upper=False, p=0.9, seed=0, W=None, 
 TENSOR_CORE_MIN_ROWS = [17]  # `engine="auto"` uses the tcgen05 Gram kernel from this many rows (<= 32)
 
 
-def select(gradients, mode, f=0, m=0, neighbors=0, squared=True, engine="auto"):
+def select(gradients, mode, f=0, m=0, neighbors=0, squared=True, engine="auto", workspace_tag=0):
     """Distances + selection in one launch. Returns the device workspace dict with
     `dist` (n×n), `W` (n×n buffer, first θ rows valid) and `info`.
 
@@ -122,7 +124,7 @@ def select(gradients, mode, f=0, m=0, neighbors=0, squared=True, engine="auto"):
     aligned rows), "auto" = tc for TENSOR_CORE_MIN_ROWS <= n <= 32 when the rows qualify."""
     rows, n, d, device = _prep(gradients)
     lib = _lib.require()
-    ws = _Workspace.get(device, n)
+    ws = _Workspace.get(device, n, workspace_tag)
     aligned = all(r.data_ptr() % 16 == 0 for r in rows)
     use_tc = engine == "tc" or (engine == "auto" and TENSOR_CORE_MIN_ROWS[0] <= n <= 32 and aligned and d >= 4096)
     if use_tc:
@@ -246,13 +248,23 @@ _DISTANCE_RULES = {
 }
 
 
-def aggregate_sharded(name, slice_rows, f, allreduce, m=None, update=None, want_out=True, out=None, **kw):
+def distance_rules():
+    """Names of the rules whose selection depends on pairwise distances (and can therefore be coordinate-sharded
+    or have part of their distances computed ahead of time)."""
+    return tuple(_DISTANCE_RULES)
+
+
+def aggregate_sharded(name, slice_rows, f, allreduce, m=None, update=None, want_out=True, out=None, apply_rows=None, **kw):
     """Coordinate-sharded form of `aggregate`: `slice_rows` are this rank's coordinate slice of the
     n gradients; `allreduce(tensor)` sums a small device tensor over the ranks in place.
 
     Per-coordinate rules need no communication. Distance-based rules compute the partial squared
     distances of the slice, all-reduce the n×n matrix, run the (replicated) selection and apply the
-    resulting weights to the slice — the robust analogue of a reduce-scatter."""
+    resulting weights to the slice — the robust analogue of a reduce-scatter.
+
+    `apply_rows` (distance rules only): rows the selected weights are applied to instead of `slice_rows` — used when the
+    distances of the remaining coordinates were computed elsewhere (e.g. during the backward pass) and `allreduce`
+    adds them in, while the aggregate is still wanted over the whole vector."""
     n = len(slice_rows)
     common = dict(update=update, want_out=want_out, out=out)
     if name == "aksel":
@@ -269,13 +281,14 @@ def aggregate_sharded(name, slice_rows, f, allreduce, m=None, update=None, want_
     ws = select(slice_rows, "none", engine=kw.get("engine", "auto"))
     allreduce(ws["dist"])
     device = slice_rows[0].device
+    target = slice_rows if apply_rows is None else apply_rows
     m_eff = n - f - 2 if m is None else m
     if mode == "krum":
         select_only(ws, n, device, "krum", f=f, m=m_eff, neighbors=n - f - 2 if native else n - f - 1, squared=native)
-        return coordwise(slice_rows, "linear", W=ws["W"], theta=1, **common)
+        return coordwise(target, "linear", W=ws["W"], theta=1, **common)
     if mode == "mda":
         select_only(ws, n, device, "mda", f=f, squared=native)
-        return coordwise(slice_rows, "linear", W=ws["W"], theta=1, **common)
+        return coordwise(target, "linear", W=ws["W"], theta=1, **common)
     theta = n - 2 * f - 2
     select_only(ws, n, device, mode, f=f, m=m_eff, squared=native)
-    return coordwise(slice_rows, "averaged_median", beta=theta - 2 * f, upper=native, W=ws["W"], theta=theta, **common)
+    return coordwise(target, "averaged_median", beta=theta - 2 * f, upper=native, W=ws["W"], theta=theta, **common)

@@ -157,7 +157,7 @@ class SSMWEngine:
     def __init__(self, model, dataset, loss, num_workers, f, gar, batch, optimizer="sgd", opt_args=None, byzantine=None,
                  device=None, group=None, use_graphs=True, train_set=None, seed=1234, gar_kwargs=None, sharded=None,
                  channels_last=True, sync="nccl", flag_timeout=5.0, gather_grads=True, fast_bn=True,
-                 split_backward=None, fuse_workers=None, fusion_chains=1, scatter_grads=None):
+                 split_backward=None, fuse_workers=None, fusion_chains=1, scatter_grads=None, overlap_distances=None):
         self.rank = dist.get_rank(group) if dist.is_initialized() else 0
         self.world = dist.get_world_size(group) if dist.is_initialized() else 1
         self.group = group
@@ -238,6 +238,17 @@ class SSMWEngine:
         if fuse_workers and self.workers:
             self._fuse_workers(module, loss_fn, 1 if self.scatter else max(1, min(int(fusion_chains), len(self.workers))))
 
+        # distances during the backward pass (one GPU, distance-based rule, honest local workers): squared distances are sums
+        # over coordinates and the LAST layers' gradients are complete early in the backward pass, so the pairwise kernel
+        # runs on that coordinate range on a side stream while the earlier layers are still being differentiated
+        self._tail_at = None
+        # opt-in: measured +0.6 % on the flagship (75.3 vs 74.8 k images/s) — the persistent pairwise kernel takes every SM
+        # while it runs, so the backward pass it overlaps with stalls; it needs an SM-limited launch to pay off
+        want_overlap = bool(overlap_distances)
+        if (want_overlap and self.fused is not None and self.world == 1 and len(self._chains) == 1 and not self.byzantine
+                and gar in gar_ops.distance_rules()):
+            self._setup_distance_overlap()
+
         # server state (whole vector on rank 0, or this rank's coordinate slice when sharded)
         if self.sharded:
             self.lo, self.hi = self._bounds(self.rank)
@@ -276,6 +287,35 @@ class SSMWEngine:
         self.use_graphs = use_graphs
         self.steps_done = 0
         self.h2d_bytes = 0
+
+    def _setup_distance_overlap(self):
+        """Pick the top-level child whose parameters start the coordinate tail — the first one starting at >= 5 % of d, so
+        that almost all distances leave the critical path while enough of the backward pass (the earlier children) is
+        still to run when its gradients are complete — and hook its backward completion."""
+        module = self.fused.module
+        params = list(module.parameters())
+        offsets = {id(p): off for p, (off, _, _) in zip(params, self.fused.replica.slices)}
+        chosen = None
+        for child in module.children():
+            own = list(child.parameters())
+            if own and 0.05 * self.d <= min(offsets[id(p)] for p in own) <= 0.9 * self.d:
+                chosen = child
+                break
+        if chosen is None:
+            return
+        self._early_stream = torch.cuda.Stream(device=self.device)
+        start = self.fused.add_milestone(chosen, self._early_distances)
+        self._tail_at = (start + 63) // 64 * 64                     # 256-byte aligned split of every row
+        self._early_ws = None
+
+    def _early_distances(self):
+        """Backward-pass hook: the gradients of coordinates [tail_at, d) are in the rows (or in flight on the side
+        streams) — compute their share of the pairwise distances now, off the critical path."""
+        main = torch.cuda.current_stream(self.device)
+        self._early_stream.wait_stream(main)
+        self.fused.join_side_streams(self._early_stream)
+        with torch.cuda.stream(self._early_stream):
+            self._early_ws = gar_ops.select([w.row[self._tail_at:] for w in self.workers], "none", workspace_tag=1)
 
     def _bounds(self, rank):
         lo = min(self.d, rank * self.per)
@@ -421,6 +461,8 @@ class SSMWEngine:
             if len(self._chains) == 1:
                 group, data, target, losses, _ = self._chains[0]
                 group.forward_backward(data, target, losses)
+                if self._tail_at is not None:      # the early-distance branch rejoins here (also closes it inside a graph capture)
+                    torch.cuda.current_stream(self.device).wait_stream(self._early_stream)
                 return
             main = torch.cuda.current_stream(self.device)
             for group, data, target, losses, stream in self._chains:
@@ -506,7 +548,12 @@ class SSMWEngine:
         opt = self.optimizer
         if self.scatter and self.byzantine and self.rows:
             self._attack_slices()
-        if self.sharded:
+        if self._tail_at is not None and self._early_ws is not None:
+            early, self._early_ws = self._early_ws["dist"], None
+            head = [row[:self._tail_at] for row in self.rows]
+            run = lambda **kw: gar_ops.aggregate_sharded(self.gar_name, head, self.f, lambda dist: dist.add_(early), apply_rows=self.rows,
+                                                         **kw, **self.gar_kwargs)
+        elif self.sharded:
             if opt is None:  # empty slice: still take part in the distance all-reduce
                 raise RuntimeError("empty coordinate slice: use fewer ranks than d / 64")
             run = lambda **kw: gar_ops.aggregate_sharded(self.gar_name, self.rows, self.f, self._allreduce, **kw, **self.gar_kwargs)

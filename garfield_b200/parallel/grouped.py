@@ -75,12 +75,18 @@ class _GradSink:
         """grads: a [G, *shape] tensor or a list of G tensors of the parameter's shape."""
         self.pending[index] = grads
 
-    def flush(self):
+    def flush(self, first_index=0):
+        """Scatter the pending gradients of parameters `first_index…` (everything by default) into the rows; a partial
+        flush marks them done so the final one skips them."""
         srcs, offs, sizes = [], [], []
         for index, (p, (off, n, shape)) in enumerate(zip(self.params, self.slices)):
+            if index < first_index:
+                continue
             grads = self.pending.get(index)
             if grads is self.DONE:
                 continue
+            if first_index:
+                self.pending[index] = self.DONE
             for g in range(self.groups):
                 row = self.rows[g]
                 if grads is None:
@@ -99,7 +105,8 @@ class _GradSink:
             _lib.check(_lib.require().gb_multi_copy((ctypes.c_void_p * k)(*srcs), (ctypes.c_uint64 * k)(*offs), (ctypes.c_uint32 * k)(*sizes), k,
                                                     base.data_ptr(), _lib.stream_ptr(base.device)))
             _lib.count((k + 111) // 112)
-        self.pending = {}
+        if not first_index:
+            self.pending = {}
 
 
 class ScatterSink:
@@ -246,7 +253,7 @@ class _GroupedConv(torch.autograd.Function):
                 torch.bmm(gm.transpose(1, 2), cols, out=owner.sink.direct(widx, cout, k))
             owner.sink.put(widx, owner.sink.DONE)
         else:
-            sides = owner.side_streams
+            sides = owner.all_sides()
             cur = torch.cuda.current_stream(x.device) if sides else None
             if sides:
                 for s in sides:
@@ -350,6 +357,7 @@ class GroupedWorkers:
         self.sink = sink(params, replica.slices, replica._view) if sink is not None else _GradSink(params, replica.slices, self.rows, replica._view)
         device = params[0].device
         self.side_streams = [torch.cuda.Stream(device=device) for _ in range(side_streams)] if device.type == "cuda" and side_streams else []
+        self._used_sides = set()
         self.running_tables = {}
         for name, m in self.module.named_modules():
             if isinstance(m, torch.nn.Conv2d):
@@ -415,11 +423,37 @@ class GroupedWorkers:
             return _GroupedLinear.apply(x, lin.weight, lin.bias, owner, widx, bidx)
         return forward
 
+    def add_milestone(self, module, callback):
+        """Call `callback()` during the backward pass as soon as the gradients of `module` and of everything after it in
+        the forward order have been produced (their small gradients are flushed into the rows first). Used to start
+        work on that coordinate range — e.g. pairwise distances — while the rest of the backward pass runs."""
+        params = list(self.module.parameters())
+        first = min(i for i, p in enumerate(params) if any(p is q for q in module.parameters()))
+        self.milestone_offset = self.replica.slices[first][0]
+
+        def hook(_module, _grad_input, _grad_output):
+            self.sink.flush(first_index=first)
+            callback()
+        module.register_full_backward_hook(hook)
+        return self.milestone_offset
+
+    def join_side_streams(self, stream):
+        """Make `stream` wait for the side streams that carried work in this pass (waiting on an untouched stream would
+        tie a graph capture to uncaptured work)."""
+        for k in sorted(self._used_sides):
+            stream.wait_stream(self.side_streams[k])
+
     def next_side(self):
         if not self.side_streams:
             return None
         self._side_rr = (getattr(self, "_side_rr", 0) + 1) % len(self.side_streams)
+        self._used_sides.add(self._side_rr)
         return self.side_streams[self._side_rr]
+
+    def all_sides(self):
+        """Every side stream, marked as used (the per-worker weight-gradient kernels are spread over all of them)."""
+        self._used_sides.update(range(len(self.side_streams)))
+        return self.side_streams
 
     def tf32_matmul(self):
         return _Tf32(torch.backends.cudnn.allow_tf32)   # weight-gradient GEMMs at the precision of the convolutions they replace
@@ -427,6 +461,7 @@ class GroupedWorkers:
     # -- one step ------------------------------------------------------------------------------------------------
     def forward_backward(self, data, target, losses):
         G = self.groups
+        self._used_sides = set()
         self.module.train()
         out = self.module(data)
         if self.loss_kind == "ce":
@@ -439,9 +474,7 @@ class GroupedWorkers:
         per_worker.sum().backward()
         losses.copy_(per_worker.detach())
         if self.side_streams:
-            cur = torch.cuda.current_stream(data.device)
-            for s in self.side_streams:
-                cur.wait_stream(s)
+            self.join_side_streams(torch.cuda.current_stream(data.device))
         self.sink.flush()
 
 

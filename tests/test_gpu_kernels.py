@@ -236,6 +236,33 @@ def test_device_topology_engines_single_gpu():
     dec.close()
 
 
+@pytest.mark.parametrize("gar", ["krum", "bulyan", "brute"])
+def test_engine_distances_during_backward_match_plain_aggregation(gar):
+    """Pairwise distances of the coordinate tail computed from a backward-pass hook + the head afterwards == one call."""
+    import os
+    os.environ.setdefault("GARFIELD_SYNTHETIC_SIZE", "1500")
+    from garfield_b200.parallel.engine import SSMWEngine
+    cuda_lib()
+    finals = {}
+    for overlap in (False, True):
+        for graphs in (False, True):
+            eng = SSMWEngine("cnn", "synthetic-cifar10", "cross-entropy", 8, 1, gar, 8, "sgd", dict(lr=0.02, momentum=0.9),
+                             seed=3, overlap_distances=overlap, use_graphs=graphs)
+            assert (eng._tail_at is not None) == overlap
+            for module in [w.replica.module for w in eng.workers] + [eng.fused.module]:
+                for m in module.modules():
+                    if isinstance(m, (torch.nn.Dropout, torch.nn.Dropout2d)):
+                        m.p = 0.0
+            for i in range(4):
+                eng.step(i)
+            torch.cuda.synchronize()
+            finals[(overlap, graphs)] = eng.master.to_reference_order(eng.flat).clone()
+            eng.close()
+    for key in ((True, False), (True, True), (False, True)):
+        diff = (finals[key] - finals[(False, False)]).abs()
+        assert diff.max().item() < 2e-3 and (diff > 2e-4).float().mean().item() < 1e-3, (key, diff.max().item())
+
+
 def test_msmw_worker_fusion_matches_per_worker_path():
     """ByzSGD engine: one fused pass for a rank's workers (shared median model, channels-last arenas, CUDA graph)
     gives the same server models as the worker-by-worker path."""

@@ -219,3 +219,32 @@ def test_scatter_sink_slices_every_gradient_to_its_owner_cpu():
         assert torch.allclose(got, grads[g], rtol=1e-4, atol=1e-5), g
     untouched = torch.cat([a[:first_row * per] for a in arenas] + [a[(first_row + G) * per:] for a in arenas])
     assert torch.isnan(untouched).all()                      # other ranks' rows are never written
+
+
+def test_milestone_hook_sees_final_tail_gradients_cpu():
+    """add_milestone: when the hook fires, every coordinate from the milestone module's first parameter on is already
+    in the rows (large gradients written in place, small ones by the partial flush) and is not touched again."""
+    torch.manual_seed(5)
+    module = _Net()
+    G, B = 2, 3
+    xs = [torch.randn(B, 3, 8, 8) for _ in range(G)]
+    ys = [torch.randint(0, 5, (B,)) for _ in range(G)]
+    loss_fn = torch.nn.CrossEntropyLoss()
+    flat_model = FlatModel(copy.deepcopy(module), torch.device("cpu"))
+    matrix = torch.full((G, flat_model.numel), float("nan"))
+    group = GroupedWorkers(flat_model, [matrix[g] for g in range(G)], loss_fn, side_streams=0)
+    seen = {}
+    start = group.add_milestone(group.module.b2, lambda: seen.update(tail=matrix[:, start:].clone(), head_nan=bool(torch.isnan(matrix[:, :start]).any())))
+    assert 0 < start < flat_model.numel
+    losses = torch.zeros(G)
+    group.forward_backward(torch.cat(xs), torch.cat(ys), losses)
+    assert "tail" in seen and seen["head_nan"]                      # fired during the pass, before the head was complete
+    assert not torch.isnan(seen["tail"]).any()
+    assert torch.equal(seen["tail"], matrix[:, start:])             # final already at hook time
+    grads, _, _ = _reference(module, xs, ys, loss_fn)
+    for g in range(G):
+        assert torch.allclose(matrix[g], grads[g], rtol=1e-4, atol=1e-5)
+    matrix.fill_(float("nan"))                                      # a second pass behaves the same (pending state is reset)
+    group.forward_backward(torch.cat(xs), torch.cat(ys), losses)
+    for g in range(G):
+        assert torch.allclose(matrix[g], grads[g], rtol=1e-4, atol=1e-5)
