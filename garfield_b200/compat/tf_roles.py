@@ -53,7 +53,7 @@ class Server:
         return [client.get_model(iteration) for client in self._ps_clients]
 
     def write_model(self, flat):
-        self.flat_model.write(torch.from_numpy(np.ascontiguousarray(flat, dtype=np.float32)).to(self.device))
+        self.flat_model.write(torch.from_numpy(np.array(flat, dtype=np.float32, copy=True)).to(self.device))   # gRPC payloads are read-only buffers
 
     def flat(self):
         return self.flat_model.flat.detach().cpu().numpy().copy()
