@@ -34,7 +34,7 @@ class Aggregator_tf:
 
     def aggregate(self, gradients):
         """`gradients`: sequence (or 2-D array) of n flat float32 vectors → aggregated float32 vector."""
-        rows = [torch.as_tensor(np.ascontiguousarray(g, dtype=np.float32)).reshape(-1).to(self.device) for g in gradients]
+        rows = [torch.from_numpy(np.array(g, dtype=np.float32, copy=True)).reshape(-1).to(self.device) for g in gradients]   # inputs may be read-only gRPC buffers
         out = self._rule(gradients=rows, f=self.f)
         return out.detach().cpu().numpy()
 
