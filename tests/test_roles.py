@@ -218,3 +218,44 @@ def test_trainers_run_end_to_end(tmp_path):
                "median", "--num_iter", "3", "--server_attack", "random", "--device", "cpu"], msmw=True)
     learn.main(["--dataset", "mnist", "--model", "convnet", "--num_nodes", "6", "--f", "1", "--gar", "median", "--num_iter", "3",
                 "--attack", "random", "--non_iid", "true", "--device", "cpu"])
+
+
+def test_ssmw_trajectory_matches_plain_torch_simulator():
+    """End to end: the Server/Worker loop follows the same parameter trajectory as a from-scratch simulation of
+    the reference's step (§3.2) written with plain torch only: per-worker forward/backward on a copy of the current model,
+    `torch.cat` of the gradients, `grad * -100` for the Byzantine worker, Multi-Krum restated inline, `optim.SGD` on the
+    unflattened aggregate."""
+    n, f, steps = 7, 1, 5
+    (ps,), workers = deployment(n=n, f=f, attack="reverse", model="cifarnet", dataset="cifar10", loss="cross-entropy", lr=0.05, momentum=0.9,
+                                  weight_decay=5e-4)     # a model without dropout: both sides must be deterministic
+    torch.manual_seed(1234)
+    model = tools.select_model("cifarnet", torch.device("cpu"), "cifar10")
+    with torch.no_grad():
+        for p, q in zip(model.parameters(), ps.flat_model.module.parameters()):
+            p.copy_(q)
+    sim_opt = torch.optim.SGD(model.parameters(), lr=0.05, momentum=0.9, weight_decay=5e-4)
+    loss_fn = torch.nn.CrossEntropyLoss()
+    import copy
+    for it in range(steps):
+        grads = []
+        for k, w in enumerate(workers):
+            replica = copy.deepcopy(model)
+            replica.train()
+            data, target = w.train_set[it % len(w.train_set)]
+            loss_fn(replica(data), target).backward()
+            g = torch.cat([p.grad.reshape(-1) for p in replica.parameters()])
+            grads.append(g * -100 if k >= n - f else g)
+        # Multi-Krum, python semantics: distances (not squared), n-f-1 neighbours, m = n-f-2 best averaged
+        dist = [[(grads[i] - grads[j]).norm().item() if i != j else float("inf") for j in range(n)] for i in range(n)]
+        scores = [sum(sorted(d for j, d in enumerate(dist[i]) if j != i)[:n - f - 1]) for i in range(n)]
+        best = sorted(range(n), key=lambda i: scores[i])[:n - f - 2]
+        aggregate = sum(grads[i] for i in best) / len(best)
+        at = 0
+        for p in model.parameters():
+            p.grad = aggregate[at:at + p.numel()].view_as(p).clone()
+            at += p.numel()
+        sim_opt.step()
+        # the framework's step
+        ps.update_model(aggregators.gars["krum"](gradients=ps.get_gradients(it, n), f=f))
+    want = torch.cat([p.detach().reshape(-1) for p in model.parameters()])
+    torch.testing.assert_close(ps.flat_model.flat, want, rtol=1e-4, atol=1e-6)
