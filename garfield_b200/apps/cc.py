@@ -29,7 +29,7 @@ import torch.distributed as dist
 from . import common
 from ..ops import attacks
 from ..parallel.arena import FlatModel
-from ..utils.trace import Tracer
+from ..utils.tracing import Tracer
 
 
 def parser():

@@ -21,7 +21,7 @@ import torch
 
 from . import common
 from ..utils.checkpoint import save_checkpoint
-from ..utils.trace import Tracer
+from ..utils.tracing import Tracer
 
 
 def build_local(args):

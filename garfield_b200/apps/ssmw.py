@@ -20,7 +20,7 @@ import torch
 
 from . import common
 from ..utils.checkpoint import load_checkpoint, save_checkpoint
-from ..utils.trace import Metrics, Tracer
+from ..utils.tracing import Metrics, Tracer
 
 
 def build_local(args, msmw):

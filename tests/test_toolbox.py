@@ -1,0 +1,144 @@
+"""The `tools` toolbox and the auxiliary subsystems of §5 that run without a GPU:
+registries, key:value parsing, timed contexts, cluster specs, access checks, flat-tensor helpers, tracing and metrics."""
+import json
+import os
+
+import pytest
+import torch
+
+import tools
+from garfield_b200.utils import access, cluster, flat, misc, tracing
+
+
+def test_class_register_and_method_call_replicator():
+    reg = misc.ClassRegister("optimizer")
+    reg.register("sgd", dict)
+    assert list(reg.itemize()) == ["sgd"] and reg.instantiate("sgd", lr=1) == {"lr": 1}
+    with pytest.raises(AssertionError):
+        reg.register("sgd", list)
+    with pytest.raises(tools.UserException) as err:
+        reg.instantiate("adam")
+    assert "available optimizer(s): 'sgd'" in str(err.value)
+    with pytest.raises(tools.UserException) as err:
+        misc.ClassRegister("rule").instantiate("x")
+    assert "no registered rule" in str(err.value)
+    both = misc.MethodCallReplicator([1, 2, 2], [2, 2])
+    assert both.count(2) == [2, 2]
+    with pytest.raises(AssertionError):
+        misc.MethodCallReplicator()
+
+
+def test_parse_keyval_types_defaults_and_errors():
+    got = misc.parse_keyval(["lr:0.1", "nesterov:true", "name:adam", "steps:3"])
+    assert got == {"lr": 0.1, "nesterov": True, "name": "adam", "steps": 3}
+    got = misc.parse_keyval(["lr:1", "flag:0"], defaults={"lr": 0.5, "flag": True, "momentum": 0.9})
+    assert got == {"lr": 1.0, "flag": False, "momentum": 0.9} and isinstance(got["lr"], float)
+    for bad in (["novalue"], ["a:1", "a:2"]):
+        with pytest.raises(tools.UserException):
+            misc.parse_keyval(bad)
+    with pytest.raises(tools.UserException):
+        misc.parse_keyval(["lr:abc"], defaults={"lr": 0.1})
+
+
+def test_misc_helpers():
+    assert list(misc.pairwise([1, 2, 3])) == [(1, 2), (1, 3), (2, 3)]
+    assert misc.fullqual(dict).endswith("dict") and misc.fullqual({}).startswith("instance of")
+    best = misc.line_maximize(lambda x: -(x - 3.0) ** 2, evals=40, start=0.0, delta=1.0)
+    assert abs(best - 3.0) < 0.2
+    is_set, set_it = misc.onetime("probe")
+    assert is_set() is False
+    set_it()
+    assert is_set() is True and misc.onetime("probe")[0]() is True      # named flags are shared
+    assert misc.onetime()[0]() is False                                  # anonymous ones are private
+    with misc.TimedContext("block", "info"):
+        pass
+    assert isinstance(misc.deltatime_format(misc.deltatime_point(), misc.deltatime_point()), str)
+    deps = misc.get_loaded_dependencies()
+    assert any("torch" in str(d) for d in deps)
+
+
+def test_cluster_parsers(tmp_path, monkeypatch):
+    spec = {"ps": ["a:1"], "workers": ["b:2", "c:3"]}
+    assert cluster.cluster_parse(json.dumps(spec)) == spec
+    monkeypatch.setenv("MASTER_ADDR", "10.0.0.1")
+    monkeypatch.setenv("MASTER_PORT", "29000")
+    monkeypatch.setenv("WORLD_SIZE", "3")
+    got = cluster.cluster_parse("torchrun")
+    assert got["ps"] == ["10.0.0.1:29000"] and got["workers"] == ["10.0.0.1:29001", "10.0.0.1:29002", "10.0.0.1:29003"]
+    nodes = tmp_path / "oar"
+    nodes.write_text("n1\nn1\nn2\nn3\nn3\n")
+    monkeypatch.setenv("OAR_FILE_NODES", str(nodes))
+    cluster._cache.clear()
+    assert cluster.cluster_parse("G5k") == {"ps": ["n1:7000"], "workers": ["n2:7000", "n3:7000"]}
+
+
+def test_can_access(tmp_path):
+    f = tmp_path / "d" / "x.txt"
+    f.parent.mkdir()
+    f.write_text("x")
+    assert access.can_access(f, read=True) and access.can_access(tmp_path, read=True, write=True, recurse=True)
+    assert not access.can_access(tmp_path / "missing", read=True)
+
+
+def test_flat_helpers():
+    a, b = torch.arange(6.0).reshape(2, 3), torch.arange(4.0)
+    common = flat.flatten([a, b])
+    assert common.numel() == 10
+    common[0] = 42.0
+    assert a[0, 0].item() == 42.0                      # relinked: the tensors are views of the common buffer
+    p = torch.nn.Parameter(torch.ones(3))
+    assert torch.equal(flat.grad_of(p), torch.zeros(3)) and p.grad is not None
+    samples = [torch.tensor([1.0, 0.0]), torch.tensor([3.0, 0.0]), torch.tensor([2.0, 6.0])]
+    mean, norm, dev, top = flat.compute_avg_dev_max(samples)
+    assert torch.equal(mean, torch.tensor([2.0, 2.0])) and abs(norm - 8 ** 0.5) < 1e-6 and top == 2.0
+    assert abs(dev - ((5 + 5 + 16) / 2) ** 0.5) < 1e-6               # sqrt(sum ||g - mean||^2 / (k - 1))
+    assert flat.compute_avg_dev_max([])[0] is None
+    import io
+    buf = io.BytesIO()
+    flat.pnm(buf, torch.zeros(2, 3))
+    assert buf.getvalue().startswith(b"P5\n2 3 255\n") and len(buf.getvalue()) == len(b"P5\n2 3 255\n") + 6
+
+
+def test_tracer_and_metrics(tmp_path):
+    tracer = tracing.Tracer(enabled=True, device="cpu")
+    for step in range(3):
+        with tracer.phase("gradients", step):
+            sum(range(1000))
+        with tracer.phase("gar", step):
+            pass
+    stats = tracer.summary()
+    assert stats["gradients"]["count"] == 3 and stats["gar"]["mean_ms"] >= 0.0
+    path = tracer.dump_chrome_trace(str(tmp_path / "trace.json"))
+    events = json.load(open(path))["traceEvents"]
+    assert len(events) == 6 and {e["name"] for e in events} == {"gradients", "gar"} and all(e["ph"] == "X" for e in events)
+    off = tracing.Tracer(enabled=False)
+    with off.phase("x"):
+        pass
+    assert off.summary() == {}
+    metrics = tracing.Metrics(str(tmp_path / "m.jsonl"))
+    metrics.log(step=1, loss=0.5)
+    metrics.log(step=2, loss=0.4)
+    rows = [json.loads(line) for line in open(tmp_path / "m.jsonl")]
+    assert [r["step"] for r in rows] == [1, 2] and "time" in rows[0]
+
+
+def test_trace_function_survives_importing_the_tracing_module():
+    """`tools.trace` is the console function whatever the import order (the tracing module has its own name)."""
+    import importlib
+    importlib.import_module("garfield_b200.utils.tracing")
+    import garfield_b200.utils as utils
+    assert callable(utils.trace) and callable(tools.trace)
+
+
+def test_console_contexts_prefix_output(capsys):
+    with tools.Context("train", "info"):
+        with tools.Context("step", None):
+            header = tools.Context._get()[0]
+            print("hello")
+    assert "train" in header and "step" in header and header.index("train") < header.index("step")     # outermost first
+    assert "hello" in capsys.readouterr().out
+    assert tools.Context._get()[0] == "" or "train" not in tools.Context._get()[0]
+    with pytest.raises(AssertionError):
+        tools.Context("x", "no-such-colour")
+    with pytest.raises(tools.UserException):
+        raise tools.UserException("boom")
