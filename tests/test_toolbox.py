@@ -142,3 +142,29 @@ def test_console_contexts_prefix_output(capsys):
         tools.Context("x", "no-such-colour")
     with pytest.raises(tools.UserException):
         raise tools.UserException("boom")
+
+
+def test_application_flag_system(capsys):
+    """§5.6: the trainers' shared parser — reference flag names, real booleans (the reference's `type=bool` is truthy for
+    any non-empty string), `--opt_args` JSON with float casting, sanity asserts."""
+    from garfield_b200.apps import common
+    ap = common.base_parser("t")
+    args = common.finish_args(ap.parse_args(["--dataset", "cifar10", "--batch", "25", "--num_workers", "8", "--fw", "1", "--gar", "krum",
+                                            "--opt_args", '{"lr":"0.2","momentum":"0.9","weight_decay":"0.0005"}', "--bench", "False", "--log", "true"]))
+    assert args.opt_args == {"lr": 0.2, "momentum": 0.9, "weight_decay": 0.0005}
+    assert args.bench is False and args.log is True and args.device in ("cpu", "cuda")
+    assert common.str2bool("0") is False and common.str2bool("no") is False and common.str2bool("yes") is True and common.str2bool(True) is True
+    dec = common.base_parser("t", decentralized=True).parse_args(["--num_nodes", "6", "--f", "1", "--non_iid", "true"])
+    assert dec.num_nodes == 6 and dec.non_iid is True and not hasattr(dec, "num_ps")
+    with pytest.raises(AssertionError):
+        common.finish_args(ap.parse_args(["--opt_args", '{"momentum":"0.9"}']))
+    assert common.pick_gar("median") is __import__("aggregators").gars["median"]
+    with pytest.raises(AssertionError):
+        common.pick_gar("nope")
+    assert common.iterations_per_epoch(8, 25) == 250
+    common.banner(args, 3)
+    out = capsys.readouterr().out
+    assert "SETUP AT NODE 3" in out and "gar:" in out
+    timer = common.StepTimer(True, "cpu")
+    assert timer.run(0, lambda: 5) == 5
+    assert "Training step 0 takes" in capsys.readouterr().out
