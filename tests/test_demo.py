@@ -57,3 +57,21 @@ def test_playground_scripts_run(tmp_path):
                           "--num_workers", "7", "--fw", "1", "--gar", "krum", "--num_iter", "4", "--acc_freq", "2", "--batch", "16"],
                          env=env, capture_output=True, text=True, timeout=240)
     assert out.returncode == 0, out.stderr[-800:]
+
+
+def test_benchmark_scripts_run_on_cpu(tmp_path):
+    """applications/benchmarks: the GAR sweep (CPU device, small budget) writes its JSON, and the collective model-pull
+    benchmark runs in a single process."""
+    import json
+    import os
+    import subprocess
+    import sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    out = tmp_path / "gar.json"
+    run = subprocess.run([sys.executable, os.path.join(root, "applications/benchmarks/gar_bench.py"), "--device", "cpu", "--sweep", "f",
+                          "--gars", "median,krum,native-krum", "--reps", "1", "--max-bytes", "20000000", "--json", str(out)],
+                         capture_output=True, text=True, timeout=600, env=dict(os.environ, CUDA_VISIBLE_DEVICES=""))
+    assert run.returncode == 0, run.stderr[-1500:]
+    rows = json.load(open(out))
+    rows = rows["results"] if isinstance(rows, dict) and "results" in rows else rows
+    assert len(rows) >= 3
