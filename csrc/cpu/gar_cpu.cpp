@@ -37,6 +37,8 @@ int fail(char const* what) {
     return 1;
 }
 
+constexpr int kNetworkRows = 32;   // rows handled by the vectorised sorting-network median
+constexpr int kLanes = 64;         // coordinates sorted together (one cache line of fp32 per row)
 constexpr std::size_t kBlock = 4096;  // coordinates per work item (n rows × 16 KiB fp32 stays in L1/L2)
 
 template <class T>
@@ -66,18 +68,20 @@ void pairwise_sqdist(T const* const* in, int n, std::int64_t d, std::vector<doub
                 T const* gi = in[i];
                 for (int j = i + 1; j < n; ++j, ++p) {
                     T const* gj = in[j];
-                    T s0 = 0, s1 = 0, s2 = 0, s3 = 0;  // 4 lanes of input-precision partial sums
+                    T lane[8] = {0, 0, 0, 0, 0, 0, 0, 0};  // 8 lanes of input-precision partial sums (a SIMD-shaped loop)
                     std::size_t x = x0;
-                    for (; x + 4 <= x1; x += 4) {
-                        T const a = gi[x] - gj[x], c = gi[x + 1] - gj[x + 1];
-                        T const e = gi[x + 2] - gj[x + 2], g = gi[x + 3] - gj[x + 3];
-                        s0 += a * a; s1 += c * c; s2 += e * e; s3 += g * g;
-                    }
+                    for (; x + 8 <= x1; x += 8)
+                        for (int l = 0; l < 8; ++l) {
+                            T const a = gi[x + l] - gj[x + l];
+                            lane[l] += a * a;
+                        }
                     for (; x < x1; ++x) {
                         T const a = gi[x] - gj[x];
-                        s0 += a * a;
+                        lane[0] += a * a;
                     }
-                    acc[p] = static_cast<double>(s0) + static_cast<double>(s1) + static_cast<double>(s2) + static_cast<double>(s3);
+                    double total = 0.0;
+                    for (int l = 0; l < 8; ++l) total += static_cast<double>(lane[l]);
+                    acc[p] = total;
                 }
             }
         }
@@ -208,6 +212,7 @@ int bulyan(T const* const* in, int n, std::int64_t d, int f, int m, T* out) {
     std::size_t const blocks = (static_cast<std::size_t>(d) + kBlock - 1) / kBlock;
     gb::parallel_for(0, blocks, [&](std::size_t lo, std::size_t hi) {
         std::vector<T> tile(static_cast<std::size_t>(theta) * kBlock);
+        std::vector<T> keys(theta <= kNetworkRows ? static_cast<std::size_t>(theta) * kBlock : 0);
         for (std::size_t b = lo; b < hi; ++b) {
             std::size_t const x0 = b * kBlock;
             std::size_t const len = std::min<std::size_t>(static_cast<std::size_t>(d), x0 + kBlock) - x0;
@@ -221,7 +226,54 @@ int bulyan(T const* const* in, int n, std::int64_t d, int f, int m, T* out) {
                     for (std::size_t x = 0; x < len; ++x) row[x] += g[x] * w;
                 }
             }
-            // order statistics run in place along the (strided) θ axis of the tile — no per-coordinate gather
+            if (theta <= kNetworkRows) {
+                // Small θ: two odd-even transposition networks over whole tile rows (contiguous, branch-free min/max and
+                // selects → SIMD): sort the θ mixes per coordinate, take the median row, then sort (|v − med|, v) pairs by
+                // key and average the first β values.
+                for (int round = 0; round < theta; ++round)
+                    for (int k = round & 1; k + 1 < theta; k += 2) {
+                        T* __restrict__ a = tile.data() + static_cast<std::size_t>(k) * kBlock;
+                        T* __restrict__ b = a + kBlock;
+                        for (std::size_t x = 0; x < len; ++x) {
+                            T const u = a[x], v = b[x];
+                            T const lo2 = v < u ? v : u;
+                            T const hi2 = v < u ? u : v;
+                            a[x] = lo2;
+                            b[x] = hi2;
+                        }
+                    }
+                T const* __restrict__ med = tile.data() + static_cast<std::size_t>(theta / 2) * kBlock;
+                for (int k = 0; k < theta; ++k) {
+                    T const* __restrict__ v = tile.data() + static_cast<std::size_t>(k) * kBlock;
+                    T* __restrict__ key = keys.data() + static_cast<std::size_t>(k) * kBlock;
+                    for (std::size_t x = 0; x < len; ++x) key[x] = std::fabs(v[x] - med[x]);
+                }
+                for (int round = 0; round < theta; ++round)
+                    for (int k = round & 1; k + 1 < theta; k += 2) {
+                        T* __restrict__ ka = keys.data() + static_cast<std::size_t>(k) * kBlock;
+                        T* __restrict__ kb = ka + kBlock;
+                        T* __restrict__ va = tile.data() + static_cast<std::size_t>(k) * kBlock;
+                        T* __restrict__ vb = va + kBlock;
+                        for (std::size_t x = 0; x < len; ++x) {
+                            bool const swap = kb[x] < ka[x];
+                            T const k0 = swap ? kb[x] : ka[x], k1 = swap ? ka[x] : kb[x];
+                            T const v0 = swap ? vb[x] : va[x], v1 = swap ? va[x] : vb[x];
+                            ka[x] = k0; kb[x] = k1;
+                            va[x] = v0; vb[x] = v1;
+                        }
+                    }
+                T* __restrict__ dst = out + x0;
+                T const* __restrict__ first = tile.data();
+                for (std::size_t x = 0; x < len; ++x) dst[x] = first[x];
+                for (int k = 1; k < beta; ++k) {
+                    T const* __restrict__ v = tile.data() + static_cast<std::size_t>(k) * kBlock;
+                    for (std::size_t x = 0; x < len; ++x) dst[x] += v[x];
+                }
+                T const denom = static_cast<T>(beta);
+                for (std::size_t x = 0; x < len; ++x) dst[x] /= denom;
+                continue;
+            }
+            // larger θ: order statistics run in place along the (strided) θ axis of the tile — no per-coordinate gather
             gb::StridedView<T> const rounds(tile.data(), {static_cast<std::size_t>(theta), kBlock});
             for (std::size_t x = 0; x < len; ++x) {
                 auto const column = rounds.at(1, x).line(0);
@@ -242,6 +294,46 @@ int bulyan(T const* const* in, int n, std::int64_t d, int f, int m, T* out) {
 template <class T>
 int median(T const* const* in, int n, std::int64_t d, T* out) {
     if (n < 1 || d < 1) return fail("median: expected at least one non-empty gradient");
+    if (n <= kNetworkRows) {
+        // Small n (the usual case): sort kLanes coordinates at once with an odd-even transposition network over the n rows.
+        // Non-finite values become +inf (they sink to the end), the finite count picks element count/2 per coordinate.
+        // Every inner loop runs over a contiguous lane array with branch-free min/max, which the compiler vectorises.
+        std::size_t const groups = (static_cast<std::size_t>(d) + kLanes - 1) / kLanes;
+        gb::parallel_for(0, groups, [&](std::size_t lo, std::size_t hi) {
+            alignas(64) T vals[kNetworkRows][kLanes];
+            alignas(64) int count[kLanes];
+            T const inf = std::numeric_limits<T>::infinity();
+            for (std::size_t g = lo; g < hi; ++g) {
+                std::size_t const x0 = g * kLanes;
+                int const width = static_cast<int>(std::min<std::size_t>(kLanes, static_cast<std::size_t>(d) - x0));
+                for (int l = 0; l < kLanes; ++l) count[l] = 0;
+                for (int i = 0; i < n; ++i) {
+                    T const* row = in[i] + x0;
+                    for (int l = 0; l < width; ++l) {
+                        T const v = row[l];
+                        bool const ok = v - v == T(0);                     // false for NaN and ±inf
+                        vals[i][l] = ok ? v : inf;
+                        count[l] += ok ? 1 : 0;
+                    }
+                    for (int l = width; l < kLanes; ++l) vals[i][l] = inf;
+                }
+                for (int round = 0; round < n; ++round)
+                    for (int i = round & 1; i + 1 < n; i += 2) {
+                        T* __restrict__ a = vals[i];
+                        T* __restrict__ b = vals[i + 1];
+                        for (int l = 0; l < kLanes; ++l) {
+                            T const u = a[l], v = b[l];
+                            T const lo = v < u ? v : u;
+                            T const hi = v < u ? u : v;
+                            a[l] = lo;
+                            b[l] = hi;
+                        }
+                    }
+                for (int l = 0; l < width; ++l) out[x0 + l] = count[l] == 0 ? T(0) : vals[count[l] / 2][l];
+            }
+        }, 64);
+        return 0;
+    }
     gb::parallel_for(0, static_cast<std::size_t>(d), [&](std::size_t lo, std::size_t hi) {
         std::vector<T> column(n);
         for (std::size_t x = lo; x < hi; ++x) {

@@ -15,6 +15,11 @@ ROBUST = ("median", "krum", "bulyan", "brute", "aksel", "trimmed_mean", "average
 ALL = ("average",) + ROBUST
 
 
+# MDA ("brute") is excluded: its ties are structural, not measure-zero — every subset containing the same farthest pair has
+# the same diameter, and the reference breaks such ties by lexicographic order of the subset, i.e. by input order.
+ORDER_FREE = tuple(name for name in ALL if "brute" not in name)
+
+
 def _inputs(seed, n, d, dtype=torch.float32):
     gen = torch.Generator().manual_seed(seed)
     return [torch.randn(d, generator=gen, dtype=dtype) for _ in range(n)]
@@ -25,7 +30,7 @@ def _n_for(name, f):
 
 
 @settings(max_examples=25, deadline=None)
-@given(seed=st.integers(0, 10_000), f=st.integers(1, 2), extra=st.integers(0, 3), d=st.integers(1, 40), name=st.sampled_from(ALL))
+@given(seed=st.integers(0, 10_000), f=st.integers(1, 2), extra=st.integers(0, 3), d=st.integers(1, 40), name=st.sampled_from(ORDER_FREE))
 def test_permutation_invariance(seed, f, extra, d, name):
     """The aggregate does not depend on the order in which the gradients are listed (ties aside: continuous random inputs)."""
     n = _n_for(name, f) + extra
@@ -38,10 +43,11 @@ def test_permutation_invariance(seed, f, extra, d, name):
 
 
 @settings(max_examples=25, deadline=None)
-@given(seed=st.integers(0, 10_000), f=st.integers(1, 2), d=st.integers(1, 40), name=st.sampled_from(ALL),
+@given(seed=st.integers(0, 10_000), f=st.integers(1, 2), d=st.integers(3, 40), name=st.sampled_from(ORDER_FREE),
        scale=st.floats(0.25, 8.0), shift=st.floats(-3.0, 3.0))
 def test_translation_and_positive_scaling_equivariance(seed, f, d, name, scale, shift):
-    """rule(a·g_i + b) = a·rule(g_i) + b for a > 0: distances scale uniformly, order statistics commute with monotone maps."""
+    """rule(a·g_i + b) = a·rule(g_i) + b for a > 0: distances scale uniformly, order statistics commute with monotone maps.
+    (d >= 3: on a line, sums of neighbour distances tie exactly — |a−b| + |b−c| = |a−c| — and rounding then decides.)"""
     n = _n_for(name, f) + 1
     grads = _inputs(seed, n, d, torch.float64)
     rule = aggregators.gars[name]
@@ -81,3 +87,23 @@ def test_average_is_not_robust_but_declares_it():
     out = aggregators.gars["average"](gradients=honest + [torch.full((5,), 1e9)], f=1)
     assert out.abs().max().item() > 1e7
     assert math.isclose(aggregators.gars["average"].influence(honest, [torch.zeros(5)], f=1), 1 / 8)
+
+
+@settings(max_examples=25, deadline=None)
+@given(seed=st.integers(0, 10_000), f=st.integers(1, 2), extra=st.integers(0, 2), d=st.integers(1, 20), name=st.sampled_from(("brute", "native-brute")))
+def test_mda_selects_a_minimum_diameter_subset_in_any_order(seed, f, extra, d, name):
+    """MDA under permutation: the selected subset may change (ties) but it always has the minimum diameter, i.e. the
+    aggregate is the mean of SOME minimum-diameter subset of n - f inputs."""
+    import itertools
+    n = 2 * f + 3 + extra
+    grads = _inputs(seed, n, d, torch.float64)
+    perm = torch.randperm(n, generator=torch.Generator().manual_seed(seed + 1)).tolist()
+    shuffled = [grads[i] for i in perm]
+    out = aggregators.gars[name](gradients=shuffled, f=f)
+
+    def diameter(subset):
+        return max(((shuffled[i] - shuffled[j]) ** 2).sum().item() for i, j in itertools.combinations(subset, 2))
+    subsets = list(itertools.combinations(range(n), n - f))
+    best = min(diameter(s) for s in subsets)
+    candidates = [sum(shuffled[i] for i in s) / len(s) for s in subsets if diameter(s) <= best * (1 + 1e-12)]
+    assert any(torch.allclose(out, c, rtol=1e-9, atol=1e-12) for c in candidates)
