@@ -15,6 +15,7 @@
 // do not depend on the thread count.
 
 #include <algorithm>
+#include <atomic>
 #include <cmath>
 #include <cstdint>
 #include <cstring>
@@ -353,6 +354,100 @@ int median(T const* const* in, int n, std::int64_t d, T* out) {
     return 0;
 }
 
+// Python-semantics coordinate-wise rules on the host, n <= kNetworkRows, with the same SIMD-shaped network as `median`:
+//   rule 0  lower median, NaN-propagating (torch.median)            — aggregators/median.py:31-39
+//   rule 1  f-trimmed mean (arg = f)                                — drop the f smallest / f largest, average the rest
+//   rule 2  mean of the arg = beta values closest to the lower median, ties: lower value first
+// Returns 0, or 2 when a column held a value the fast path does not reproduce bit-for-bit semantics for (NaN for rule 1,
+// any non-finite for rule 2): the caller then recomputes with the reference formulation. 3 = n too large.
+template <class T>
+int coordwise_host(T const* const* in, int n, std::int64_t d, int rule, int arg, T* out) {
+    if (n < 1 || d < 1) return fail("coordwise: expected at least one non-empty gradient");
+    if (rule < 0 || rule > 2) return fail("coordwise: unknown rule");
+    if (rule == 1 && (arg < 0 || n < 2 * arg + 1)) return fail("coordwise: need 0 <= f and n >= 2f+1");
+    if (rule == 2 && (arg < 1 || arg > n)) return fail("coordwise: need 1 <= beta <= n");
+    if (n > kNetworkRows) return 3;
+    std::atomic<int> odd{0};
+    std::size_t const groups = (static_cast<std::size_t>(d) + kLanes - 1) / kLanes;
+    gb::parallel_for(0, groups, [&](std::size_t lo, std::size_t hi) {
+        alignas(64) T vals[kNetworkRows][kLanes];
+        alignas(64) T keys[kNetworkRows][kLanes];
+        alignas(64) int nans[kLanes];
+        T const inf = std::numeric_limits<T>::infinity();
+        T const nan = std::numeric_limits<T>::quiet_NaN();
+        int const mid = (n - 1) / 2;
+        for (std::size_t g = lo; g < hi; ++g) {
+            std::size_t const x0 = g * kLanes;
+            int const width = static_cast<int>(std::min<std::size_t>(kLanes, static_cast<std::size_t>(d) - x0));
+            int strange = 0;
+            for (int l = 0; l < kLanes; ++l) nans[l] = 0;
+            for (int i = 0; i < n; ++i) {
+                T const* row = in[i] + x0;
+                for (int l = 0; l < width; ++l) {
+                    T const v = row[l];
+                    bool const is_nan = v != v;
+                    vals[i][l] = is_nan ? inf : v;             // NaN sorts last, like torch.sort
+                    nans[l] += is_nan ? 1 : 0;
+                    strange |= (v - v == T(0)) ? 0 : 1;         // NaN or ±inf
+                }
+                for (int l = width; l < kLanes; ++l) vals[i][l] = T(0);
+            }
+            for (int round = 0; round < n; ++round)
+                for (int i = round & 1; i + 1 < n; i += 2) {
+                    T* __restrict__ a = vals[i];
+                    T* __restrict__ b = vals[i + 1];
+                    for (int l = 0; l < kLanes; ++l) {
+                        T const u = a[l], v = b[l];
+                        T const small = v < u ? v : u;
+                        T const large = v < u ? u : v;
+                        a[l] = small;
+                        b[l] = large;
+                    }
+                }
+            if (rule == 0) {
+                for (int l = 0; l < width; ++l) out[x0 + l] = nans[l] > 0 ? nan : vals[mid][l];
+            } else if (rule == 1) {
+                int any_nan = 0;
+                for (int l = 0; l < width; ++l) any_nan |= nans[l];
+                if (any_nan) odd.store(1, std::memory_order_relaxed);
+                T* __restrict__ dst = out + x0;
+                T const denom = static_cast<T>(n - 2 * arg);
+                for (int l = 0; l < width; ++l) dst[l] = vals[arg][l];
+                for (int k = arg + 1; k < n - arg; ++k)
+                    for (int l = 0; l < width; ++l) dst[l] += vals[k][l];
+                for (int l = 0; l < width; ++l) dst[l] /= denom;
+            } else {
+                if (strange) odd.store(1, std::memory_order_relaxed);
+                for (int k = 0; k < n; ++k)
+                    for (int l = 0; l < kLanes; ++l) keys[k][l] = std::fabs(vals[k][l] - vals[mid][l]);
+                // stable (strict-comparison, adjacent-exchange) sort by distance to the median: equal keys keep the
+                // ascending value order of the first sort, i.e. "ties: lower value first"
+                for (int round = 0; round < n; ++round)
+                    for (int i = round & 1; i + 1 < n; i += 2) {
+                        T* __restrict__ ka = keys[i];
+                        T* __restrict__ kb = keys[i + 1];
+                        T* __restrict__ va = vals[i];
+                        T* __restrict__ vb = vals[i + 1];
+                        for (int l = 0; l < kLanes; ++l) {
+                            bool const swap = kb[l] < ka[l];
+                            T const k0 = swap ? kb[l] : ka[l], k1 = swap ? ka[l] : kb[l];
+                            T const v0 = swap ? vb[l] : va[l], v1 = swap ? va[l] : vb[l];
+                            ka[l] = k0; kb[l] = k1;
+                            va[l] = v0; vb[l] = v1;
+                        }
+                    }
+                T* __restrict__ dst = out + x0;
+                T const denom = static_cast<T>(arg);
+                for (int l = 0; l < width; ++l) dst[l] = vals[0][l];
+                for (int k = 1; k < arg; ++k)
+                    for (int l = 0; l < width; ++l) dst[l] += vals[k][l];
+                for (int l = 0; l < width; ++l) dst[l] /= denom;
+            }
+        }
+    }, 64);
+    return odd.load() ? 2 : 0;
+}
+
 template <class T>
 int brute(T const* const* in, int n, std::int64_t d, int f, T* out) {
     if (n < 1 || d < 1) return fail("brute: expected at least one non-empty gradient");
@@ -435,6 +530,8 @@ GB_API int gb_cpu_bulyan_f32(float const* const* in, int n, int64_t d, int f, in
 GB_API int gb_cpu_bulyan_f64(double const* const* in, int n, int64_t d, int f, int m, double* out) { return guarded([&] { return bulyan(in, n, d, f, m, out); }); }
 GB_API int gb_cpu_median_f32(float const* const* in, int n, int64_t d, float* out) { return guarded([&] { return median(in, n, d, out); }); }
 GB_API int gb_cpu_median_f64(double const* const* in, int n, int64_t d, double* out) { return guarded([&] { return median(in, n, d, out); }); }
+GB_API int gb_cpu_coordwise_f32(float const* const* in, int n, int64_t d, int rule, int arg, float* out) { return guarded([&] { return coordwise_host(in, n, d, rule, arg, out); }); }
+GB_API int gb_cpu_coordwise_f64(double const* const* in, int n, int64_t d, int rule, int arg, double* out) { return guarded([&] { return coordwise_host(in, n, d, rule, arg, out); }); }
 GB_API int gb_cpu_brute_f32(float const* const* in, int n, int64_t d, int f, float* out) { return guarded([&] { return brute(in, n, d, f, out); }); }
 GB_API int gb_cpu_brute_f64(double const* const* in, int n, int64_t d, int f, double* out) { return guarded([&] { return brute(in, n, d, f, out); }); }
 GB_API int gb_cpu_pairwise_sqdist_f32(float const* const* in, int n, int64_t d, double* out) { return guarded([&] { return sqdist_matrix(in, n, d, out); }); }

@@ -49,3 +49,24 @@ def native_cpu():
     except Exception:
         return None
     return _native if _native.available() else None
+
+
+def host_distances(gradients, squared):
+    """n×n list-of-lists of (squared) L2 distances with +inf on the diagonal and for non-finite values — from the C++ host
+    library (blocked, multi-threaded, one pass) when it can take the inputs, else the direct torch formulation."""
+    import math
+    from . import _host
+    native = native_cpu()
+    if (native is not None and isinstance(gradients, (list, tuple)) and native.supports(gradients)
+            and all(g.dim() == 1 and g.is_contiguous() for g in gradients)):
+        n = len(gradients)
+        matrix = native.pairwise_sqdist(list(gradients)).tolist()
+        for i in range(n):
+            for j in range(n):
+                v = matrix[i][j]
+                if i == j or not math.isfinite(v):
+                    matrix[i][j] = math.inf
+                elif not squared:
+                    matrix[i][j] = math.sqrt(v)
+        return matrix
+    return _host.pairwise_distances(gradients, squared=squared)

@@ -12,11 +12,11 @@ subset per thread) with a block-wide lexicographic arg-min — no host combinati
 
 from . import register
 from . import _host
-from ._common import basic_list_error, byz_error, on_device, device_ops, native_cpu
+from ._common import basic_list_error, byz_error, on_device, device_ops, native_cpu, host_distances
 
 
 def _selection(gradients, f, native):
-    dist = _host.pairwise_distances(gradients, squared=native)
+    dist = host_distances(gradients, squared=native)
     if native:  # non-finite distances count as the largest representable value, never skipped
         big = float("1.79e308")
         dist = [[big if v == float("inf") else v for v in row] for row in dist]

@@ -14,17 +14,23 @@ coordinate in registers (W·x) and runs the sorting network on them.
 
 import math
 
+import torch
+
 from . import register
 from . import _host
-from ._common import basic_list_error, byz_error, on_device, device_ops, native_cpu
+from ._common import basic_list_error, byz_error, on_device, device_ops, native_cpu, host_distances
 
 
 def _host_bulyan(gradients, f, m, native):
-    dist = _host.pairwise_distances(gradients, squared=native)
+    dist = host_distances(gradients, squared=native)
     rounds = (_host.bulyan_rounds_native if native else _host.bulyan_rounds_python)(dist, f, m)
     weights = _host.weights_from_rounds(rounds, len(gradients), dtype=gradients[0].dtype)
     selected = _host.apply_weights(gradients, weights)
-    return _host.bulyan_phase2(selected, f, upper=native)
+    fast = None
+    backend = native_cpu()
+    if not native and backend is not None and selected.device.type == "cpu" and selected.dtype in (torch.float32, torch.float64):
+        fast = backend.coordwise(list(selected.unbind(0)), "averaged_median", selected.shape[0] - 2 * f)   # lower median, β = θ − 2f
+    return fast if fast is not None else _host.bulyan_phase2(selected, f, upper=native)
 
 
 def aggregate(gradients, f, m=None, **kwargs):

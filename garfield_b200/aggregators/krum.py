@@ -14,14 +14,14 @@ import math
 
 from . import register
 from . import _host
-from ._common import basic_list_error, byz_error, on_device, device_ops, native_cpu
+from ._common import basic_list_error, byz_error, on_device, device_ops, native_cpu, host_distances
 
 
 def _selection(gradients, f, m, native):
     n = len(gradients)
     if m is None:
         m = n - f - 2
-    dist = _host.pairwise_distances(gradients, squared=native)
+    dist = host_distances(gradients, squared=native)
     return _host.krum_selection(dist, f, m, n - f - 2 if native else n - f - 1), m
 
 

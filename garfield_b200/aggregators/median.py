@@ -19,11 +19,22 @@ from . import _host
 from ._common import basic_list_error, on_device, device_ops, native_cpu
 
 
+def _host_fast(gradients, rule, arg=0):
+    """The vectorised C++ kernel for CPU fp32/fp64 lists (None when unavailable or when it declines the input)."""
+    native = native_cpu()
+    if native is None or not isinstance(gradients, (list, tuple)) or not native.supports(gradients):
+        return None
+    if any(g.dim() != 1 or not g.is_contiguous() for g in gradients):
+        return None
+    return native.coordwise(list(gradients), rule, arg)
+
+
 def aggregate(gradients, **kwargs):
     """Coordinate-wise (lower) median."""
     if on_device(gradients):
         return device_ops().coordwise(gradients, "median_lower")
-    return _host.median_lower(_host.as_matrix(gradients))
+    fast = _host_fast(gradients, "median_lower")
+    return fast if fast is not None else _host.median_lower(_host.as_matrix(gradients))
 
 
 def aggregate_native(gradients, **kwargs):
@@ -40,7 +51,8 @@ def aggregate_trimmed(gradients, f, **kwargs):
     """Coordinate-wise f-trimmed mean."""
     if on_device(gradients):
         return device_ops().coordwise(gradients, "trimmed_mean", f=f)
-    return _host.trimmed_mean(_host.as_matrix(gradients), f)
+    fast = _host_fast(gradients, "trimmed_mean", f)
+    return fast if fast is not None else _host.trimmed_mean(_host.as_matrix(gradients), f)
 
 
 def aggregate_avgmed(gradients, f, beta=None, **kwargs):
@@ -49,7 +61,8 @@ def aggregate_avgmed(gradients, f, beta=None, **kwargs):
         beta = len(gradients) - f
     if on_device(gradients):
         return device_ops().coordwise(gradients, "averaged_median", beta=beta)
-    return _host.averaged_median(_host.as_matrix(gradients), beta)
+    fast = _host_fast(gradients, "averaged_median", beta)
+    return fast if fast is not None else _host.averaged_median(_host.as_matrix(gradients), beta)
 
 
 def check(gradients, **kwargs):

@@ -20,7 +20,7 @@ import torch
 
 from .. import _build
 
-__all__ = ["available", "supports", "krum", "bulyan", "median", "brute", "pairwise_sqdist",
+__all__ = ["available", "supports", "krum", "bulyan", "median", "brute", "pairwise_sqdist", "coordwise",
            "combinations", "num_threads", "lib"]
 
 _lib = None
@@ -67,6 +67,8 @@ def _declare(h):
     h.gb_combinations_seek.argtypes = [ctypes.c_uint, ctypes.c_uint, ctypes.c_uint64, ctypes.POINTER(ctypes.c_int)]
     h.gb_combinations_next.argtypes = [ctypes.c_uint, ctypes.c_uint, ctypes.POINTER(ctypes.c_int)]
     h.gb_cpu_parallel_for_probe.argtypes = [i64, i64, vp]
+    for suffix in ("f32", "f64"):
+        getattr(h, "gb_cpu_coordwise_" + suffix).argtypes = [pp, i32, i64, i32, i32, vp]
     h.gb_cpu_axis_nth_f32.argtypes = [vp, i32, ctypes.POINTER(ctypes.c_int64), i32, i64, vp]
     h.gb_mreg_create.restype = vp
     h.gb_mreg_create.argtypes = [i32, i64, i32]
@@ -154,6 +156,23 @@ def _brute(inputs, f):
     if inputs[0].is_cuda:
         return _device(inputs).mda(_validate(inputs), f=f, squared=True)
     return _call("gb_cpu_brute", inputs, int(f))
+
+
+_COORDWISE_RULES = {"median_lower": 0, "trimmed_mean": 1, "averaged_median": 2}
+
+
+def coordwise(inputs, rule, arg=0):
+    """Python-semantics coordinate-wise rules on CPU tensors through the vectorised host kernel (n <= 32):
+    `median_lower` (torch.median semantics), `trimmed_mean` (arg = f), `averaged_median` (arg = beta).
+    Returns None when the fast path declines (too many rows, or a column with NaN / non-finite values whose
+    reference semantics it does not reproduce) — the caller then uses the reference formulation."""
+    inputs = _validate(inputs)
+    out = torch.empty_like(inputs[0])
+    fn = getattr(lib(), "gb_cpu_coordwise_" + _suffix(inputs[0]))
+    rc = fn(_rows(inputs), len(inputs), inputs[0].numel(), _COORDWISE_RULES[rule], int(arg), out.data_ptr())
+    if rc == 1:
+        raise ValueError(lib().gb_cpu_last_error().decode())
+    return out if rc == 0 else None
 
 
 krum = types.SimpleNamespace(aggregate=_krum)

@@ -39,6 +39,12 @@ GB_API int gb_cpu_bulyan_f64(double const* const* in, int n, int64_t d, int f, i
 /* Non-finite-resilient coordinate-wise median. ref: py_median/median.cpp:42-77 */
 GB_API int gb_cpu_median_f32(float const* const* in, int n, int64_t d, float* out);
 GB_API int gb_cpu_median_f64(double const* const* in, int n, int64_t d, double* out);
+/* Python-semantics coordinate-wise rules for n <= 32 (vectorised sorting network): rule 0 = lower median, NaN-propagating
+ * (ref: aggregators/median.py:31-39); 1 = arg-trimmed mean; 2 = mean of the arg values closest to the lower median
+ * (ref: tensorflow_impl/rsrcs/aggregators/averaged-median.py:30-67). Returns 0; 1 error; 2 = a column held NaN (rule 1) or a
+ * non-finite value (rule 2): recompute with the reference formulation; 3 = n too large for the network. */
+GB_API int gb_cpu_coordwise_f32(float const* const* in, int n, int64_t d, int rule, int arg, float* out);
+GB_API int gb_cpu_coordwise_f64(double const* const* in, int n, int64_t d, int rule, int arg, double* out);
 /* Brute / MDA. ref: py_brute/brute.cpp:47-113 */
 GB_API int gb_cpu_brute_f32(float const* const* in, int n, int64_t d, int f, float* out);
 GB_API int gb_cpu_brute_f64(double const* const* in, int n, int64_t d, int f, double* out);

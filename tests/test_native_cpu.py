@@ -152,3 +152,42 @@ def test_multiregister_consume_mode_is_a_queue():
     reg.close()
     th.join()
     assert got == [float(v) for v in range(20)]
+
+
+@pytest.mark.parametrize("dtype", [torch.float32, torch.float64])
+@pytest.mark.parametrize("n,d", [(1, 5), (2, 70), (7, 129), (8, 1000), (23, 333), (32, 64), (33, 50)])
+def test_host_coordwise_kernel_matches_the_reference_formulations(n, d, dtype):
+    """gb_cpu_coordwise (vectorised network) against aggregators/_host.py: lower median with NaN propagation and ±inf,
+    trimmed mean, mean-around-median; inputs it declines (NaN / non-finite columns, n > 32) must return None."""
+    from garfield_b200.aggregators import _host
+    gen = torch.Generator().manual_seed(n * 1000 + d)
+    rows = [torch.randn(d, generator=gen, dtype=dtype) for _ in range(n)]
+    matrix = torch.stack(rows)
+    got = native.coordwise(rows, "median_lower")
+    if n > 32:
+        assert got is None
+        return
+    assert torch.equal(got, _host.median_lower(matrix))
+    f = (n - 1) // 2 if n < 5 else 2
+    assert torch.allclose(native.coordwise(rows, "trimmed_mean", f), _host.trimmed_mean(matrix, f), rtol=1e-6, atol=1e-7)
+    for beta in {1, max(1, n - f), n}:
+        assert torch.allclose(native.coordwise(rows, "averaged_median", beta), _host.averaged_median(matrix, beta), rtol=1e-6, atol=1e-7), beta
+    if n >= 3 and d >= 5:
+        rows[0][1] = float("nan"); rows[1][2] = float("inf"); rows[2][3] = float("-inf"); rows[n - 1][4] = float("nan")
+        matrix = torch.stack(rows)
+        got, want = native.coordwise(rows, "median_lower"), _host.median_lower(matrix)
+        assert torch.equal(torch.isnan(got), torch.isnan(want)) and torch.equal(got[~torch.isnan(got)], want[~torch.isnan(want)])
+        assert native.coordwise(rows, "trimmed_mean", 1) is None and native.coordwise(rows, "averaged_median", 2) is None
+    with pytest.raises(ValueError):
+        native.coordwise(rows, "trimmed_mean", n)
+
+
+def test_registry_cpu_rules_use_the_host_kernel_and_fall_back():
+    import aggregators
+    rows = [torch.randn(257) for _ in range(9)]
+    matrix = torch.stack(rows)
+    assert torch.equal(aggregators.gars["median"](gradients=rows, f=1), matrix.median(0).values)
+    rows[3][5] = float("nan")
+    out = aggregators.gars["trimmed_mean"](gradients=rows, f=1)           # NaN column: reference formulation takes over
+    want = torch.stack(rows).sort(0).values[1:8].mean(0)
+    assert torch.allclose(out, want, equal_nan=True)
