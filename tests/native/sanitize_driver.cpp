@@ -33,6 +33,12 @@ int main() {
     CHECK(gb_cpu_krum_f32(ptrs.data(), n, d, f, n - f - 2, out.data()) == 0);
     CHECK(gb_cpu_bulyan_f32(ptrs.data(), n, d, f, n - f - 2, out.data()) == 0);
     CHECK(gb_cpu_brute_f32(ptrs.data(), n, d, f, out.data()) == 0);
+    CHECK(gb_cpu_coordwise_f32(ptrs.data(), n, d, 0, 0, out.data()) == 0);                 // lower median: NaN columns are exact
+    CHECK(std::isnan(out[17]) && !std::isnan(out[16]));
+    CHECK(gb_cpu_coordwise_f32(ptrs.data(), n, d, 1, f, out.data()) == 2);                 // trimmed mean declines the NaN column
+    CHECK(gb_cpu_coordwise_f32(ptrs.data(), n, d, 2, n - f, out.data()) == 2);             // and so does mean-around-median
+    CHECK(gb_cpu_coordwise_f32(ptrs.data() + 6, 5, d, 1, 1, out.data()) == 0);             // rows 6..10 are finite
+    CHECK(gb_cpu_coordwise_f32(ptrs.data() + 6, 5, d, 2, 3, out.data()) == 0);
     std::vector<double> dist(static_cast<size_t>(n) * n);
     CHECK(gb_cpu_pairwise_sqdist_f32(ptrs.data(), n, d, dist.data()) == 0);
     int const sel[3] = {0, 4, 9};
