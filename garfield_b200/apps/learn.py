@@ -129,6 +129,34 @@ def run_rpc(args):
     rpc.shutdown()
 
 
+def run_spmd(args):
+    """One process per GPU (torchrun): the device-resident `DecentralizedEngine` (node k lives on rank k mod N; gradient
+    aggregation, the non-iid agreement rounds and the contract step are fused gather + GAR kernels over peer memory)."""
+    import os
+    import torch
+    import torch.distributed as dist
+    from ..parallel.topologies import DecentralizedEngine
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    if int(os.environ.get("WORLD_SIZE", "1")) > 1 and not dist.is_initialized():
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    byz = {args.num_nodes - 1 - k: args.attack for k in range(args.f)} if args.attack else {}
+    engine = DecentralizedEngine(args.model, args.dataset, args.loss, args.num_nodes, args.f, args.gar, args.batch, optimizer=args.optimizer,
+                                 opt_args=args.opt_args, byzantine=byz, non_iid=args.non_iid)
+    start = time.time()
+    for i in range(args.num_iter):
+        loss = engine.step(i)
+        if args.log and i % 10 == 0 and engine.rank == 0:
+            print("Iteration {} loss {}".format(i, loss.item()))
+    torch.cuda.synchronize()
+    if engine.rank == 0:
+        elapsed = time.time() - start
+        print("{} iterations in {:.3f} s: {:.1f} images/s".format(args.num_iter, elapsed, args.num_iter * args.num_nodes * args.batch / elapsed))
+    engine.close()
+    if dist.is_initialized():
+        dist.destroy_process_group()
+
+
 def main(argv=None):
     args = common.finish_args(common.base_parser("LEARN (decentralized) on garfield-b200\n" + common.__doc__, decentralized=True).parse_args(argv))
     assert args.num_nodes >= 1 and args.f * 2 < args.num_nodes
@@ -136,4 +164,6 @@ def main(argv=None):
     common.seed_everything()
     if args.transport == "rpc":
         return run_rpc(args)
+    if args.transport == "spmd":
+        return run_spmd(args)
     return run_local(args)

@@ -144,18 +144,26 @@ def run_rpc(args, msmw):
     rpc.shutdown()
 
 
-def run_spmd(args):
-    """One process per GPU (torchrun): the device-resident SSMW engine."""
+def run_spmd(args, msmw=False):
+    """One process per GPU (torchrun): the device-resident engines — `SSMWEngine` (AggregaThor), or `MSMWEngine` (ByzSGD:
+    `num_ps` replicated servers, the same rule aggregates gradients and — between servers — models, as in the reference's
+    ByzSGD/trainer.py:237-244)."""
     import os
     import torch.distributed as dist
-    from ..parallel.engine import SSMWEngine
     local = int(os.environ.get("LOCAL_RANK", "0"))
     torch.cuda.set_device(local)
     if int(os.environ.get("WORLD_SIZE", "1")) > 1 and not dist.is_initialized():
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     byz = {args.num_workers - 1 - k: args.attack for k in range(args.fw)} if args.attack else {}
-    engine = SSMWEngine(args.model, args.dataset, args.loss, args.num_workers, args.fw, args.gar, args.batch, args.optimizer,
-                        args.opt_args, byzantine=byz)
+    if msmw and args.num_ps > 1:
+        from ..parallel.topologies import MSMWEngine
+        byz_ps = {args.num_ps - 1 - k: args.server_attack for k in range(args.fps)} if args.server_attack else {}
+        engine = MSMWEngine(args.model, args.dataset, args.loss, args.num_workers, args.num_ps, args.fw, args.fps, args.gar, args.batch,
+                            mar=args.gar, optimizer=args.optimizer, opt_args=args.opt_args, byzantine_workers=byz, byzantine_servers=byz_ps)
+    else:
+        from ..parallel.engine import SSMWEngine
+        engine = SSMWEngine(args.model, args.dataset, args.loss, args.num_workers, args.fw, args.gar, args.batch, args.optimizer,
+                            args.opt_args, byzantine=byz)
     start = time.time()
     for i in range(args.num_iter):
         loss = engine.step(i)
@@ -182,6 +190,6 @@ def main(argv=None, msmw=False):
     if args.transport == "rpc":
         return run_rpc(args, msmw)
     if args.transport == "spmd":
-        return run_spmd(args)
+        return run_spmd(args, msmw)
     servers, _ = build_local(args, msmw)
     return server_loop(args, servers, msmw)

@@ -168,3 +168,54 @@ def test_application_flag_system(capsys):
     timer = common.StepTimer(True, "cpu")
     assert timer.run(0, lambda: 5) == 5
     assert "Training step 0 takes" in capsys.readouterr().out
+
+
+def test_spmd_transport_wires_the_device_engines(monkeypatch):
+    """`--transport spmd` hands the trainers' flags to the right device engine (checked with stand-in engines: the real
+    ones need a GPU and are covered by the GPU tests)."""
+    import torch
+    from garfield_b200.apps import learn, ssmw
+    from garfield_b200.parallel import engine as engine_mod, topologies
+    made = []
+
+    class Fake:
+        rank = 0
+
+        def __init__(self, *args, **kwargs):
+            made.append((type(self).__name__, args, kwargs))
+            self.steps = 0
+
+        def step(self, i):
+            self.steps += 1
+            return torch.zeros(())
+
+        def close(self):
+            made.append(("closed", self.steps))
+
+    monkeypatch.setattr(engine_mod, "SSMWEngine", type("SSMWEngine", (Fake,), {}))
+    monkeypatch.setattr(topologies, "MSMWEngine", type("MSMWEngine", (Fake,), {}))
+    monkeypatch.setattr(topologies, "DecentralizedEngine", type("DecentralizedEngine", (Fake,), {}))
+    monkeypatch.setattr(torch.cuda, "set_device", lambda index: None)
+    monkeypatch.setattr(torch.cuda, "synchronize", lambda *a: None)
+    monkeypatch.delenv("WORLD_SIZE", raising=False)
+    common_flags = ["--dataset", "cifar10", "--model", "resnet50", "--loss", "cross-entropy", "--batch", "25", "--gar", "krum", "--num_iter", "3",
+                    "--transport", "spmd", "--opt_args", '{"lr":"0.2","momentum":"0.9"}']
+    ssmw.main(common_flags + ["--num_workers", "8", "--fw", "1", "--attack", "reverse"], msmw=False)
+    name, args, kwargs = made[0]
+    assert name == "SSMWEngine" and args[:7] == ("resnet50", "cifar10", "cross-entropy", 8, 1, "krum", 25)
+    assert args[8] == {"lr": 0.2, "momentum": 0.9} and kwargs["byzantine"] == {7: "reverse"} and made[1] == ("closed", 3)
+    made.clear()
+    ssmw.main(common_flags + ["--num_workers", "5", "--fw", "1", "--num_ps", "3", "--fps", "1", "--attack", "reverse", "--server_attack", "random"],
+              msmw=True)
+    name, args, kwargs = made[0]
+    assert name == "MSMWEngine" and args == ("resnet50", "cifar10", "cross-entropy", 5, 3, 1, 1, "krum", 25)
+    assert kwargs["mar"] == "krum" and kwargs["byzantine_workers"] == {4: "reverse"} and kwargs["byzantine_servers"] == {2: "random"}
+    made.clear()
+    ssmw.main(common_flags + ["--num_workers", "5", "--fw", "1"], msmw=True)          # one server: ByzSGD degenerates to SSMW
+    assert made[0][0] == "SSMWEngine" and made[0][2]["byzantine"] == {}
+    made.clear()
+    learn.main(["--dataset", "cifar10", "--model", "vgg16", "--loss", "cross-entropy", "--batch", "25", "--gar", "median", "--num_iter", "2",
+                "--transport", "spmd", "--num_nodes", "8", "--f", "1", "--non_iid", "true", "--attack", "lie"])
+    name, args, kwargs = made[0]
+    assert name == "DecentralizedEngine" and args == ("vgg16", "cifar10", "cross-entropy", 8, 1, "median", 25)
+    assert kwargs["byzantine"] == {7: "lie"} and kwargs["non_iid"] is True and made[1] == ("closed", 2)
