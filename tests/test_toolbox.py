@@ -219,3 +219,33 @@ def test_spmd_transport_wires_the_device_engines(monkeypatch):
     name, args, kwargs = made[0]
     assert name == "DecentralizedEngine" and args == ("vgg16", "cifar10", "cross-entropy", 8, 1, "median", 25)
     assert kwargs["byzantine"] == {7: "lie"} and kwargs["non_iid"] is True and made[1] == ("closed", 2)
+
+
+def test_plugin_loader_and_interactive_console(tmp_path, monkeypatch, capsys):
+    """`tools.import_directory` (the mechanism behind the auto-importing registries) loads every module of a directory,
+    exports `__all__`, and survives a broken plugin; `tools.interactive` is a REPL over the caller's scope."""
+    (tmp_path / "alpha.py").write_text("__all__ = ['answer']\nanswer = 42\nhidden = 1\n")
+    (tmp_path / "beta.py").write_text("def shout():\n    return 'b'\n_private = 0\n")
+    (tmp_path / "broken.py").write_text("raise RuntimeError('boom')\n")
+    (tmp_path / "__init__.py").write_text("")
+    (tmp_path / "notes.txt").write_text("ignored")
+    scope = {"__name__": "plugins_under_test"}
+    tools.import_directory(tmp_path, scope)
+    assert scope["answer"] == 42 and "hidden" not in scope and scope["shout"]() == "b" and "_private" not in scope
+    capsys.readouterr()                                                              # the failure is reported on the console, not raised
+    import sys
+    assert "plugins_under_test.alpha" in sys.modules and "plugins_under_test.broken" not in sys.modules
+    for name in ("plugins_under_test.alpha", "plugins_under_test.beta"):
+        sys.modules.pop(name, None)
+
+    lines = iter(["result.append(seed + 1)"])
+
+    def fake_input(prompt=""):
+        try:
+            return next(lines)
+        except StopIteration:
+            raise EOFError
+    monkeypatch.setattr("builtins.input", fake_input)
+    result, seed = [], 6
+    misc.interactive()
+    assert result == [7]
