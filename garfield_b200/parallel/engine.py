@@ -343,7 +343,8 @@ class SSMWEngine:
                 arenas = [self.grad_arena.peer(r) for r in range(self.world)]
                 bounds = [self._bounds(r) for r in range(self.world)]
                 first, per = self.rank * self.max_local, self.per
-                sink = lambda params, slices, view_of: ScatterSink(params, slices, view_of, G, arenas, first, per, bounds)
+                rank = self.rank
+                sink = lambda params, slices, view_of: ScatterSink(params, slices, view_of, G, arenas, first, per, bounds, rank)
             group = GroupedWorkers(replica, [w.row for w in self.workers[lo:hi]], loss_fn, sink=sink)
             stream = torch.cuda.Stream(device=self.device) if chains > 1 else None
             self._chains.append((group, data[lo * b:hi * b], target[lo * t:hi * t], self._group_losses[lo:hi], stream))

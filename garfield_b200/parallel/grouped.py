@@ -75,6 +75,13 @@ class _GradSink:
         """grads: a [G, *shape] tensor or a list of G tensors of the parameter's shape."""
         self.pending[index] = grads
 
+    def can_direct(self, index):
+        return self.pitch is not None
+
+    def done(self, index):
+        """The kernel writing `direct(index, …)` has been enqueued: nothing is left to scatter for this parameter."""
+        self.pending[index] = self.DONE
+
     def flush(self, first_index=0):
         """Scatter the pending gradients of parameters `first_index…` (everything by default) into the rows; a partial
         flush marks them done so the final one skips them."""
@@ -110,20 +117,25 @@ class _GradSink:
 
 
 class ScatterSink:
-    """Gradient sink for the coordinate-sharded server: the gradient of worker g (arena row `first_row + g`) is written
-    slice by slice straight into the arena of the rank that AGGREGATES that coordinate range — a reduce-scatter by
-    construction. `arenas[r]` is rank r's peer-mapped arena ([rows, per] floats, row pitch `per`), `bounds[r]` the
-    coordinate range [lo, hi) rank r owns. Parameters lying inside one range are written in place by the producing
-    batched GEMM (its epilogue stores go over NVLink while the backward pass continues); parameters straddling a
-    boundary, BatchNorm parameters and biases are scattered by one multi-tensor copy per destination rank."""
+    """Gradient sink for the coordinate-sharded server: the gradient of worker g (arena row `first_row + g`) ends up,
+    slice by slice, in the arena of the rank that AGGREGATES that coordinate range — a reduce-scatter by construction.
+    `arenas[r]` is rank r's peer-mapped arena ([rows, per] floats, row pitch `per`), `bounds[r]` the coordinate range
+    [lo, hi) rank r owns, `rank` this process's rank.
+
+    Library kernels (the batched weight-gradient GEMMs) only ever write THIS GPU's memory: `direct()` hands them a view of
+    the local arena when this rank owns the whole parameter, otherwise a persistent local staging tensor. `done()` then
+    moves the staged slices to their owners with our own multi-tensor copy kernel (plain `st.global` on the peer-mapped
+    pointers), on the stream that produced them, so the NVLink transfer overlaps the rest of the backward pass.
+    BatchNorm parameters, biases and anything else `put()` here follow in one multi-tensor copy per destination rank."""
 
     DONE = _GradSink.DONE
 
-    def __init__(self, params, slices, view_of, groups, arenas, first_row, per, bounds):
+    def __init__(self, params, slices, view_of, groups, arenas, first_row, per, bounds, rank=0):
         self.params, self.slices, self.view_of, self.groups = params, slices, view_of, groups
-        self.arenas, self.first_row, self.per, self.bounds = arenas, first_row, per, bounds
+        self.arenas, self.first_row, self.per, self.bounds, self.rank = arenas, first_row, per, bounds, rank
         self.pending = {}
         self._pieces = [self._owners(off, n) for off, n, _ in slices]
+        self._staging = {}
 
     def _owners(self, off, n):
         pieces = []
@@ -136,14 +148,67 @@ class ScatterSink:
     def put(self, index, grads):
         self.pending[index] = grads
 
+    def is_local(self, tensor):
+        """True when `tensor` lies in memory of THIS GPU (the local arena or an ordinary torch allocation) — what every
+        operand of a library kernel must satisfy."""
+        if not tensor.is_cuda:
+            return True
+        ptr = tensor.data_ptr()
+        for r, arena in enumerate(self.arenas):
+            if r != self.rank and arena.is_cuda and arena.data_ptr() <= ptr < arena.data_ptr() + 4 * arena.numel():
+                return False
+        return True
+
+    def can_direct(self, index):
+        return True
+
     def direct(self, index, rows, cols):
+        """A LOCAL [G, rows, cols] destination for the per-worker gradients of parameter `index`: the arena rows
+        themselves when this rank aggregates the whole parameter, else a staging tensor that `done()` pushes."""
         pieces = self._pieces[index]
-        if len(pieces) != 1:
-            return None
-        r, a, _ = pieces[0]
-        base = self.arenas[r]
-        return torch.as_strided(base, (self.groups, rows, cols), (self.per, cols, 1),
-                                base.storage_offset() + self.first_row * self.per + (a - self.bounds[r][0]))
+        if len(pieces) == 1 and pieces[0][0] == self.rank:
+            a = pieces[0][1]
+            base = self.arenas[self.rank]
+            out = torch.as_strided(base, (self.groups, rows, cols), (self.per, cols, 1),
+                                   base.storage_offset() + self.first_row * self.per + (a - self.bounds[self.rank][0]))
+        else:
+            out = self._staging.get(index)
+            if out is None or out.shape != (self.groups, rows, cols):
+                out = self._staging[index] = torch.empty((self.groups, rows, cols), device=self.params[index].device)
+        assert self.is_local(out), "library kernels must only write this GPU's memory"
+        return out
+
+    def done(self, index):
+        """The GEMM writing `direct(index, …)` has been enqueued on the current stream: push staged slices to the ranks
+        that aggregate them (same stream) and mark the parameter complete."""
+        staged = self._staging.get(index)
+        pieces = self._pieces[index]
+        if staged is not None and not (len(pieces) == 1 and pieces[0][0] == self.rank):
+            off, n, _ = self.slices[index]
+            table = {}
+            for g in range(self.groups if not staged.is_cuda else 0):      # host arenas (unit tests of the slicing logic)
+                for r, a, b in pieces:
+                    at = (self.first_row + g) * self.per + (a - self.bounds[r][0])
+                    self.arenas[r][at:at + (b - a)].copy_(staged[g].reshape(-1)[a - off:b - off])
+            for g in range(self.groups if staged.is_cuda else 0):
+                src = staged.data_ptr() + 4 * g * n
+                for r, a, b in pieces:
+                    entry = table.setdefault(r, ([], [], []))
+                    entry[0].append(src + 4 * (a - off))
+                    entry[1].append((self.first_row + g) * self.per + (a - self.bounds[r][0]))
+                    entry[2].append(b - a)
+            self._push(table)
+        self.pending[index] = self.DONE
+
+    def _push(self, table):
+        """One launch of our multi-tensor copy kernel per destination rank (its table lives in the kernel parameters)."""
+        lib = _lib.require() if table else None
+        for r, (srcs, offs, sizes) in table.items():
+            k = len(srcs)
+            base = self.arenas[r]
+            _lib.check(lib.gb_multi_copy((ctypes.c_void_p * k)(*srcs), (ctypes.c_uint64 * k)(*offs), (ctypes.c_uint32 * k)(*sizes), k,
+                                         base.data_ptr(), _lib.stream_ptr(base.device)))
+            _lib.count((k + 111) // 112)
 
     def flush(self):
         table = {}
@@ -166,21 +231,28 @@ class ScatterSink:
                     src = t.data_ptr()
                 for r, a, b in self._pieces[index]:
                     dst_off = (self.first_row + g) * self.per + (a - self.bounds[r][0])
-                    if src is None:
-                        self.arenas[r][dst_off:dst_off + (b - a)].zero_()
-                    elif not self.arenas[r].is_cuda:      # host arenas (unit tests of the slicing logic)
-                        self.arenas[r][dst_off:dst_off + (b - a)].copy_(t.reshape(-1)[a - off:b - off])
+                    if not self.arenas[r].is_cuda:      # host arenas (unit tests of the slicing logic)
+                        if src is None:
+                            self.arenas[r][dst_off:dst_off + (b - a)].zero_()
+                        else:
+                            self.arenas[r][dst_off:dst_off + (b - a)].copy_(t.reshape(-1)[a - off:b - off])
                     else:
+                        if src is None:                  # no gradient: push zeros with the same kernel
+                            zeros = self._zeros(b - a, p.device)
+                            keep.append(zeros)
+                            entry = table.setdefault(r, ([], [], []))
+                            entry[0].append(zeros.data_ptr()); entry[1].append(dst_off); entry[2].append(b - a)
+                            continue
                         entry = table.setdefault(r, ([], [], []))
                         entry[0].append(src + 4 * (a - off)); entry[1].append(dst_off); entry[2].append(b - a)
-        lib = _lib.require() if table else None
-        for r, (srcs, offs, sizes) in table.items():
-            k = len(srcs)
-            base = self.arenas[r]
-            _lib.check(lib.gb_multi_copy((ctypes.c_void_p * k)(*srcs), (ctypes.c_uint64 * k)(*offs), (ctypes.c_uint32 * k)(*sizes), k,
-                                         base.data_ptr(), _lib.stream_ptr(base.device)))
-            _lib.count((k + 111) // 112)
+        self._push(table)
         self.pending = {}
+
+    def _zeros(self, n, device):
+        z = getattr(self, "_zero_buf", None)
+        if z is None or z.numel() < n:
+            z = self._zero_buf = torch.zeros(n, device=device)
+        return z[:n]
 
 
 class _GroupedConv(torch.autograd.Function):
@@ -227,7 +299,7 @@ class _GroupedConv(torch.autograd.Function):
                     out = owner.sink.direct(widx, cout, cin)
                     if out is not None:
                         torch.bmm(gm.transpose(1, 2), xm, out=out)
-                        owner.sink.put(widx, owner.sink.DONE)
+                        owner.sink.done(widx)
                     else:
                         owner.sink.put(widx, torch.bmm(gm.transpose(1, 2), xm).unsqueeze(-1).unsqueeze(-1))
                 if strided and ctx.needs_input_grad[0]:
@@ -237,7 +309,7 @@ class _GroupedConv(torch.autograd.Function):
                     gx = torch.zeros_like(x)
                     gx[:, :, ::conv.stride[0], ::conv.stride[1]] = dxs.view(xs.shape[0], xs.shape[2], xs.shape[3], cin).permute(0, 3, 1, 2)
         elif (x.is_cuda and owner.replica.channels_last and conv.groups == 1 and conv.dilation == (1, 1) and x.shape[1] % 4 == 0
-              and x.is_contiguous(memory_format=torch.channels_last) and owner.sink.direct(widx, 1, 1) is not None):
+              and x.is_contiguous(memory_format=torch.channels_last) and owner.sink.can_direct(widx)):
             # k×k convolution: gather the patches once (own im2col kernel, (kh, kw, c) order), then ONE batched GEMM
             # dW[g] = dY[g]ᵀ · cols[g] writes all workers' gradients in OHWI order straight into their rows
             if not gy.is_contiguous(memory_format=torch.channels_last):
@@ -251,7 +323,7 @@ class _GroupedConv(torch.autograd.Function):
                 cols = im2col_nhwc(x, conv.kernel_size, conv.stride, conv.padding).view(G, -1, k)
                 gm = gy.permute(0, 2, 3, 1).reshape(G, -1, cout)
                 torch.bmm(gm.transpose(1, 2), cols, out=owner.sink.direct(widx, cout, k))
-            owner.sink.put(widx, owner.sink.DONE)
+                owner.sink.done(widx)
         else:
             sides = owner.all_sides()
             cur = torch.cuda.current_stream(x.device) if sides else None
@@ -304,7 +376,7 @@ class _GroupedLinear(torch.autograd.Function):
         out = owner.sink.direct(widx, gm.shape[-1], xm.shape[-1])
         if out is not None:
             torch.bmm(gm.transpose(1, 2), xm, out=out)
-            owner.sink.put(widx, owner.sink.DONE)
+            owner.sink.done(widx)
         else:
             owner.sink.put(widx, torch.bmm(gm.transpose(1, 2), xm))
         if bidx is not None:

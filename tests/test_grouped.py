@@ -208,7 +208,7 @@ def test_scatter_sink_slices_every_gradient_to_its_owner_cpu():
     bounds = [(min(d, r * per), min(d, r * per + per)) for r in range(world)]
     first_row, rows_total = 2, 2 + G + 1                      # this "rank" owns arena rows 2 .. 2+G-1
     arenas = [torch.full((rows_total * per,), float("nan")) for _ in range(world)]
-    sink = lambda params, slices, view_of: ScatterSink(params, slices, view_of, G, arenas, first_row, per, bounds)
+    sink = lambda params, slices, view_of: ScatterSink(params, slices, view_of, G, arenas, first_row, per, bounds, rank=1)
     group = GroupedWorkers(flat_model, [None] * G, loss_fn, side_streams=0, sink=sink)
     straddling = sum(1 for pieces in group.sink._pieces if len(pieces) > 1)
     assert straddling >= 1 and any(len(pieces) == 1 for pieces in group.sink._pieces)
