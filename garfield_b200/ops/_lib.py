@@ -37,6 +37,19 @@ def _declare(h):
     h.gb_gram_select_tc.argtypes = [pp, i32, i64, i32, i32, i32, i32, i32, vp, i64, vp, vp, vp, vp]
     h.gb_select_only.argtypes = [vp, i32, i32, i32, i32, i32, i32, vp, vp, vp]
     h.gb_gemm_nt.argtypes = [vp, vp, vp, vp, i32, i32, i32, i64, i64, i64, i32, i32, vp]
+    h.gb_conv_fprop_tc.argtypes = [vp, vp, vp, vp] + [i32] * 14 + [vp]
+    h.gb_conv_dgrad_tc.argtypes = [vp, vp, vp] + [i32] * 11 + [vp]
+    h.gb_conv_wgrad_tc.argtypes = [vp, vp, vp] + [i32] * 15 + [i64, i64, vp]
+    h.gb_im2col_pad_nhwc.argtypes = [vp, vp] + [i32] * 12 + [vp]
+    h.gb_pad_rows.argtypes = [vp, vp, i64, i32, i64, i32, vp]
+    h.gb_col2im_nhwc.argtypes = [vp, vp] + [i32] * 12 + [vp]
+    h.gb_upsample_zero_nhwc.argtypes = [vp, vp] + [i32] * 8 + [vp]
+    h.gb_maxpool_nhwc_forward.argtypes = [vp, vp, vp] + [i32] * 7 + [vp]
+    h.gb_maxpool_nhwc_backward.argtypes = [vp, vp, vp] + [i32] * 7 + [vp]
+    h.gb_softmax_ce_grouped.argtypes = [vp, i32, vp, vp, vp, i32, i32, i32, i32, vp]
+    h.gb_colsum_grouped.argtypes = [vp, i64, vp, i32, i32, i32, f32, vp]
+    h.gb_avgpool_nhwc_forward.argtypes = [vp, vp, i64, i32, i32, vp]
+    h.gb_avgpool_nhwc_backward.argtypes = [vp, vp, i64, i32, i32, vp]
     h.gb_conv2d_forward.argtypes = [vp, vp, vp, vp] + [i32] * 10 + [vp]
     h.gb_conv2d_backward.argtypes = [vp, vp, vp, vp, vp, vp] + [i32] * 9 + [vp]
     h.gb_maxpool2d_forward.argtypes = [vp, vp, vp, i32, i32, i32, i32, i32, vp]

@@ -26,7 +26,7 @@ import types
 import torch
 import torch.nn.functional as F
 
-from ..ops import _lib
+from ..ops import _lib, conv as convops
 from ..ops.nn import gemm_nt, grouped_batch_norm, im2col_nhwc
 
 __all__ = ["GroupedWorkers", "ScatterSink"]
@@ -38,6 +38,11 @@ _aten = torch.ops.aten
 # gradient pass against 2.34 ms with the library kernels (profiles/README.md §3); it needs a small-tile variant
 # before it can be the default.
 POINTWISE_GEMM = [os.environ.get("GARFIELD_POINTWISE_GEMM", "0") != "0"]
+
+# Convolutions, Linear layers, pooling and the loss of the fused pass on this library's own sm_100a kernels (tcgen05
+# implicit GEMMs, ops/conv.py) — the default on CUDA with channels-last replicas. GARFIELD_OWN_CONV=0 switches back to the
+# library (cuDNN / cuBLAS) kernels for A/B measurements.
+OWN_KERNELS = [os.environ.get("GARFIELD_OWN_CONV", "1") != "0"]
 
 
 def _same_layout(a, b):
@@ -385,6 +390,118 @@ class _GroupedLinear(torch.autograd.Function):
         return gx, None, None, None, None, None
 
 
+class _TcConv(torch.autograd.Function):
+    """Conv2d of the fused pass on the tcgen05 implicit-GEMM kernels: forward, data gradient (once over the concatenated
+    batch) and the G per-worker weight gradients (one launch, written straight into the workers' gradient rows)."""
+
+    @staticmethod
+    def forward(ctx, x, w, b, owner, conv, widx, bidx):
+        if not x.is_contiguous(memory_format=torch.channels_last):
+            x = x.contiguous(memory_format=torch.channels_last)
+        ctx.save_for_backward(x, w)
+        ctx.cfg = (owner, conv, widx, bidx)
+        cache = {}
+        ho, wo = convops.out_size(x.shape[2], x.shape[3], conv.kernel_size, conv.stride, conv.padding)
+        # the output is allocated here in its logical NCHW shape (channels-last strides) so that autograd sees a fresh tensor,
+        # not a view — layers after it may work in place
+        y = torch.empty((x.shape[0], w.shape[0], ho, wo), device=x.device, memory_format=torch.channels_last)
+        convops.conv_fprop(x.permute(0, 2, 3, 1), w.permute(0, 2, 3, 1), b, conv.stride, conv.padding, out=y.permute(0, 2, 3, 1), cache=cache)
+        ctx.cols = cache.get("cols")       # explicit patch matrix (RGB stem): reused by the weight gradient
+        return y
+
+    @staticmethod
+    def backward(ctx, gy):
+        x, w = ctx.saved_tensors
+        owner, conv, widx, bidx = ctx.cfg
+        G = owner.groups
+        if not gy.is_contiguous(memory_format=torch.channels_last):
+            gy = gy.contiguous(memory_format=torch.channels_last)
+        xn, gyn, wn = x.permute(0, 2, 3, 1), gy.permute(0, 2, 3, 1), w.permute(0, 2, 3, 1)
+        cout, kh, kw, cin = wn.shape
+        side = owner.next_side()
+        if side is not None:
+            side.wait_stream(torch.cuda.current_stream(x.device))
+            x.record_stream(side); gy.record_stream(side)
+        with torch.cuda.stream(side) if side is not None else _NoStream():
+            if owner.sink.can_direct(widx):
+                convops.conv_wgrad(xn, gyn, G, (kh, kw), conv.stride, conv.padding, out=owner.sink.direct(widx, cout, kh * kw * cin), cols=ctx.cols)
+                owner.sink.done(widx)
+            else:
+                dw = convops.conv_wgrad(xn, gyn, G, (kh, kw), conv.stride, conv.padding, cols=ctx.cols)
+                owner.sink.put(widx, dw.view(G, cout, kh, kw, cin).permute(0, 1, 4, 2, 3))
+            if bidx is not None:
+                owner.sink.put(bidx, convops.colsum_grouped(gyn.reshape(-1, cout), G))
+        gx = None
+        if ctx.needs_input_grad[0]:
+            gx = convops.conv_dgrad(gyn, wn, (x.shape[2], x.shape[3]), conv.stride, conv.padding).permute(0, 3, 1, 2)
+        return gx, None, None, None, None, None, None
+
+
+class _TcLinear(torch.autograd.Function):
+    """Linear layer of the fused pass as a 1×1-geometry GEMM on the same kernels."""
+
+    @staticmethod
+    def forward(ctx, x, w, b, owner, widx, bidx):
+        ctx.save_for_backward(x, w)
+        ctx.cfg = (owner, widx, bidx)
+        y = torch.empty((x.shape[0], w.shape[0]), device=x.device)
+        convops.conv_fprop(x.unsqueeze(1).unsqueeze(1), w.unsqueeze(1).unsqueeze(1), b, out=y.unsqueeze(1).unsqueeze(1))
+        return y
+
+    @staticmethod
+    def backward(ctx, gy):
+        x, w = ctx.saved_tensors
+        owner, widx, bidx = ctx.cfg
+        G = owner.groups
+        xn, gyn, wn = x.unsqueeze(1).unsqueeze(1), gy.unsqueeze(1).unsqueeze(1), w.unsqueeze(1).unsqueeze(1)
+        nout, nin = w.shape
+        if owner.sink.can_direct(widx):
+            convops.conv_wgrad(xn, gyn, G, (1, 1), out=owner.sink.direct(widx, nout, nin))
+            owner.sink.done(widx)
+        else:
+            owner.sink.put(widx, convops.conv_wgrad(xn, gyn, G, (1, 1)))
+        if bidx is not None:
+            owner.sink.put(bidx, convops.colsum_grouped(gy, G, cols=nout))
+        gx = convops.conv_dgrad(gyn, wn, (1, 1)).view(x.shape) if ctx.needs_input_grad[0] else None
+        return gx, None, None, None, None, None
+
+
+class _TcMaxPool(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, k, s, p):
+        if not x.is_contiguous(memory_format=torch.channels_last):
+            x = x.contiguous(memory_format=torch.channels_last)
+        ho, wo = convops.out_size(x.shape[2], x.shape[3], k, s, p)
+        y = torch.empty((x.shape[0], x.shape[1], ho, wo), device=x.device, memory_format=torch.channels_last)
+        _, arg = convops.max_pool_nhwc(x.permute(0, 2, 3, 1), k, s, p, out=y.permute(0, 2, 3, 1))
+        ctx.save_for_backward(arg)
+        ctx.cfg = ((x.shape[0], x.shape[2], x.shape[3], x.shape[1]), k, s, p)
+        return y
+
+    @staticmethod
+    def backward(ctx, gy):
+        arg, = ctx.saved_tensors
+        shape, k, s, p = ctx.cfg
+        if not gy.is_contiguous(memory_format=torch.channels_last):
+            gy = gy.contiguous(memory_format=torch.channels_last)
+        return convops.max_pool_nhwc_backward(gy.permute(0, 2, 3, 1), arg, shape, k, s, p).permute(0, 3, 1, 2), None, None, None
+
+
+class _TcAvgPool(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x):
+        if not x.is_contiguous(memory_format=torch.channels_last):
+            x = x.contiguous(memory_format=torch.channels_last)
+        ctx.hw = (x.shape[2], x.shape[3])
+        y = torch.empty((x.shape[0], x.shape[1], 1, 1), device=x.device)
+        convops.avg_pool_nhwc(x.permute(0, 2, 3, 1), out=y.view(x.shape[0], x.shape[1]))
+        return y
+
+    @staticmethod
+    def backward(ctx, gy):
+        return convops.avg_pool_nhwc_backward(gy.reshape(gy.shape[0], gy.shape[1]), ctx.hw).permute(0, 3, 1, 2)
+
+
 class _NoStream:
     def __enter__(self):
         return None
@@ -444,6 +561,11 @@ class GroupedWorkers:
                     self.running_tables[name] = tables
                 m._gb_group = _BnGroup(self, index[id(m.weight)], index[id(m.bias)], tables)
                 m.forward = types.MethodType(lambda bn, x: bn._gb_group(bn, x, None, False), m)
+            elif (isinstance(m, torch.nn.MaxPool2d) and isinstance(m.kernel_size, int) and isinstance(m.padding, int) and m.dilation == 1
+                  and not m.ceil_mode and not m.return_indices and isinstance(m.stride if m.stride is not None else m.kernel_size, int)):
+                m.forward = types.MethodType(self._maxpool_forward(type(m).forward), m)
+            elif isinstance(m, torch.nn.AdaptiveAvgPool2d) and m.output_size in (1, (1, 1)):
+                m.forward = types.MethodType(self._avgpool_forward(type(m).forward), m)
 
     # -- what the fusion covers ---------------------------------------------------------------------------------
     @staticmethod
@@ -483,6 +605,8 @@ class GroupedWorkers:
         owner = self
 
         def forward(conv, x):
+            if owner.own_kernels(x) and conv.groups == 1 and conv.dilation == (1, 1) and x.dim() == 4:
+                return _TcConv.apply(x, conv.weight, conv.bias, owner, conv, widx, bidx)
             return _GroupedConv.apply(x, conv.weight, conv.bias, owner, conv, widx, bidx)
         return forward
 
@@ -492,7 +616,34 @@ class GroupedWorkers:
         def forward(lin, x):
             if x.dim() != 2:
                 raise ValueError("worker fusion expects 2-D inputs to Linear layers")
+            if owner.own_kernels(x) and x.is_contiguous() and lin.in_features % 4 == 0:
+                return _TcLinear.apply(x, lin.weight, lin.bias, owner, widx, bidx)
             return _GroupedLinear.apply(x, lin.weight, lin.bias, owner, widx, bidx)
+        return forward
+
+    def own_kernels(self, x):
+        """Run this layer on the library's own sm_100a kernels? (CUDA fp32 activations, channels-last parameter storage)"""
+        return (OWN_KERNELS[0] and x.is_cuda and x.dtype == torch.float32 and getattr(self.replica, "channels_last", False)
+                and _lib.available())
+
+    def _maxpool_forward(self, stock):
+        owner = self
+
+        def forward(pool, x):
+            if owner.own_kernels(x) and x.dim() == 4 and x.shape[1] % 4 == 0:
+                return _TcMaxPool.apply(x, pool.kernel_size, pool.stride if pool.stride is not None else pool.kernel_size, pool.padding)
+            return stock(pool, x)
+        return forward
+
+    def _avgpool_forward(self, stock):
+        owner = self
+
+        def forward(pool, x):
+            if owner.own_kernels(x) and x.dim() == 4:
+                if x.shape[2] == 1 and x.shape[3] == 1:
+                    return x                      # a 1×1 plane is its own average
+                return _TcAvgPool.apply(x)
+            return stock(pool, x)
         return forward
 
     def add_milestone(self, module, callback):
@@ -536,6 +687,16 @@ class GroupedWorkers:
         self._used_sides = set()
         self.module.train()
         out = self.module(data)
+        if self.loss_kind == "ce" and self.own_kernels(out) and out.dim() == 2 and out.is_contiguous():
+            # fused grouped cross-entropy: per-row losses and d(Σ_g mean_g)/d(logits) in one launch, the backward pass starts
+            # from the (16-byte padded) logit gradients
+            row_loss, dlogits = convops.softmax_ce_grouped(out.detach(), target, G)
+            out.backward(dlogits[:, :out.shape[1]])
+            convops.colsum_grouped(row_loss.view(-1, 1), G, scale=1.0 / (out.shape[0] // G), out=losses.view(G, 1))
+            if self.side_streams:
+                self.join_side_streams(torch.cuda.current_stream(data.device))
+            self.sink.flush()
+            return
         if self.loss_kind == "ce":
             per_sample = F.cross_entropy(out, target, reduction="none")
         elif self.loss_kind == "nll":

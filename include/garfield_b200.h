@@ -159,6 +159,40 @@ GB_API int gb_pairwise_select_noalloc(float const* const* rows, int n, int64_t d
 GB_API int gb_gemm_nt(void const* A, void const* B, float* C, float const* bias, int M, int N, int K, int64_t lda, int64_t ldb,
                       int64_t ldc, int dtype, int relu, void* stream);
 
+/* Implicit-GEMM convolutions on tcgen05 tensor cores (TF32 operands, fp32 accumulation in TMEM) over channels-last
+ * activations; operand tiles are tiled-TMA boxes of the activation tensor shifted by the filter tap (zero fill = padding,
+ * traversal stride = convolution stride), weights are read in OHWI order [cout][kh][kw][cin]. A 1 x 1 geometry makes the
+ * same entry points plain GEMMs (Linear layers, explicit patch matrices). Pixel pitches are in floats.
+ * ref: cuDNN / cuBLAS behind nn.Conv2d / nn.Linear (garfieldpp/models/nets.py:40-78, garfieldpp/tools.py:69-75,
+ * garfieldpp/worker.py:85-91). */
+GB_API int gb_conv_fprop_tc(float const* x, float const* w, float const* bias, float* y, int n, int h, int wd, int cin, int x_pitch, int cout,
+                            int y_pitch, int kh, int kw, int stride_h, int stride_w, int pad_h, int pad_w, int relu, void* stream);
+/* dx of a stride-1 convolution (strided layers: zero-upsample dy first, gb_upsample_zero_nhwc). */
+GB_API int gb_conv_dgrad_tc(float const* dy, float const* w, float* dx, int n, int h, int wd, int cin, int dx_pitch, int cout, int dy_pitch,
+                            int kh, int kw, int pad_h, int pad_w, void* stream);
+/* Per-worker weight gradients: images g*b ... g*b+b-1 belong to worker g; matrix g is written at dw + g*dw_group_stride
+ * ([cout][kh*kw*dw_cols], row stride dw_ld) — straight into the workers' gradient rows. */
+GB_API int gb_conv_wgrad_tc(float const* x, float const* dy, float* dw, int groups, int b, int h, int wd, int cin, int x_pitch, int cout,
+                            int dy_pitch, int kh, int kw, int stride_h, int stride_w, int pad_h, int pad_w, int dw_cols, int64_t dw_ld,
+                            int64_t dw_group_stride, void* stream);
+/* Channels-last layers around them (csrc/cuda/nn_nhwc.cu). ref: ATen/cuDNN behind nn.MaxPool2d, nn.AdaptiveAvgPool2d,
+ * nn.CrossEntropyLoss and the strided-convolution backward (garfieldpp/tools.py:47-57,69-75). */
+GB_API int gb_im2col_pad_nhwc(float const* x, float* cols, int N, int H, int W, int C, int pitch, int KH, int KW, int stride_h, int stride_w,
+                              int pad_h, int pad_w, int kpad, void* stream);
+GB_API int gb_pad_rows(float const* src, float* dst, int64_t rows, int k, int64_t ld, int kpad, void* stream);
+GB_API int gb_col2im_nhwc(float const* dcols, float* dx, int N, int H, int W, int C, int pitch, int KH, int KW, int stride_h, int stride_w,
+                          int pad_h, int pad_w, int kpad, void* stream);
+GB_API int gb_upsample_zero_nhwc(float const* in, float* out, int N, int Ho, int Wo, int C, int stride_h, int stride_w, int H, int W, void* stream);
+GB_API int gb_maxpool_nhwc_forward(float const* x, float* y, unsigned char* arg, int N, int H, int W, int C, int k, int stride, int pad, void* stream);
+GB_API int gb_maxpool_nhwc_backward(float const* dy, unsigned char const* arg, float* dx, int N, int H, int W, int C, int k, int stride, int pad,
+                                    void* stream);
+/* Grouped cross-entropy: row_loss[row] and dlogits = d(sum over workers of their mean loss)/d(logits), padded columns zeroed. */
+GB_API int gb_softmax_ce_grouped(float const* logits, int ld, int64_t const* target, float* row_loss, float* dlogits, int ldd, int rows,
+                                 int classes, int rows_per_group, void* stream);
+GB_API int gb_colsum_grouped(float const* in, int64_t ld, float* out, int groups, int rows_per_group, int cols, float scale, void* stream);
+GB_API int gb_avgpool_nhwc_forward(float const* x, float* y, int64_t n, int hw, int C, void* stream);
+GB_API int gb_avgpool_nhwc_backward(float const* dy, float* dx, int64_t n, int hw, int C, void* stream);
+
 /* Layer kernels of the small reference networks (fp32, NCHW). ref: cuDNN/ATen behind nn.Conv2d, MaxPool2d,
  * BatchNorm2d, NLLLoss/CrossEntropyLoss (garfieldpp/models/nets.py:40-144, garfieldpp/tools.py:47-57). */
 GB_API int gb_conv2d_forward(float const* x, float const* w, float const* bias, float* y, int n, int cin, int h, int wd, int cout, int kh, int kw,

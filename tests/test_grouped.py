@@ -112,16 +112,18 @@ def test_unsupported_models_are_reported():
 
 
 @pytest.mark.gpu
-@pytest.mark.parametrize("pointwise_gemm", [False, True])
-def test_grouped_workers_match_separate_replicas_gpu(pointwise_gemm):
-    """pointwise_gemm: 1×1 convolutions forward on the tcgen05 GEMM (TF32 operands → looser tolerance)."""
+@pytest.mark.parametrize("own_kernels,pointwise_gemm", [(True, False), (False, False), (False, True)])
+def test_grouped_workers_match_separate_replicas_gpu(own_kernels, pointwise_gemm):
+    """own_kernels: convolutions / Linear / pooling / loss on the tcgen05 implicit-GEMM kernels (TF32 operands → looser
+    tolerance); otherwise the library kernels in exact fp32, optionally with 1×1 convolutions on the tcgen05 GEMM."""
     from garfield_b200.parallel import grouped
-    previous = grouped.POINTWISE_GEMM[0]
-    grouped.POINTWISE_GEMM[0] = pointwise_gemm
+    previous = grouped.POINTWISE_GEMM[0], grouped.OWN_KERNELS[0]
+    grouped.POINTWISE_GEMM[0], grouped.OWN_KERNELS[0] = pointwise_gemm, own_kernels
     try:
-        _check_grouped_gpu(8e-2 if pointwise_gemm else 2e-4, pointwise_gemm)   # TF32 everywhere vs exact fp32
+        tf32 = own_kernels or pointwise_gemm
+        _check_grouped_gpu(8e-2 if tf32 else 2e-4, tf32)   # TF32 everywhere vs exact fp32
     finally:
-        grouped.POINTWISE_GEMM[0] = previous
+        grouped.POINTWISE_GEMM[0], grouped.OWN_KERNELS[0] = previous
 
 
 def _check_grouped_gpu(tolerance, allow_tf32):
