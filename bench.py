@@ -50,7 +50,8 @@ def parse_args(argv=None):
     ap.add_argument("--fuse-workers", default="auto", choices=["auto", "on", "off"],
                     help="one batched forward/backward for the workers hosted by a GPU (auto: whenever the model is covered)")
     ap.add_argument("--fusion-chains", type=int, default=1, help="split a rank's fused workers into this many concurrent passes")
-    ap.add_argument("--sync", default="nccl", choices=["nccl", "flags"], help="inter-rank synchronisation (N > 1)")
+    ap.add_argument("--sync", default="flags", choices=["nccl", "flags"],
+                    help="inter-rank synchronisation (N > 1): peer-mapped epoch flags (default, no NCCL call inside a step) or NCCL barriers")
     return ap.parse_args(argv)
 
 
@@ -218,7 +219,8 @@ def run_ours(args):
             "impl": "ours",
             "config": {"model": "resnet50 (torchvision, 10 classes, 3x32x32 inputs)", "global_batch": N_WORKERS * BATCH,
                        "seq_len": None, "parallelism": ("ssmw n=8 f=1 over %d gpu(s); workers r, r+N, ... on rank r; the server's aggregation + optimizer "
-                                       "are sharded by coordinate range over the ranks (peer-memory loads/stores)" % world) if world > 1
+                                       "are sharded by coordinate range over the ranks (peer-memory loads/stores, %s)" % (
+                                           world, "epoch-flag synchronisation, no NCCL call inside a step" if args.sync == "flags" else "NCCL barriers")) if world > 1
                        else "ssmw n=8 f=1, all roles on 1 gpu",
                        "gar": args.gar, "optimizer": "sgd lr=0.2 momentum=0.9 wd=5e-4 (fused in the GAR epilogue)",
                        "l2": "per-step working set 8 x 94 MB gradient rows = 753 MB > 126 MB L2 (no flush needed)",

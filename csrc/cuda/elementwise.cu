@@ -247,6 +247,93 @@ __global__ void flag_wait_kernel(FlagTable flags, int count, uint32_t value, uns
 }  // namespace
 }  // namespace gb
 
+namespace gb {
+namespace {
+// Device-resident epoch: the step counter lives in device memory so that a CUDA graph of the whole iteration, replayed every
+// step, signals and waits for the right epoch without any kernel argument changing.
+__global__ void epoch_bump_kernel(uint32_t* epoch) { *epoch += 1u; }
+
+__global__ void flag_signal_ep_kernel(uint32_t* flag, const uint32_t* epoch) {
+    __threadfence_system();
+    ptx::st_release_sys(flag, *epoch);
+}
+
+// Wait until every flag reached *epoch − lag, or `quorum` of them did AND the deadline passed... precisely:
+//   * all flags there                      → done
+//   * deadline passed                      → done, the missing ones are late
+// arrived[i] (optional) = 1 when flag i made it. Thread i polls flag i; the block agrees through shared memory.
+__global__ void flag_wait_ep_kernel(FlagTable flags, int count, const uint32_t* epoch, uint32_t lag, unsigned long long timeout_ns, uint32_t* late,
+                                    uint32_t* arrived) {
+    int const i = threadIdx.x;
+    if (i >= count) return;
+    uint32_t const value = *epoch - lag;
+    unsigned long long const deadline = ptx::globaltimer_ns() + timeout_ns;
+    bool ready = false;
+    while (!(ready = (static_cast<int32_t>(ptx::ld_acquire_sys(flags.p[i]) - value) >= 0))) {
+        if (ptx::globaltimer_ns() > deadline) break;
+        __nanosleep(100);
+    }
+    if (!ready && late != nullptr) atomicAdd(late, 1u);
+    if (arrived != nullptr) arrived[i] = ready ? 1u : 0u;
+}
+
+// Quorum decision by the lead server (device-side form of the reference's "hand the rule the replies that made it",
+// garfieldpp/server.py:134-155): poll the peers' "gradients ready" flags until all arrived, or the deadline passed with at
+// least `quorum` of them there (below the quorum it keeps waiting, up to 16 deadlines). The resulting bit mask (bit i = flag
+// i arrived) is stored into every rank's decision word, then every rank's decision flag is released with the epoch.
+struct DecisionTable {
+    uint32_t* word[kMaxRows];
+    uint32_t* flag[kMaxRows];
+};
+__global__ void quorum_decide_kernel(FlagTable flags, int count, const uint32_t* epoch, int quorum, unsigned long long timeout_ns,
+                                     DecisionTable out, int n_out, uint32_t* late) {
+    __shared__ unsigned long long mask_sh;
+    int const i = threadIdx.x;
+    uint32_t const value = *epoch;
+    if (i == 0) mask_sh = 0ull;
+    __syncthreads();
+    unsigned long long const start = ptx::globaltimer_ns();
+    bool ready = false;
+    if (i < count) {
+        for (;;) {
+            if (!ready && static_cast<int32_t>(ptx::ld_acquire_sys(flags.p[i]) - value) >= 0) {
+                ready = true;
+                atomicOr(&mask_sh, 1ull << i);
+            }
+            unsigned long long const seen = *reinterpret_cast<volatile unsigned long long*>(&mask_sh);
+            int const have = __popcll(seen);
+            unsigned long long const waited = ptx::globaltimer_ns() - start;
+            if (have == count) break;
+            if (waited > timeout_ns && have >= quorum) break;
+            if (waited > 16ull * timeout_ns) break;
+            __nanosleep(100);
+        }
+    }
+    __syncthreads();
+    unsigned long long const mask = mask_sh;
+    if (i < count && !((mask >> i) & 1ull) && late != nullptr) atomicAdd(late, 1u);
+    if (i < n_out) {
+        out.word[i][0] = static_cast<uint32_t>(mask & 0xffffffffull);
+        out.word[i][1] = static_cast<uint32_t>(mask >> 32);
+        __threadfence_system();
+        ptx::st_release_sys(out.flag[i], value);
+    }
+}
+
+struct SlotTable {
+    const float* p[kMaxRows];
+};
+// out[i] = Σ_r slots[r][i] in rank order (deterministic; every rank computes bitwise the same sum). Slots may be peer-mapped.
+__global__ void __launch_bounds__(256) reduce_slots_kernel(SlotTable slots, int nslots, int count, float* __restrict__ out) {
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < count; i += gridDim.x * blockDim.x) {
+        float acc = 0.f;
+        for (int r = 0; r < nslots; ++r) acc += slots.p[r][i];
+        out[i] = acc;
+    }
+}
+}  // namespace
+}  // namespace gb
+
 extern "C" {
 
 GB_API int gb_flag_signal(uint32_t* flag, uint32_t value, void* stream) {
@@ -262,6 +349,46 @@ GB_API int gb_flag_wait(uint32_t* const* flags, int count, uint32_t value, uint6
     for (int i = 0; i < count; ++i) table.p[i] = flags[i];
     flag_wait_kernel<<<1, 64, 0, static_cast<cudaStream_t>(stream)>>>(table, count, value, timeout_ns, late);
     return cuda_check(cudaGetLastError(), "flag wait");
+}
+
+GB_API int gb_epoch_bump(uint32_t* epoch, void* stream) {
+    epoch_bump_kernel<<<1, 1, 0, static_cast<cudaStream_t>(stream)>>>(epoch);
+    return cuda_check(cudaGetLastError(), "epoch bump");
+}
+
+GB_API int gb_flag_signal_ep(uint32_t* flag, uint32_t const* epoch, void* stream) {
+    flag_signal_ep_kernel<<<1, 1, 0, static_cast<cudaStream_t>(stream)>>>(flag, epoch);
+    return cuda_check(cudaGetLastError(), "flag signal (device epoch)");
+}
+
+GB_API int gb_flag_wait_ep(uint32_t* const* flags, int count, uint32_t const* epoch, uint32_t lag, uint64_t timeout_ns, uint32_t* late,
+                           uint32_t* arrived, void* stream) {
+    if (count < 1 || count > kMaxRows) return cuda_fail("flag wait: need 1..64 flags");
+    FlagTable table{};
+    for (int i = 0; i < count; ++i) table.p[i] = flags[i];
+    flag_wait_ep_kernel<<<1, 64, 0, static_cast<cudaStream_t>(stream)>>>(table, count, epoch, lag, timeout_ns, late, arrived);
+    return cuda_check(cudaGetLastError(), "flag wait (device epoch)");
+}
+
+GB_API int gb_quorum_decide(uint32_t* const* flags, int count, uint32_t const* epoch, int quorum, uint64_t timeout_ns, uint32_t* const* words,
+                            uint32_t* const* decision_flags, int n_out, uint32_t* late, void* stream) {
+    if (count < 1 || count > kMaxRows || n_out < 1 || n_out > kMaxRows || quorum < 1 || quorum > count)
+        return cuda_fail("quorum decide: need 1..64 flags, 1..64 destinations and 1 <= quorum <= count");
+    FlagTable table{};
+    DecisionTable out{};
+    for (int i = 0; i < count; ++i) table.p[i] = flags[i];
+    for (int i = 0; i < n_out; ++i) { out.word[i] = words[i]; out.flag[i] = decision_flags[i]; }
+    quorum_decide_kernel<<<1, 64, 0, static_cast<cudaStream_t>(stream)>>>(table, count, epoch, quorum, timeout_ns, out, n_out, late);
+    return cuda_check(cudaGetLastError(), "quorum decide");
+}
+
+GB_API int gb_reduce_slots(float const* const* slots, int nslots, int count, float* out, void* stream) {
+    if (nslots < 1 || nslots > kMaxRows || count < 1) return cuda_fail("reduce_slots: need 1..64 slots");
+    SlotTable table{};
+    for (int r = 0; r < nslots; ++r) table.p[r] = slots[r];
+    int const blocks = (count + 255) / 256 < 16 ? (count + 255) / 256 : 16;
+    reduce_slots_kernel<<<blocks, 256, 0, static_cast<cudaStream_t>(stream)>>>(table, nslots, count, out);
+    return cuda_check(cudaGetLastError(), "reduce_slots");
 }
 
 }  // extern "C"

@@ -59,6 +59,11 @@ def _declare(h):
     h.gb_batchnorm_backward.argtypes = [vp] * 8 + [i32, i32, i32, vp]
     h.gb_flag_signal.argtypes = [vp, ctypes.c_uint32, vp]
     h.gb_flag_wait.argtypes = [pp, i32, ctypes.c_uint32, u64, vp, vp]
+    h.gb_epoch_bump.argtypes = [vp, vp]
+    h.gb_flag_signal_ep.argtypes = [vp, vp, vp]
+    h.gb_flag_wait_ep.argtypes = [pp, i32, vp, ctypes.c_uint32, u64, vp, vp, vp]
+    h.gb_reduce_slots.argtypes = [pp, i32, i32, vp, vp]
+    h.gb_quorum_decide.argtypes = [pp, i32, vp, i32, u64, pp, pp, i32, vp, vp]
     h.gb_multi_copy.argtypes = [pp, vp, vp, i32, vp, vp]
     h.gb_global_avgpool_forward.argtypes = [vp, vp, i64, i32, vp]
     h.gb_global_avgpool_backward.argtypes = [vp, vp, i64, i32, vp]

@@ -156,8 +156,13 @@ class _LocalWorker:
 class SSMWEngine:
     def __init__(self, model, dataset, loss, num_workers, f, gar, batch, optimizer="sgd", opt_args=None, byzantine=None,
                  device=None, group=None, use_graphs=True, train_set=None, seed=1234, gar_kwargs=None, sharded=None,
-                 channels_last=True, sync="nccl", flag_timeout=5.0, gather_grads=True, fast_bn=True,
-                 split_backward=None, fuse_workers=None, fusion_chains=1, scatter_grads=None, overlap_distances=None):
+                 channels_last=True, sync=None, flag_timeout=5.0, gather_grads=True, fast_bn=True,
+                 split_backward=None, fuse_workers=None, fusion_chains=1, scatter_grads=None, overlap_distances=None, num_wait=None):
+        """`sync`: "flags" (default with several GPUs) — ranks synchronise through peer-mapped epoch flags and exchange the
+        partial distance matrices through peer-visible slots, so that no NCCL call remains in a step (NCCL only bootstraps:
+        IPC handles, initial broadcast); "nccl" keeps the 4-byte all-reduce barriers and the n×n all-reduce (baseline).
+        `num_wait`: quorum — aggregate as soon as this many gradients are there and the deadline `flag_timeout` has passed;
+        the rule is then given only the rows that made it (reference: server.get_gradients(iter, n − f))."""
         self.rank = dist.get_rank(group) if dist.is_initialized() else 0
         self.world = dist.get_world_size(group) if dist.is_initialized() else 1
         self.group = group
@@ -267,20 +272,31 @@ class SSMWEngine:
                     self.rows.append(self.grad_arena.peer(owner)[j * self.pitch + self.lo:j * self.pitch + self.hi])
             self.mirrors = [self.param_arena.peer(r)[self.lo:self.hi] for r in range(self.world) if r != self.rank]
         self._flag = torch.zeros(1, device=self.device)
-        # sync="flags": ranks synchronise through peer-mapped epoch flags polled by a tiny kernel with a
-        # deadline (late peers are counted in `late_peers` and NOT waited for — their rows are stale, which
-        # the robust rule tolerates like any other Byzantine input) instead of NCCL barriers.
+        # sync="flags": peer-mapped epoch flags polled by a one-warp kernel with a deadline instead of NCCL barriers, and
+        # peer-visible slots + a fixed-order sum instead of the NCCL all-reduce of the partial distances. The epoch lives in
+        # device memory (bumped by a kernel), so the whole multi-GPU iteration is one replayable CUDA graph.
+        if sync is None:
+            sync = "flags"
         self.sync = sync if self.world > 1 else "none"
         self.flag_timeout_ns = int(flag_timeout * 1e9)
         self.epoch = 0
+        self.num_wait = int(num_wait) if (num_wait and num_wait < self.n and self.sync == "flags") else None
+        self.last_arrived = None
         if self.sync == "flags":
             self.flag_arena = PeerArena(64, self.device, group)
+            self.dist_arena = PeerArena((gar_ops.MAX_ROWS + 1) ** 2 + 63, self.device, group)
             self._late = torch.zeros(1, dtype=torch.int32, device=self.device)
+            self._epoch_dev = torch.zeros(1, dtype=torch.int32, device=self.device)
+            self._arrived = torch.zeros(64, dtype=torch.int32, device=self.device)
             word = lambda r, k: self.flag_arena.peer(r).data_ptr() + 4 * k      # flag k of rank r (uint32)
-            self._my_grad_flag, self._my_param_flag = word(self.rank, 0), word(self.rank, 1)
+            self._word = word
+            self._my_grad_flag, self._my_param_flag, self._my_dist_flag = word(self.rank, 0), word(self.rank, 1), word(self.rank, 2)
             self._grad_flags = [word(r, 0) for r in range(self.world)]
-            servers = range(self.world) if self.sharded else [0]
+            servers = list(range(self.world)) if self.sharded else [0]
+            self._servers = servers
             self._param_flags = [word(r, 1) for r in servers]
+            self._dist_flags = [word(r, 2) for r in servers]
+            self._reductions_this_step = 0
         self._graph = None
         self._whole_step = None          # None: try the whole-iteration graph on one GPU; False: it failed to capture
         self._copy_stream = None
@@ -541,14 +557,47 @@ class SSMWEngine:
             raise ValueError("unknown attack %r" % (w.attack,))
 
     def _allreduce(self, tensor):
-        dist.all_reduce(tensor, group=self.group)
+        """Sum a small device tensor (the n×n partial distances of this rank's coordinate slice) over the server ranks."""
+        if self.sync != "flags":
+            dist.all_reduce(tensor, group=self.group)        # baseline
+            return
+        # peer slots: publish my partial, raise my flag, wait for everyone's, sum the slots in rank order (bitwise the same on
+        # every rank) — device to device, no collective library
+        import ctypes
+        if self._reductions_this_step:
+            raise RuntimeError("one partial-distance reduction per step (the flags carry the step's epoch)")
+        self._reductions_this_step += 1
+        k = tensor.numel()
+        self.dist_arena.local[:k].copy_(tensor.reshape(-1))
+        self._signal(self._my_dist_flag)
+        self._wait(self._dist_flags)
+        slots = (ctypes.c_void_p * len(self._servers))(*[self.dist_arena.peer(r).data_ptr() for r in self._servers])
+        _lib.check(_lib.require().gb_reduce_slots(slots, len(self._servers), k, tensor.data_ptr(), _lib.stream_ptr(self.device)))
+        _lib.count()
 
-    def aggregate_and_update(self):
+    def aggregate_and_update(self, rows=None):
         """Server side: fused gather + GAR + optimizer step + parameter publication, on the whole
-        vector (rank 0) or on this rank's coordinate slice (sharded)."""
+        vector (rank 0) or on this rank's coordinate slice (sharded). `rows`: the subset of gradient rows to hand to the
+        rule (quorum mode: only those that arrived); default all n."""
         opt = self.optimizer
         if self.scatter and self.byzantine and self.rows:
             self._attack_slices()
+        all_rows, self.rows = self.rows, (rows if rows is not None else self.rows)
+        try:
+            self._aggregate(opt)
+        finally:
+            self.rows = all_rows
+
+    def _rule_kwargs(self):
+        if self.gar_name == "condense":
+            return dict(self.gar_kwargs, seed=self._condense_seed)
+        return self.gar_kwargs
+
+    def _aggregate(self, opt):
+        if self.gar_name == "condense":
+            # a fresh Bernoulli mask per step and per coordinate shard (the reference draws one per call, aggregators/condense.py:35)
+            base = int(self.gar_kwargs.get("seed", 0))
+            self._condense_seed = (base * 0x9E3779B97F4A7C15 + (self.steps_done + 1) * 0xBF58476D1CE4E5B9 + self.lo * 0x94D049BB133111EB) & (2 ** 63 - 1)
         if self._tail_at is not None and self._early_ws is not None:
             early, self._early_ws = self._early_ws["dist"], None
             head = [row[:self._tail_at] for row in self.rows]
@@ -557,9 +606,9 @@ class SSMWEngine:
         elif self.sharded:
             if opt is None:  # empty slice: still take part in the distance all-reduce
                 raise RuntimeError("empty coordinate slice: use fewer ranks than d / 64")
-            run = lambda **kw: gar_ops.aggregate_sharded(self.gar_name, self.rows, self.f, self._allreduce, **kw, **self.gar_kwargs)
+            run = lambda **kw: gar_ops.aggregate_sharded(self.gar_name, self.rows, self.f, self._allreduce, **kw, **self._rule_kwargs())
         else:
-            run = lambda **kw: gar_ops.aggregate(self.gar_name, self.rows, self.f, **kw, **self.gar_kwargs)
+            run = lambda **kw: gar_ops.aggregate(self.gar_name, self.rows, self.f, **kw, **self._rule_kwargs())
         if opt.name == "sgd":
             run(update=opt.sgd_fusion(self.mirrors), want_out=False)
             opt.note_fused_step()
@@ -567,24 +616,57 @@ class SSMWEngine:
             opt.step(run(), mirrors=self.mirrors)
 
     # -- flag synchronisation -------------------------------------------------------------------------
-    def _signal(self, flag_ptr, value):
+    def _bump(self):
+        _lib.check(_lib.require().gb_epoch_bump(self._epoch_dev.data_ptr(), _lib.stream_ptr(self.device)))
+        _lib.count()
+        self._reductions_this_step = 0
+
+    def _signal(self, flag_ptr):
         import ctypes
-        lib = _lib.require()
-        _lib.check(lib.gb_flag_signal(ctypes.c_void_p(flag_ptr), value, _lib.stream_ptr(self.device)))
+        _lib.check(_lib.require().gb_flag_signal_ep(ctypes.c_void_p(flag_ptr), self._epoch_dev.data_ptr(), _lib.stream_ptr(self.device)))
         _lib.count()
 
-    def _wait(self, flag_ptrs, value):
+    def _wait(self, flag_ptrs, lag=0, arrived=None, patience=1):
+        import ctypes
+        table = (ctypes.c_void_p * len(flag_ptrs))(*flag_ptrs)
+        _lib.check(_lib.require().gb_flag_wait_ep(table, len(flag_ptrs), self._epoch_dev.data_ptr(), lag, patience * self.flag_timeout_ns, self._late.data_ptr(),
+                                                 arrived.data_ptr() if arrived is not None else None, _lib.stream_ptr(self.device)))
+        _lib.count()
+
+    def _quorum_rows(self):
+        """Quorum mode: the lead server (rank 0) decides which ranks' gradients made it — all of them, or at least the
+        quorum once the deadline has passed — and publishes that mask to every server rank; each server then hands the
+        rule only those workers' rows (reference: garfieldpp/server.py:134-155). One host read per step."""
         import ctypes
         lib = _lib.require()
-        table = (ctypes.c_void_p * len(flag_ptrs))(*flag_ptrs)
-        _lib.check(lib.gb_flag_wait(table, len(flag_ptrs), value, self.flag_timeout_ns, self._late.data_ptr(), _lib.stream_ptr(self.device)))
-        _lib.count()
+        need_ranks = max(1, min(self.world, -(-self.num_wait // self.max_local)))
+        if self.rank == 0:
+            k = len(self._servers)
+            flags = (ctypes.c_void_p * self.world)(*self._grad_flags)
+            words = (ctypes.c_void_p * k)(*[self._word(r, 4) for r in self._servers])
+            dflags = (ctypes.c_void_p * k)(*[self._word(r, 3) for r in self._servers])
+            _lib.check(lib.gb_quorum_decide(flags, self.world, self._epoch_dev.data_ptr(), need_ranks, self.flag_timeout_ns, words, dflags, k,
+                                            self._late.data_ptr(), _lib.stream_ptr(self.device)))
+            _lib.count()
+        self._wait([self._word(self.rank, 3)], patience=20)       # the lead server decides after ITS deadline (and gives up after 16)
+        mask_words = self.flag_arena.local[4:6].view(torch.int32).cpu()          # synchronises: the host picks the row subset
+        mask = (int(mask_words[0]) & 0xffffffff) | ((int(mask_words[1]) & 0xffffffff) << 32)
+        arrived = [bool((mask >> r) & 1) for r in range(self.world)]
+        self.last_arrived = arrived
+        if all(arrived):
+            return None
+        keep = [row for wid, row in enumerate(self.rows) if arrived[wid % self.world]]
+        from .. import aggregators
+        rule = aggregators.gars.get(self.gar_name)
+        if rule is not None and rule.check(gradients=[torch.zeros(1)] * len(keep), f=self.f, **self.gar_kwargs) is not None:
+            return None      # too few timely rows for this rule: fall back to everything that is in the arenas
+        return keep
 
     def wait_published(self):
         """Block the stream until every shard's parameters of the last step have landed in this rank's arena
         (flags mode defers that wait to the next step; NCCL mode already ends each step with a barrier)."""
         if self.sync == "flags" and self.epoch > 0:
-            self._wait(self._param_flags, self.epoch)
+            self._wait(self._param_flags)
 
     @property
     def late_peers(self):
@@ -596,23 +678,27 @@ class SSMWEngine:
         `stall=True` (fault injection, flags mode) makes this rank withhold its "gradients ready" signal."""
         if load:
             self.load_batches(iter_num)
+        if self._whole_step_capturable() and not stall:
+            return self._step_whole()
         if self.sync == "flags":
             self.epoch += 1
-            if self.epoch > 1:
-                self._wait(self._param_flags, self.epoch - 1)      # every shard published the previous update
+            self._bump()
+            self._wait(self._param_flags, lag=1)                   # every shard published the previous update
             self.compute_gradients()
             if not stall:
-                self._signal(self._my_grad_flag, self.epoch)
+                self._signal(self._my_grad_flag)
             if self.is_server:
-                self._wait(self._grad_flags, self.epoch)           # all ranks' gradient rows are complete (or late)
-                self.aggregate_and_update()
-                self._signal(self._my_param_flag, self.epoch)
+                rows = None
+                if self.num_wait:
+                    rows = self._quorum_rows()
+                else:
+                    self._wait(self._grad_flags)                   # all ranks' gradient rows are complete (or late)
+                self.aggregate_and_update(rows)
+                self._signal(self._my_param_flag)
             self.steps_done += 1
             if self.workers:
                 return torch.stack([w.loss for w in self.workers]).mean()
             return torch.zeros((), device=self.device)
-        if self._whole_step_capturable():
-            return self._step_whole()
         self.compute_gradients()
         self._barrier()                      # all gradient rows are complete
         if self.is_server:
@@ -625,15 +711,30 @@ class SSMWEngine:
 
     # -- single-GPU fast path: the WHOLE iteration (gradient pass, attacks, GAR + fused SGD, loss) is one CUDA graph ----
     def _whole_step_capturable(self):
-        return (self.world == 1 and self.use_graphs and self._whole_step is not False and self.workers and self.optimizer is not None
-                and self.optimizer.name == "sgd" and all(w.attack in (None, "reverse", "lie", "empire") for w in self.workers))
+        """One GPU, or several with flag synchronisation (no NCCL call in the step) and a server shard on every rank."""
+        multi = self.world > 1
+        if multi and not (self.sync == "flags" and self.sharded and not self.num_wait):
+            return False
+        attacks_ok = all(a in (None, "reverse", "lie", "empire") for a in
+                         (self.byzantine.values() if self.scatter else [w.attack for w in self.workers]))
+        return bool(self.use_graphs and self._whole_step is not False and self.workers and self.optimizer is not None
+                    and self.optimizer.name == "sgd" and attacks_ok and self.gar_name != "condense")   # condense: per-step seed argument
 
     def _step_body(self):
+        flags = self.sync == "flags"
+        if flags:
+            self._bump()
+            self._wait(self._param_flags, lag=1)
         self._run_workers()
-        for w in self.workers:
+        for w in ([] if self.scatter else self.workers):
             if w.attack is not None:
                 self._attack(w)
+        if flags:
+            self._signal(self._my_grad_flag)
+            self._wait(self._grad_flags)
         self.aggregate_and_update()
+        if flags:
+            self._signal(self._my_param_flag)
         self._step_loss.copy_(self._group_losses.mean() if self.fused is not None else torch.stack([w.loss for w in self.workers]).mean())
 
     def _step_whole(self):
@@ -663,6 +764,7 @@ class SSMWEngine:
             opt.note_fused_step()
             _lib.count(self._step_launches)
         self.steps_done += 1
+        self.epoch += 1
         return self._step_loss
 
     # -- evaluation and checkpoints -----------------------------------------------------------------------
@@ -719,6 +821,7 @@ class SSMWEngine:
         self.wait_published()
         torch.cuda.synchronize(self.device)
         if self.sync == "flags":
+            self.dist_arena.close()
             self.flag_arena.close()
         self.grad_arena.close()
         self.param_arena.close()

@@ -258,6 +258,20 @@ GB_API int gb_attack_collude(float const* const* rows, int fw, int64_t d, int ki
  * (garfieldpp/server.py:134-155). Only for kernels on different GPUs. */
 GB_API int gb_flag_signal(uint32_t* flag, uint32_t value, void* stream);
 GB_API int gb_flag_wait(uint32_t* const* flags, int count, uint32_t value, uint64_t timeout_ns, uint32_t* late, void* stream);
+/* The same with the epoch in DEVICE memory (a whole-iteration CUDA graph replays unchanged every step): gb_epoch_bump
+ * increments it, signal stores *epoch, wait targets *epoch - lag and reports per-flag arrival in arrived[count] (optional).
+ * gb_reduce_slots sums `nslots` small peer-visible buffers in slot order (the n x n partial distances of the coordinate
+ * shards) - the device-side replacement of the reference's gather over RPC / an NCCL all-reduce. */
+GB_API int gb_epoch_bump(uint32_t* epoch, void* stream);
+GB_API int gb_flag_signal_ep(uint32_t* flag, uint32_t const* epoch, void* stream);
+GB_API int gb_flag_wait_ep(uint32_t* const* flags, int count, uint32_t const* epoch, uint32_t lag, uint64_t timeout_ns, uint32_t* late,
+                           uint32_t* arrived, void* stream);
+GB_API int gb_reduce_slots(float const* const* slots, int nslots, int count, float* out, void* stream);
+/* Quorum decision of the lead server: wait for all `count` flags, or for the deadline with >= `quorum` of them; store the 64-bit
+ * arrival mask into words[i][0..1] of every rank and release decision_flags[i] with the epoch.
+ * ref: the first-q wait of garfieldpp/server.py:134-155. */
+GB_API int gb_quorum_decide(uint32_t* const* flags, int count, uint32_t const* epoch, int quorum, uint64_t timeout_ns, uint32_t* const* words,
+                            uint32_t* const* decision_flags, int n_out, uint32_t* late, void* stream);
 
 /* Gather `count` separate device tensors into their slots (element offsets) of one flat vector in one
  * launch per 112 tensors; table passed in kernel parameters (CUDA-graph capturable).

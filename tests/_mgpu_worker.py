@@ -24,6 +24,7 @@ def main():
                              byzantine={n - 1: "reverse"}, use_graphs=False, sharded=sharded, seed=99)
             for i in range(3):
                 eng.step(i)
+            eng.wait_published()          # flag synchronisation defers "parameters landed" to the next step
             torch.cuda.synchronize()
             flat = eng.flat.clone()
             gathered = [torch.empty_like(flat) for _ in range(world)]
@@ -61,6 +62,28 @@ def main():
     torch.testing.assert_close(finals[0], finals[1], rtol=1e-4, atol=1e-6)   # cuDNN wgrad is not bitwise reproducible
     if rank == 0:
         print("ok flags", flush=True)
+    # quorum: the last rank withholds its "gradients ready" signal; the lead server decides after the deadline, publishes the
+    # arrival mask, and every shard hands the rule ONLY the timely workers' rows (reference: server.get_gradients(i, n - f))
+    eng = SSMWEngine("cifarnet", "synthetic-cifar10", "cross-entropy", 8, 1, "median", 16, "sgd", dict(lr=0.05), use_graphs=False,
+                     sharded=True, seed=11, scatter_grads=False, flag_timeout=0.5, num_wait=8 - 8 // world)
+    for i in range(2):
+        eng.step(i)
+    assert eng.last_arrived == [True] * world
+    eng.wait_published()
+    torch.cuda.synchronize()
+    dist.barrier()
+    before = eng.flat.clone()
+    eng.step(2, stall=(rank == world - 1))
+    eng.wait_published()
+    torch.cuda.synchronize()
+    dist.barrier()
+    assert eng.last_arrived == [True] * (world - 1) + [False], eng.last_arrived
+    timely = [row for wid, row in enumerate(eng.rows) if wid % world != world - 1]
+    expect = before[eng.lo:eng.hi] - 0.05 * torch.stack([r.clone() for r in timely]).median(0)[0]
+    torch.testing.assert_close(eng.flat[eng.lo:eng.hi], expect, rtol=1e-5, atol=1e-7)
+    eng.close()
+    if rank == 0:
+        print("ok quorum", flush=True)
     # scatter mode (every gradient slice written straight into its aggregating rank's arena, owner-side attacks, CUDA graph)
     # against the pull-over-NVLink sharded server, on a model with BatchNorm and k×k / 1×1 / Linear weight-gradient paths
     finals = []
@@ -74,6 +97,7 @@ def main():
                     m.p = 0.0
         for i in range(4):
             eng.step(i)
+        eng.wait_published()
         torch.cuda.synchronize()
         finals.append(eng.master.to_reference_order(eng.flat).clone())
         eng.close()
@@ -84,6 +108,8 @@ def main():
                      byzantine={7: "lie"}, use_graphs=True, sharded=True, seed=17)
     assert eng.scatter
     losses = [eng.step(i).item() for i in range(3)]
+    eng.wait_published()
+    torch.cuda.synchronize()
     assert all(l == l for l in losses) and torch.isfinite(eng.flat).all()
     eng.close()
     if rank == 0:
