@@ -37,7 +37,7 @@ __all__ = ["DecentralizedEngine", "MSMWEngine"]
 
 
 class _Base:
-    def _init_dist(self, group, device):
+    def _init_dist(self, group, device, sync="flags", flag_timeout=20.0):
         self.group = group
         self.rank = dist.get_rank(group) if dist.is_initialized() else 0
         self.world = dist.get_world_size(group) if dist.is_initialized() else 1
@@ -45,10 +45,41 @@ class _Base:
         self._flag = torch.zeros(1, device=self.device)
         if not gar_ops.available():
             raise RuntimeError("the device engines need a CUDA device and the sm_100a library")
+        # Phase boundaries between ranks ("all gradients written", "all models published", ...) are device-side: every rank
+        # bumps a device-resident counter, releases its peer-mapped flag with it and polls the others' flags (one-warp kernel
+        # with a deadline). No NCCL call inside a step; sync="nccl" keeps the 4-byte all-reduce as a baseline.
+        self.sync = sync if self.world > 1 else "none"
+        self._flag_arena = None
+        if self.sync == "flags":
+            self._flag_arena = PeerArena(64, self.device, group)
+            self._seq = torch.zeros(1, dtype=torch.int32, device=self.device)
+            self._late = torch.zeros(1, dtype=torch.int32, device=self.device)
+            self._flag_timeout_ns = int(flag_timeout * 1e9)
+            self._flags = [self._flag_arena.peer(r).data_ptr() for r in range(self.world)]
 
     def _barrier(self):
-        if self.world > 1:
+        if self.world <= 1:
+            return
+        if self.sync != "flags":
             dist.all_reduce(self._flag, group=self.group)
+            return
+        import ctypes
+        from ..ops import _lib
+        lib, st = _lib.require(), _lib.stream_ptr(self.device)
+        _lib.check(lib.gb_epoch_bump(self._seq.data_ptr(), st))
+        _lib.check(lib.gb_flag_signal_ep(ctypes.c_void_p(self._flags[self.rank]), self._seq.data_ptr(), st))
+        table = (ctypes.c_void_p * self.world)(*self._flags)
+        _lib.check(lib.gb_flag_wait_ep(table, self.world, self._seq.data_ptr(), 0, self._flag_timeout_ns, self._late.data_ptr(), None, st))
+        _lib.count(3)
+
+    @property
+    def late_peers(self):
+        return int(self._late.item()) if self.sync == "flags" else 0
+
+    def _close_sync(self):
+        if self._flag_arena is not None:
+            self._flag_arena.close()
+            self._flag_arena = None
 
     @staticmethod
     def _attack_row(kind, row, honest_rows):
@@ -78,8 +109,8 @@ class DecentralizedEngine(_Base):
     """
 
     def __init__(self, model, dataset, loss, num_nodes, f, gar, batch, optimizer="sgd", opt_args=None, byzantine=None,
-                 non_iid=False, device=None, group=None, seed=1234, fuse_workers=None, use_graphs=True):
-        self._init_dist(group, device)
+                 non_iid=False, device=None, group=None, seed=1234, fuse_workers=None, use_graphs=True, sync="flags"):
+        self._init_dist(group, device, sync)
         self.n, self.f, self.gar_name, self.non_iid = num_nodes, f, gar, non_iid
         self.byzantine = dict(byzantine or {})
         torch.manual_seed(seed)
@@ -239,6 +270,7 @@ class DecentralizedEngine(_Base):
 
     def close(self):
         torch.cuda.synchronize(self.device)
+        self._close_sync()
         for arena in (self.aggrs, self.grads, self.params):
             arena.close()
 
@@ -259,8 +291,8 @@ class MSMWEngine(_Base):
 
     def __init__(self, model, dataset, loss, num_workers, num_ps, fw, fps, gar, batch, mar="median", optimizer="sgd", opt_args=None,
                  byzantine_workers=None, byzantine_servers=None, device=None, group=None, seed=1234, fuse_workers=None,
-                 use_graphs=True):
-        self._init_dist(group, device)
+                 use_graphs=True, sync="flags"):
+        self._init_dist(group, device, sync)
         self.n, self.num_ps, self.fw, self.fps = num_workers, num_ps, fw, fps
         self.gar_name, self.mar_name = gar, mar
         self.byz_w, self.byz_s = dict(byzantine_workers or {}), dict(byzantine_servers or {})
@@ -330,7 +362,10 @@ class MSMWEngine(_Base):
     def _fused_pass(self, iter_num, published):
         """Median of the published models once per rank, then all local workers' gradients in one pass."""
         shared = self.wmodels.local[:self.d]
-        gar_ops.coordwise(published, "median_lower", out=shared) if self.num_ps > 1 else shared.copy_(published[0])
+        if self.num_ps > 1:
+            gar_ops.coordwise(published, "median_lower", out=shared)
+        else:
+            gar_ops.aggregate("average", published[:1], 0, out=shared)
         bx, by = self._gdata.shape[0] // len(self.workers), self._gtarget.shape[0] // len(self.workers)
         for g, wrk in enumerate(self.workers):
             data, target = wrk["batches"][iter_num % len(wrk["batches"])]
@@ -375,7 +410,10 @@ class MSMWEngine(_Base):
             self._fused_pass(iter_num, published)
         for wrk in ([] if self.fused is not None else self.workers):
             mine = self.wmodels.local[wrk["slot"] * self.pitch:wrk["slot"] * self.pitch + self.d]
-            gar_ops.coordwise(published, "median_lower", out=mine) if self.num_ps > 1 else mine.copy_(published[0])
+            if self.num_ps > 1:
+                gar_ops.coordwise(published, "median_lower", out=mine)
+            else:
+                gar_ops.aggregate("average", published[:1], 0, out=mine)
             row = self._grad(self.rank, wrk["slot"])
             row.zero_()
             wrk["replica"].bind_grads(row)
@@ -408,8 +446,10 @@ class MSMWEngine(_Base):
             published = self._published()
             for srv in self.servers:
                 nxt = self._smodel(self.rank, srv["slot"], 1 - self.cur)
-                if self.mar_name in ("vanilla", "crash"):
-                    nxt.copy_(torch.stack(published).mean(0) if self.mar_name == "vanilla" else published[0])
+                if self.mar_name == "vanilla":
+                    gar_ops.aggregate("average", published, 0, out=nxt)
+                elif self.mar_name == "crash":
+                    gar_ops.aggregate("average", published[:1], 0, out=nxt)
                 else:
                     gar_ops.aggregate(self.mar_name, published, self.fps, out=nxt)
             self._barrier()
@@ -422,5 +462,6 @@ class MSMWEngine(_Base):
 
     def close(self):
         torch.cuda.synchronize(self.device)
+        self._close_sync()
         for arena in (self.smodels, self.wmodels, self.grads):
             arena.close()

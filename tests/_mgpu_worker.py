@@ -114,7 +114,52 @@ def main():
     eng.close()
     if rank == 0:
         print("ok scatter", flush=True)
+    topologies(rank, world)
     dist.destroy_process_group()
+
+
+def topologies(rank, world):
+    """MSMW (ByzSGD) and decentralized (LEARN) engines across ranks: replicas of honest servers / nodes stay identical on
+    every rank, a Byzantine server publishing garbage is voted out by the model median, flag and NCCL synchronisation agree."""
+    from garfield_b200.parallel.topologies import DecentralizedEngine, MSMWEngine
+    finals = []
+    for sync in ("flags", "nccl"):
+        eng = MSMWEngine("cifarnet", "synthetic-cifar10", "cross-entropy", 5, 3, 1, 1, "krum", 16, mar="median", opt_args=dict(lr=0.05, momentum=0.9),
+                         byzantine_workers={4: "reverse"}, byzantine_servers={2: "random"}, seed=21, sync=sync)
+        for i in range(4):
+            eng.step(i)
+        torch.cuda.synchronize()
+        dist.barrier()
+        # every honest server holds the same model (server k lives on rank k mod world)
+        mine = [eng.server_model(j).clone() for j, srv in enumerate(eng.servers) if not srv["attack"]]
+        ref = mine[0].clone() if (rank == 0 and mine) else torch.empty(eng.d, device="cuda")
+        dist.broadcast(ref, src=0)
+        for m in mine:
+            assert torch.isfinite(m).all() and torch.equal(m, ref), "honest server replicas diverged (%s)" % sync
+        assert eng.late_peers == 0
+        finals.append(ref.clone())
+        eng.close()
+    torch.testing.assert_close(finals[0], finals[1], rtol=1e-4, atol=1e-6)
+    if rank == 0:
+        print("ok msmw", flush=True)
+    finals = []
+    for sync in ("flags", "nccl"):
+        eng = DecentralizedEngine("cifarnet", "synthetic-cifar10", "cross-entropy", 8, 1, "median", 16, opt_args=dict(lr=0.05, momentum=0.9),
+                                  byzantine={7: "lie"}, non_iid=True, seed=23, sync=sync)
+        for i in range(4):
+            eng.step(i)
+        torch.cuda.synchronize()
+        dist.barrier()
+        models = [eng.model_of(j).clone() for j in range(len(eng.nodes))]
+        ref = models[0].clone() if rank == 0 else torch.empty(eng.d, device="cuda")
+        dist.broadcast(ref, src=0)
+        for m in models:
+            assert torch.isfinite(m).all() and torch.equal(m, ref), "node models diverged after the contract step (%s)" % sync
+        finals.append(ref.clone())
+        eng.close()
+    torch.testing.assert_close(finals[0], finals[1], rtol=1e-4, atol=1e-6)
+    if rank == 0:
+        print("ok learn", flush=True)
 
 
 if __name__ == "__main__":

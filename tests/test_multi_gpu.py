@@ -23,5 +23,5 @@ def test_sharded_equals_centralized_over_peer_memory():
            "--master-port", str(port), str(ROOT / "tests" / "_mgpu_worker.py")]
     proc = subprocess.run(cmd, capture_output=True, text=True, timeout=600, cwd=str(ROOT))
     assert proc.returncode == 0, proc.stdout[-3000:] + proc.stderr[-3000:]
-    for gar in ("krum", "median", "bulyan", "brute", "aksel", "flags", "quorum", "scatter"):
+    for gar in ("krum", "median", "bulyan", "brute", "aksel", "flags", "quorum", "scatter", "msmw", "learn"):
         assert "ok " + gar in proc.stdout
