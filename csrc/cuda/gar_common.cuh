@@ -43,6 +43,7 @@ struct FusedUpdate {
     float* param;
     float* mom;
     float* mirror[kMaxMirrors];
+    float* multicast;  // NVLS multicast address of `param` (or null): publication by multimem.st
 };
 
 struct CoordArgs {

@@ -59,7 +59,9 @@ extern "C" GB_API int gb_coordwise(float const* const* rows, int n, int64_t d, i
         if (upd->param == nullptr || (upd->momentum != 0.0f && upd->mom == nullptr)) return cuda_fail("coordwise: fused update needs param (and momentum) buffers");
         a.upd.mode = upd->mode; a.upd.nesterov = upd->nesterov; a.upd.first_step = upd->first_step; a.upd.n_mirrors = upd->n_mirrors;
         a.upd.lr = upd->lr; a.upd.momentum = upd->momentum; a.upd.dampening = upd->dampening; a.upd.weight_decay = upd->weight_decay;
-        a.upd.param = upd->param; a.upd.mom = upd->mom;
+        a.upd.param = upd->param; a.upd.mom = upd->mom; a.upd.multicast = upd->multicast;
+        if (upd->multicast != nullptr && upd->n_mirrors != 0) return cuda_fail("coordwise: multicast publication excludes per-peer mirrors");
+        aligned = aligned && (reinterpret_cast<uintptr_t>(upd->multicast) & 15u) == 0;
         aligned = aligned && (reinterpret_cast<uintptr_t>(upd->param) & 15u) == 0 && (reinterpret_cast<uintptr_t>(upd->mom) & 15u) == 0;
         for (int k = 0; k < upd->n_mirrors; ++k) {
             a.upd.mirror[k] = upd->mirror[k];

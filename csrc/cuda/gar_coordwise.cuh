@@ -69,6 +69,12 @@ __device__ __forceinline__ void apply_update(FusedUpdate const& u, long long x, 
     }
 #pragma unroll
     for (int e = 0; e < V; ++e) p[e] = fmaf(-u.lr, g[e], p[e]);
+    if (u.multicast != nullptr) {   // one multicast store reaches every GPU's parameter arena (this one included)
+        if constexpr (V == 4) ptx::multimem_st(u.multicast + x, make_float4(p[0], p[1], p[2], p[3]));
+        else if constexpr (V == 2) ptx::multimem_st(u.multicast + x, make_float2(p[0], p[1]));
+        else ptx::multimem_st(u.multicast + x, p[0]);
+        return;
+    }
     vec_store<V>(u.param + x, p);
 #pragma unroll
     for (int k = 0; k < kMaxMirrors; ++k)

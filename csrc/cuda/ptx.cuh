@@ -202,6 +202,24 @@ __device__ __forceinline__ uint64_t globaltimer_ns() {
     return t;
 }
 
+// ------------------------------------------------------------------ NVLS multimem ---
+// `addr` is a multicast address (one virtual address bound to the same buffer on every GPU of the group): a store lands in
+// every GPU's copy, a ld_reduce returns the sum of all copies, computed inside the NVSwitch.
+__device__ __forceinline__ void multimem_st(float* addr, float4 v) {
+    asm volatile("multimem.st.weak.global.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(addr), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w) : "memory");
+}
+__device__ __forceinline__ void multimem_st(float* addr, float2 v) {
+    asm volatile("multimem.st.weak.global.v2.f32 [%0], {%1, %2};" ::"l"(addr), "f"(v.x), "f"(v.y) : "memory");
+}
+__device__ __forceinline__ void multimem_st(float* addr, float v) {
+    asm volatile("multimem.st.weak.global.f32 [%0], %1;" ::"l"(addr), "f"(v) : "memory");
+}
+__device__ __forceinline__ float4 multimem_ld_reduce_add(const float* addr) {
+    float4 v;
+    asm volatile("multimem.ld_reduce.weak.global.add.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(addr) : "memory");
+    return v;
+}
+
 // ----------------------------------------------------------- streaming vector access ---
 
 __device__ __forceinline__ float4 ldg_stream(const float4* p) {

@@ -23,7 +23,7 @@ class FusedUpdate(ctypes.Structure):
     """Mirror of `gb_fused_update`."""
     _fields_ = [("mode", i32), ("nesterov", i32), ("first_step", i32), ("n_mirrors", i32),
                 ("lr", f32), ("momentum", f32), ("dampening", f32), ("weight_decay", f32),
-                ("param", vp), ("mom", vp), ("mirror", vp * 8)]
+                ("param", vp), ("mom", vp), ("mirror", vp * 8), ("multicast", vp)]
 
 
 def _declare(h):
@@ -64,6 +64,9 @@ def _declare(h):
     h.gb_flag_wait_ep.argtypes = [pp, i32, vp, ctypes.c_uint32, u64, vp, vp, vp]
     h.gb_reduce_slots.argtypes = [pp, i32, i32, vp, vp]
     h.gb_quorum_decide.argtypes = [pp, i32, vp, i32, u64, pp, pp, i32, vp, vp]
+    h.gb_gossip_rounds.argtypes = [pp, pp, i32, i64, i32, i32, i32, pp, pp, i32, i32, i32, vp, vp, pp, i32, vp, u64, vp, vp]
+    h.gb_pull_median_operand.argtypes = [pp, i32, i32, i32, i32, vp, vp, vp]
+    h.gb_multimem_average.argtypes = [vp, vp, i32, i64, i64, i64, f32, vp]
     h.gb_multi_copy.argtypes = [pp, vp, vp, i32, vp, vp]
     h.gb_global_avgpool_forward.argtypes = [vp, vp, i64, i32, vp]
     h.gb_global_avgpool_backward.argtypes = [vp, vp, i64, i32, vp]

@@ -133,7 +133,9 @@ def conv_fprop(x, w, bias=None, stride=1, padding=0, relu=False, out=None, cache
             cols, _, _ = _im2col(x, (kh, kw), stride, padding)
             if cache is not None:
                 cache["cols"] = cols
-            w2 = _pad_weight(w.view(cout, -1), cols.shape[1])
+            w2 = cache.get("w2") if cache is not None else None      # operand emitted by the model-pull kernel (MSMW path 3)
+            if w2 is None or tuple(w2.shape) != (cout, cols.shape[1]):
+                w2 = _pad_weight(w.view(cout, -1), cols.shape[1])
             _lib.check(lib.gb_conv_fprop_tc(cols.data_ptr(), w2.data_ptr(), b, y.data_ptr(), cols.shape[0], 1, 1, cols.shape[1], cols.shape[1], cout,
                                             _pitch(y), 1, 1, 1, 1, 0, 0, int(relu), _st(x)))
             _lib.count()

@@ -77,10 +77,11 @@ class SgdFusion:
     (typically peer-mapped) that receive the updated parameters."""
 
     def __init__(self, param, mom, lr, momentum=0.0, dampening=0.0, weight_decay=0.0, nesterov=False,
-                 first_step=False, mirrors=()):
+                 first_step=False, mirrors=(), multicast=None):
         self.param, self.mom, self.lr, self.momentum = param, mom, lr, momentum
         self.dampening, self.weight_decay, self.nesterov = dampening, weight_decay, nesterov
         self.first_step, self.mirrors = first_step, tuple(mirrors)
+        self.multicast = multicast          # NVLS multicast address of `param` (int) or None: publish by multimem.st
 
     def struct(self):
         u = FusedUpdate()
@@ -90,6 +91,7 @@ class SgdFusion:
         u.mom = self.mom.data_ptr() if self.mom is not None else None
         for k, t in enumerate(self.mirrors):
             u.mirror[k] = t.data_ptr() if isinstance(t, torch.Tensor) else int(t)
+        u.multicast = int(self.multicast) if self.multicast else None
         return u
 
 
@@ -229,6 +231,38 @@ def aggregate(name, gradients, f, m=None, update=None, want_out=True, out=None, 
         mode = kw.get("mode", "mid")
         return aksel(gradients, (n + 1) // 2 if mode == "mid" else n - f, **common)
     raise KeyError("unknown aggregation rule %r" % (name,))
+
+
+GOSSIP_RULES = {"median": ("median_lower", lambda n, f: 0), "trimmed_mean": ("trimmed_mean", lambda n, f: f),
+                "averaged_median": ("averaged_median", lambda n, f: n - f)}
+
+
+def gossip_rounds(name, rows0, rows1, out0, out1, f, rounds, first_parity, seq, counter, my_flag=None, peer_flags=(), timeout_ns=20_000_000_000,
+                  late=None):
+    """`rounds` agreement rounds of the per-coordinate rule `name` inside one persistent kernel (csrc/cuda/gar_gossip.cu).
+    rows0 / rows1: all n nodes' vectors of parity 0 / 1 (local or peer-mapped); out0 / out1: the local nodes' buffers that
+    receive the result of a round reading parity 0 / 1. `seq`, `counter`: int32 device words (counter is zeroed here)."""
+    rule, rank_of = GOSSIP_RULES[name]
+    n, d, device = len(rows0), rows0[0].numel(), rows0[0].device
+    lib = _lib.require()
+    counter.zero_()
+    table = lambda ts: (ctypes.c_void_p * max(1, len(ts)))(*[t.data_ptr() if isinstance(t, torch.Tensor) else int(t) for t in ts])
+    with torch.cuda.device(device):
+        _lib.check(lib.gb_gossip_rounds(table(rows0), table(rows1), n, d, RULES[rule], int(rank_of(n, f)), 0, table(out0), table(out1), len(out0),
+                                        int(rounds), int(first_parity), seq.data_ptr(), ctypes.c_void_p(my_flag) if my_flag else None,
+                                        table(list(peer_flags)), len(peer_flags), counter.data_ptr(), int(timeout_ns),
+                                        late.data_ptr() if late is not None else None, _lib.stream_ptr(device)))
+    _lib.count()
+
+
+def pull_median_operand(rows, rows_out, k, flat, operand):
+    """Head of the MSMW model pull: lower median of the replicas' first-layer weights ([rows_out, k] each) into `flat` and,
+    zero-padded, into `operand` [rows_out, kpad] (csrc/cuda/gar_pull.cu)."""
+    lib = _lib.require()
+    with torch.cuda.device(flat.device):
+        _lib.check(lib.gb_pull_median_operand(_lib.row_table(rows), len(rows), rows_out, k, operand.shape[1], flat.data_ptr(), operand.data_ptr(),
+                                              _lib.stream_ptr(flat.device)))
+    _lib.count()
 
 
 def select_only(ws, n, device, mode, f=0, m=0, neighbors=0, squared=True):

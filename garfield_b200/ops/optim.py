@@ -79,15 +79,16 @@ class FlatOptimizer(torch.optim.Optimizer):
         for k, v in sd["state"].items():
             slot[k] = v.to(self.param.device).clone()
 
-    def sgd_fusion(self, mirrors=()):
-        """`ops.gar.SgdFusion` describing this optimizer's next step (SGD only)."""
+    def sgd_fusion(self, mirrors=(), multicast=None):
+        """`ops.gar.SgdFusion` describing this optimizer's next step (SGD only). `multicast`: NVLS multicast address of the
+        parameter slice — publication to every GPU by one multimem.st instead of one store per mirror."""
         from .gar import SgdFusion
         if self.name != "sgd":
             raise ValueError("only SGD can be fused into the aggregation epilogue")
         h = self.hyper
         mom = self._buf("momentum_buffer") if h["momentum"] != 0 else None
         return SgdFusion(self.param, mom, h["lr"], h["momentum"], h["dampening"], h["weight_decay"], h["nesterov"],
-                         first_step=(self.steps == 0), mirrors=mirrors)
+                         first_step=(self.steps == 0), mirrors=() if multicast else mirrors, multicast=multicast)
 
     def note_fused_step(self):
         self.steps += 1

@@ -26,7 +26,7 @@ import torch
 import torch.distributed as dist
 
 from .arena import FlatModel
-from .peer import DeviceBuffer, PeerArena
+from .peer import DeviceBuffer, PeerArena, make_arena
 from ..garfieldpp import tools
 from ..garfieldpp.datasets import DatasetManager
 from ..ops import _lib, attacks, gar as gar_ops
@@ -207,7 +207,10 @@ class SSMWEngine:
 
         # peer-mapped arenas: parameters (one per rank) and gradient rows (max_local full rows per rank, or — scatter —
         # one slice-long row per worker of the whole job)
-        self.param_arena = PeerArena(self.pitch, self.device, group)
+        import os
+        # parameters are published to every GPU through an NVLS multicast address when the platform has one (multimem.st in the
+        # aggregation epilogue: one store per 16 bytes instead of one per peer); GARFIELD_MULTICAST=0 keeps per-peer stores
+        self.param_arena = make_arena(self.pitch, self.device, group, multicast=os.environ.get("GARFIELD_MULTICAST", "1") != "0")
         self.grad_arena = PeerArena(self.world * self.max_local * self.per if self.scatter else self.max_local * self.pitch, self.device, group)
         self.flat = self.param_arena.local[:self.d]
         self.master = FlatModel(module, self.device, flat=None, channels_last=self.channels_last)
@@ -271,6 +274,7 @@ class SSMWEngine:
                 else:
                     self.rows.append(self.grad_arena.peer(owner)[j * self.pitch + self.lo:j * self.pitch + self.hi])
             self.mirrors = [self.param_arena.peer(r)[self.lo:self.hi] for r in range(self.world) if r != self.rank]
+            self.multicast = (self.param_arena.multicast_ptr + 4 * self.lo) if self.param_arena.multicast_ptr else None
         self._flag = torch.zeros(1, device=self.device)
         # sync="flags": peer-mapped epoch flags polled by a one-warp kernel with a deadline instead of NCCL barriers, and
         # peer-visible slots + a fixed-order sum instead of the NCCL all-reduce of the partial distances. The epoch lives in
@@ -610,7 +614,7 @@ class SSMWEngine:
         else:
             run = lambda **kw: gar_ops.aggregate(self.gar_name, self.rows, self.f, **kw, **self._rule_kwargs())
         if opt.name == "sgd":
-            run(update=opt.sgd_fusion(self.mirrors), want_out=False)
+            run(update=opt.sgd_fusion(self.mirrors, multicast=getattr(self, "multicast", None)), want_out=False)
             opt.note_fused_step()
         else:
             opt.step(run(), mirrors=self.mirrors)

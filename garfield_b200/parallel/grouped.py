@@ -400,7 +400,7 @@ class _TcConv(torch.autograd.Function):
             x = x.contiguous(memory_format=torch.channels_last)
         ctx.save_for_backward(x, w)
         ctx.cfg = (owner, conv, widx, bidx)
-        cache = {}
+        cache = {"w2": getattr(conv, "_gb_w2", None)}
         ho, wo = convops.out_size(x.shape[2], x.shape[3], conv.kernel_size, conv.stride, conv.padding)
         # the output is allocated here in its logical NCHW shape (channels-last strides) so that autograd sees a fresh tensor,
         # not a view — layers after it may work in place

@@ -17,7 +17,7 @@ import torch.distributed as dist
 
 from ..ops import _lib
 
-__all__ = ["DeviceBuffer", "PeerArena", "tensor_from_ptr"]
+__all__ = ["DeviceBuffer", "PeerArena", "SymmArena", "make_arena", "tensor_from_ptr"]
 
 
 class _CudaArray:
@@ -80,6 +80,7 @@ class PeerArena:
         self.local = self._own.tensor
         self._peers = {self.rank: self.local}
         self._opened = []
+        self.multicast_ptr = 0
         if self.world > 1:
             handles = [None] * self.world
             dist.all_gather_object(handles, self._own.ipc_handle(), group=group)
@@ -106,3 +107,58 @@ class PeerArena:
                 lib.gb_ipc_close(ctypes.c_void_p(ptr))
         self._opened = []
         self._own.free()
+
+
+class SymmArena:
+    """PeerArena on torch symmetric memory: the same per-rank buffer mapped into every rank, plus — where the fabric supports
+    NVLS — ONE multicast address bound to all ranks' buffers (`multicast_ptr`, 0 when unavailable). Kernels of this library
+    use it with `multimem.st` (a store that lands in every GPU's copy) and `multimem.ld_reduce` (a load that returns the sum
+    of all copies, added inside the NVSwitch). torch only allocates and exchanges handles; every access is ours."""
+
+    def __init__(self, nelem, device, group=None):
+        import torch.distributed._symmetric_memory as symm
+        self.group = group if group is not None else dist.group.WORLD
+        self.rank = dist.get_rank(group)
+        self.world = dist.get_world_size(group)
+        self.device = torch.device(device)
+        self.nelem = int(nelem)
+        with torch.cuda.device(self.device):
+            self._tensor = symm.empty(self.nelem, dtype=torch.float32, device=self.device)
+            self._handle = symm.rendezvous(self._tensor, self.group)
+        self.local = self._tensor
+        self.local.zero_()
+        ptrs = list(self._handle.buffer_ptrs)
+        self._peers = {r: (self.local if r == self.rank else tensor_from_ptr(ptrs[r], self.nelem, self.device, owner=self)) for r in range(self.world)}
+        self.multicast_ptr = int(getattr(self._handle, "multicast_ptr", 0) or 0)
+        torch.cuda.synchronize(self.device)
+        dist.barrier(group=group)
+
+    def peer(self, rank):
+        return self._peers[rank]
+
+    def close(self):
+        if dist.is_initialized():
+            torch.cuda.synchronize(self.device)
+            dist.barrier(group=self.group)
+        self._peers = {}
+        self._handle = None
+        self._tensor = None
+
+
+def make_arena(nelem, device, group=None, multicast=False):
+    """A peer arena; with `multicast=True` and several ranks, one on symmetric memory with an NVLS multicast address when
+    the platform provides it (falls back to the CUDA-IPC arena, whose `multicast_ptr` is 0)."""
+    world = dist.get_world_size(group) if dist.is_initialized() else 1
+    if multicast and world > 1:
+        try:
+            arena = SymmArena(nelem, device, group)
+            ok = torch.tensor([1 if arena.multicast_ptr else 0], device=device)
+            dist.all_reduce(ok, op=dist.ReduceOp.MIN, group=group)
+            if int(ok.item()):
+                return arena
+            arena.close()
+        except Exception:
+            pass
+    arena = PeerArena(nelem, device, group)
+    arena.multicast_ptr = 0
+    return arena

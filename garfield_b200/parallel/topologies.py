@@ -27,7 +27,7 @@ import torch.distributed as dist
 
 from .arena import FlatModel
 from .grouped import GroupedWorkers
-from .peer import PeerArena
+from .peer import PeerArena, make_arena
 from ..garfieldpp import tools
 from ..garfieldpp.datasets import DatasetManager
 from ..ops import attacks, gar as gar_ops
@@ -133,9 +133,13 @@ class DecentralizedEngine(_Base):
         slots = (self.n + self.world - 1) // self.world
         self.slots = slots
         # per node: 2 parameter buffers (double-buffered), 1 gradient row, 2 aggregated-gradient buffers
-        self.params = PeerArena(slots * 2 * self.pitch, self.device, group)
+        # gar = average: the agreement rounds and the contract step are in-switch reductions (multimem.ld_reduce / multimem.st)
+        # over a multicast address — the double-buffered arenas then live in symmetric memory
+        want_mc = gar == "average" and self.world > 1 and self.n % self.world == 0 and self.sync == "flags"
+        self.params = make_arena(slots * 2 * self.pitch, self.device, group, multicast=want_mc)
         self.grads = PeerArena(slots * self.pitch, self.device, group)
-        self.aggrs = PeerArena(slots * 2 * self.pitch, self.device, group)
+        self.aggrs = make_arena(slots * 2 * self.pitch, self.device, group, multicast=want_mc)
+        self._nvls = bool(want_mc and self.params.multicast_ptr and self.aggrs.multicast_ptr)
         init = FlatModel(module, self.device, channels_last=self.channels_last)
         self.layout = init
         if self.world > 1:
@@ -153,6 +157,12 @@ class DecentralizedEngine(_Base):
             opt = FlatOptimizer(live, optimizer, **(opt_args or {}))
             self.nodes.append(dict(id=k, slot=j, replica=replica, batches=batches, opt=opt, loss_fn=loss_fn,
                                    attack=self.byzantine.get(k), loss=torch.zeros((), device=self.device)))
+        # Agreement rounds and the contract step of per-coordinate rules run inside ONE persistent kernel per GPU
+        # (csrc/cuda/gar_gossip.cu): rounds separated by a grid barrier + peer flags instead of kernel relaunches and barriers.
+        self._gossip_ok = (gar in gar_ops.GOSSIP_RULES and self.n <= 16 and 1 <= len(self.nodes) <= 8
+                           and (self.world == 1 or self.sync == "flags"))
+        self._gseq = torch.zeros(1, dtype=torch.int32, device=self.device)
+        self._gcounter = torch.zeros(1, dtype=torch.int32, device=self.device)
         self.fused, self._graph, self._eager_passes, self.use_graphs = None, None, 0, use_graphs
         if self.fuse and self.nodes:
             G = len(self.nodes)
@@ -190,6 +200,33 @@ class DecentralizedEngine(_Base):
                 self.fused.forward_backward(self._gdata, self._gtarget, self._glosses)
             self._graph = graph
         self._graph.replay()
+
+    def _nvls_average(self, arena, src_parity):
+        """All nodes' parity-`src_parity` vectors of `arena` → their average in every node's other-parity vector: this rank
+        reduces its coordinate slice inside the switch and multicasts the result (call between two phase barriers)."""
+        import ctypes
+        from ..ops import _lib
+        per = (self.pitch // 4 + self.world - 1) // self.world * 4
+        lo, hi = min(self.pitch, self.rank * per), min(self.pitch, self.rank * per + per)
+        mc = arena.multicast_ptr
+        # slot s, parity p starts at (2 s + p)·pitch: consecutive slots of one parity are 2·pitch apart
+        src, dst = mc + 4 * src_parity * self.pitch, mc + 4 * (1 - src_parity) * self.pitch
+        _lib.check(_lib.require().gb_multimem_average(ctypes.c_void_p(src), ctypes.c_void_p(dst), self.slots, 2 * self.pitch, lo, hi,
+                                                     1.0 / self.n, _lib.stream_ptr(self.device)))
+        _lib.count()
+
+    def _gossip(self, getter, rounds, first):
+        """`rounds` rounds of the rule over every node's double-buffered vectors (`getter(rank, slot, parity)`) in one launch;
+        the result of a round reading parity p lands in parity 1 − p of every local node."""
+        rows0, rows1 = self._all(getter, 0), self._all(getter, 1)
+        out0 = [getter(self.rank, node["slot"], 1) for node in self.nodes]
+        out1 = [getter(self.rank, node["slot"], 0) for node in self.nodes]
+        my_flag, peers = None, []
+        if self.world > 1:
+            my_flag = self._flags[self.rank] + 4                   # word 1 of the flag arena (word 0 = phase barrier)
+            peers = [self._flags[r] + 4 for r in range(self.world) if r != self.rank]
+        gar_ops.gossip_rounds(self.gar_name, rows0, rows1, out0, out1, self.f, rounds, first, self._gseq, self._gcounter, my_flag, peers,
+                              timeout_ns=getattr(self, "_flag_timeout_ns", 20_000_000_000), late=getattr(self, "_late", None))
 
     # arena views -----------------------------------------------------------------------------
     def _param(self, rank, slot, which):
@@ -243,7 +280,20 @@ class DecentralizedEngine(_Base):
                 node["opt"].note_fused_step()
             else:
                 gar_ops.aggregate(self.gar_name, rows, f, out=self._aggr(self.rank, node["slot"], which))
-        # 3. agreement rounds on the aggregated gradients (double-buffered)
+        # 3. agreement rounds on the aggregated gradients (double-buffered): one persistent kernel for all rounds, or — rules
+        #    that need a selection step per round — one launch per round and node
+        if rounds and self._nvls:
+            for _ in range(rounds):
+                self._barrier()
+                self._nvls_average(self.aggrs, which)
+                which = 1 - which
+            self._barrier()          # the other ranks' slices of the last round have landed in this rank's buffers
+            rounds = 0
+        if rounds and self._gossip_ok and self.nodes:
+            self._barrier()
+            self._gossip(self._aggr, rounds, which)
+            which = (which + rounds) & 1
+            rounds = 0
         for _ in range(rounds):
             self._barrier()
             peers = self._all(self._aggr, which)
@@ -254,10 +304,15 @@ class DecentralizedEngine(_Base):
         for node in ([] if fused_sgd else self.nodes):
             node["opt"].step(self._aggr(self.rank, node["slot"], which))
         self._barrier()
-        # 5. contract: model := GAR(all nodes' live models), written into the other buffer
-        models = self._all(self._param, self.cur)
-        for node in self.nodes:
-            gar_ops.aggregate(self.gar_name, models, f, out=self._param(self.rank, node["slot"], 1 - self.cur))
+        # 5. contract: model := GAR(all nodes' live models), written into the other buffer (one pass for all local nodes)
+        if self._nvls:
+            self._nvls_average(self.params, self.cur)
+        elif self._gossip_ok and self.nodes:
+            self._gossip(self._param, 1, self.cur)
+        else:
+            models = self._all(self._param, self.cur)
+            for node in self.nodes:
+                gar_ops.aggregate(self.gar_name, models, f, out=self._param(self.rank, node["slot"], 1 - self.cur))
         self._barrier()
         self.cur = 1 - self.cur
         for node in self.nodes:  # re-alias replicas and optimizers onto the now-live buffer
@@ -347,6 +402,7 @@ class MSMWEngine(_Base):
                 modules = dict(wrk["replica"].module.named_modules())
                 for name, (mean, var) in self.fused.running_tables.items():
                     modules[name]._buffers["running_mean"], modules[name]._buffers["running_var"] = mean[g], var[g]
+        self._setup_pipelined_pull()
         for j, s in enumerate(self.local_servers):
             for which in range(3):
                 self._smodel(self.rank, j, which).copy_(init.flat)
@@ -359,26 +415,85 @@ class MSMWEngine(_Base):
         x = x.contiguous(memory_format=torch.channels_last) if x.dim() == 4 else x.contiguous()
         return x.pin_memory()
 
-    def _fused_pass(self, iter_num, published):
-        """Median of the published models once per rank, then all local workers' gradients in one pass."""
+    def _setup_pipelined_pull(self):
+        """Path 3: the model pull is cut into coordinate chunks along the top-level children of the network (forward order =
+        parameter order). Chunk k's median kernel runs on a pull stream and records an event that child k's forward waits for,
+        so the pull of the deep layers crosses NVLink while the first layers already compute. When the first layer is a
+        convolution that needs an explicit zero-padded weight operand (the RGB stem), the head kernel of the pull emits that
+        GEMM operand directly (gb_pull_median_operand)."""
+        self._pull_chunks, self._pull_events, self._pull_stream, self._head = [], [], None, None
+        if self.fused is None or self.num_ps < 2:
+            return
+        module = self.fused.module
+        offsets = {id(p): (off, n) for p, (off, n, _) in zip(module.parameters(), self.fused.replica.slices)}
+        covered = 0
+        children = []
+        for child in module.children():
+            own = [offsets[id(p)] for p in child.parameters()]
+            if not own:
+                continue
+            lo, hi = min(o for o, _ in own), max(o + n for o, n in own)
+            if lo != covered:
+                return                      # parameters are not laid out child by child: keep the single-launch pull
+            covered = hi
+            children.append((child, lo, hi))
+        if covered != self.d or len(children) < 2:
+            return
+        self._pull_stream = torch.cuda.Stream(device=self.device)
+        first = children[0][0]
+        if (isinstance(first, torch.nn.Conv2d) and first.bias is None and first.groups == 1
+                and (first.in_channels * first.kernel_size[0] * first.kernel_size[1]) % 4 != 0):
+            k = first.in_channels * first.kernel_size[0] * first.kernel_size[1]
+            self._head = (first, first.out_channels, k, torch.zeros((first.out_channels, (k + 3) // 4 * 4), device=self.device))
+        for index, (child, lo, hi) in enumerate(children):
+            self._pull_chunks.append((lo, hi))
+            event = torch.cuda.Event()
+            self._pull_events.append(event)
+            child.register_forward_pre_hook(lambda _m, _inp, ev=event: torch.cuda.current_stream(self.device).wait_event(ev))
+
+    def _pull(self, published):
+        """Worker model := coordinate-wise median of the published server models (fused gather + median over peer rows)."""
         shared = self.wmodels.local[:self.d]
-        if self.num_ps > 1:
-            gar_ops.coordwise(published, "median_lower", out=shared)
-        else:
+        if self.num_ps < 2:
             gar_ops.aggregate("average", published[:1], 0, out=shared)
+            return
+        if not self._pull_chunks:
+            gar_ops.coordwise(published, "median_lower", out=shared)
+            return
+        main = torch.cuda.current_stream(self.device)
+        self._pull_stream.wait_stream(main)
+        with torch.cuda.stream(self._pull_stream):
+            for index, ((lo, hi), event) in enumerate(zip(self._pull_chunks, self._pull_events)):
+                rows = [p[lo:hi] for p in published]
+                if index == 0 and self._head is not None:
+                    conv, cout, k, operand = self._head
+                    gar_ops.pull_median_operand(rows, cout, k, shared[lo:hi], operand)
+                    conv._gb_w2 = operand
+                else:
+                    gar_ops.coordwise(rows, "median_lower", out=shared[lo:hi])
+                event.record(self._pull_stream)
+
+    def _fused_pass(self, iter_num, published):
+        """Median of the published models once per rank (pipelined with the forward pass), then all local workers' gradients
+        in one pass."""
         bx, by = self._gdata.shape[0] // len(self.workers), self._gtarget.shape[0] // len(self.workers)
         for g, wrk in enumerate(self.workers):
             data, target = wrk["batches"][iter_num % len(wrk["batches"])]
             self._gdata[g * bx:(g + 1) * bx].copy_(data, non_blocking=True)
             self._gtarget[g * by:(g + 1) * by].copy_(target, non_blocking=True)
-        if not self.use_graphs or self._eager_passes < 2:
+        def body():
+            self._pull(published)
             self.fused.forward_backward(self._gdata, self._gtarget, self._glosses)
+            if self._pull_stream is not None:
+                torch.cuda.current_stream(self.device).wait_stream(self._pull_stream)
+        if not self.use_graphs or self._eager_passes < 2:
+            body()
             self._eager_passes += 1
             return
         if self._graph is None:
             graph = torch.cuda.CUDAGraph()
             with torch.cuda.graph(graph):
-                self.fused.forward_backward(self._gdata, self._gtarget, self._glosses)
+                body()
             self._graph = graph
         self._graph.replay()
 

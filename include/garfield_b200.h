@@ -107,6 +107,8 @@ typedef struct gb_fused_update {
     float* param;
     float* mom;
     float* mirror[8];
+    float* multicast; /* optional NVLS multicast address of `param` (symmetric memory): the updated parameters are published to every
+                         GPU of the group with ONE multimem.st per 16 bytes instead of a store per mirror; n_mirrors must then be 0 */
 } gb_fused_update;
 
 /* Per-coordinate rules. rule: 0 linear (needs W 1×n), 1 lower median (NaN-propagating),
@@ -272,6 +274,22 @@ GB_API int gb_reduce_slots(float const* const* slots, int nslots, int count, flo
  * ref: the first-q wait of garfieldpp/server.py:134-155. */
 GB_API int gb_quorum_decide(uint32_t* const* flags, int count, uint32_t const* epoch, int quorum, uint64_t timeout_ns, uint32_t* const* words,
                             uint32_t* const* decision_flags, int n_out, uint32_t* late, void* stream);
+
+/* North-star path 4: `rounds` agreement rounds of a per-coordinate rule over the n nodes' double-buffered, peer-mapped vectors
+ * inside ONE persistent kernel per GPU (grid barrier + peer flags between rounds; see csrc/cuda/gar_gossip.cu).
+ * ref: avg_agree / contract loops of applications/LEARN/trainer.py:208-222,244-258. */
+GB_API int gb_gossip_rounds(float const* const* rows0, float const* const* rows1, int n, int64_t d, int rule, int rank, int upper,
+                            float* const* out0, float* const* out1, int n_out, int rounds, int first_parity, uint32_t* seq, uint32_t* my_flag,
+                            uint32_t* const* peer_flags, int n_peers, uint32_t* counter, uint64_t timeout_ns, uint32_t* late, void* stream);
+/* out (multicast address, every rank's copy) = scale * sum over ranks and over `slots` buffers of `pitch` floats of in (multicast
+ * address): NVLS in-switch reduction (multimem.ld_reduce) + multicast store (multimem.st) of this rank's coordinate slice
+ * [lo, hi) — the `average` contract step of the decentralized topology without any per-peer load. Call between two phase barriers.
+ * ref: gar=average in applications/LEARN/trainer.py:244-258. */
+GB_API int gb_multimem_average(float const* mc_in, float* mc_out, int slots, int64_t pitch, int64_t lo, int64_t hi, float scale, void* stream);
+/* North-star path 3 head: lower median of `replicas` servers' copies of the first layer's weight ([rows_out][k], rows may be
+ * peer-mapped) written into the flat model AND as the zero-padded K-major operand [rows_out][kpad] of the first forward GEMM.
+ * ref: applications/ByzSGD/trainer.py:237-244. */
+GB_API int gb_pull_median_operand(float const* const* rows, int replicas, int rows_out, int k, int kpad, float* flat, float* operand, void* stream);
 
 /* Gather `count` separate device tensors into their slots (element offsets) of one flat vector in one
  * launch per 112 tensors; table passed in kernel parameters (CUDA-graph capturable).

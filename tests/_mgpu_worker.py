@@ -160,6 +160,29 @@ def topologies(rank, world):
     torch.testing.assert_close(finals[0], finals[1], rtol=1e-4, atol=1e-6)
     if rank == 0:
         print("ok learn", flush=True)
+    # gar = average: agreement rounds and contract are in-switch reductions over an NVLS multicast address (multimem.ld_reduce /
+    # multimem.st) when the platform has one; the NCCL-synchronised engine keeps the per-peer loads — same models
+    finals, used = [], []
+    for sync in ("flags", "nccl"):
+        eng = DecentralizedEngine("cifarnet", "synthetic-cifar10", "cross-entropy", 8, 0, "average", 16, opt_args=dict(lr=0.05, momentum=0.9),
+                                  non_iid=True, seed=29, sync=sync)
+        used.append(eng._nvls)
+        for i in range(4):
+            eng.step(i)
+        torch.cuda.synchronize()
+        dist.barrier()
+        models = [eng.model_of(j).clone() for j in range(len(eng.nodes))]
+        for m in models[1:]:
+            assert torch.equal(m, models[0])
+        assert torch.isfinite(models[0]).all()
+        finals.append(models[0])
+        eng.close()
+    # the switch adds the ranks' copies in its own order: float rounding differs from the sequential sum, and four training
+    # steps carry that through the network
+    diff = (finals[0] - finals[1]).abs()
+    assert diff.max().item() < 2e-4 and (diff > 2e-6).float().mean().item() < 0.02, diff.max().item()
+    if rank == 0:
+        print("ok nvls-average (multicast used: %s)" % used[0], flush=True)
 
 
 if __name__ == "__main__":

@@ -617,3 +617,46 @@ def _compare_fused_resnet(torchvision, fuse_resnet_blocks, copy):
     torch.testing.assert_close(outs[1], outs[0], rtol=1e-4, atol=1e-7)
     ours.eval(); ref.eval()
     torch.testing.assert_close(ours(x), ref(x), rtol=1e-3, atol=1e-3)
+
+
+def test_gossip_rounds_kernel_matches_round_by_round():
+    """Path 4: several agreement rounds inside one persistent kernel == one coordwise launch per round. Two of the six nodes
+    are hosted here (their buffers follow the rounds), the other four keep whatever their buffers hold (stale peers)."""
+    cuda_lib()
+    from garfield_b200.ops import gar
+    torch.manual_seed(12)
+    n, d, local = 6, 70_001, (1, 4)
+    for name, f in (("median", 1), ("trimmed_mean", 1), ("averaged_median", 2)):
+        for rounds in (1, 2, 3):
+            bufs = [[torch.randn(d, device="cuda") for _ in range(n)] for _ in range(2)]      # bufs[parity][node]
+            ref = [[t.clone() for t in row] for row in bufs]
+            first = 1
+            parity = first
+            for _ in range(rounds):
+                out = gar.aggregate(name, ref[parity], f)
+                for k in local:
+                    ref[1 - parity][k].copy_(out)
+                parity = 1 - parity
+            seq = torch.zeros(1, dtype=torch.int32, device="cuda")
+            counter = torch.zeros(1, dtype=torch.int32, device="cuda")
+            gar.gossip_rounds(name, bufs[0], bufs[1], [bufs[1][k] for k in local], [bufs[0][k] for k in local], f, rounds, first, seq, counter)
+            torch.cuda.synchronize()
+            for p in range(2):
+                for k in range(n):
+                    assert torch.equal(bufs[p][k], ref[p][k]), (name, rounds, p, k)
+
+
+def test_pull_median_operand_matches_torch():
+    """Path 3 head: the median of the replicas' first-layer weights lands in the flat model and, zero-padded, in the GEMM operand."""
+    cuda_lib()
+    from garfield_b200.ops import gar
+    torch.manual_seed(13)
+    cout, k, kpad = 64, 147, 148
+    for replicas in (2, 3, 5):
+        rows = [torch.randn(cout * k + 33, device="cuda") for _ in range(replicas)]
+        flat = torch.full((cout * k,), float("nan"), device="cuda")
+        operand = torch.full((cout, kpad), float("nan"), device="cuda")
+        gar.pull_median_operand([r[:cout * k] for r in rows], cout, k, flat, operand)
+        want = torch.stack([r[:cout * k] for r in rows]).median(0)[0]
+        assert torch.equal(flat, want)
+        assert torch.equal(operand[:, :k], want.view(cout, k)) and (operand[:, k:] == 0).all()

@@ -22,6 +22,9 @@ def test_sharded_equals_centralized_over_peer_memory():
     cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", str(world), "--master-addr", "127.0.0.1",
            "--master-port", str(port), str(ROOT / "tests" / "_mgpu_worker.py")]
     proc = subprocess.run(cmd, capture_output=True, text=True, timeout=600, cwd=str(ROOT))
+    out_dir = ROOT / "gpurun_out"
+    if out_dir.is_dir():     # keep the per-section log of the run (what ran on how many GPUs) next to the other GPU artefacts
+        (out_dir / ("multi_gpu_test_%dgpu.log" % world)).write_text(proc.stdout[-20000:])
     assert proc.returncode == 0, proc.stdout[-3000:] + proc.stderr[-3000:]
-    for gar in ("krum", "median", "bulyan", "brute", "aksel", "flags", "quorum", "scatter", "msmw", "learn"):
+    for gar in ("krum", "median", "bulyan", "brute", "aksel", "flags", "quorum", "scatter", "msmw", "learn", "nvls-average"):
         assert "ok " + gar in proc.stdout
