@@ -110,6 +110,7 @@ __global__ void __launch_bounds__(kBnThreads) bn_nhwc_fwd_kernel(int rows, int C
     constexpr int kLanes = kBnThreads / QUADS;                          // row lanes per CTA
     BnGeom const t = bn_geometry<QUADS>(rows, C, splits);
     cudaGridDependencySynchronize();   // no-op unless launched with programmatic stream serialization
+    cudaTriggerProgrammaticLaunchCompletion();   // the next kernel may start its prologue
     {   // blockIdx.z = statistics group: a contiguous block of `rows` rows with its own mean/variance/running buffers
         long long const goff = static_cast<long long>(blockIdx.z) * rows * C;
         int const soff = blockIdx.z * C;
@@ -209,6 +210,7 @@ __global__ void __launch_bounds__(kBnThreads) bn_nhwc_bwd_kernel(int rows, int C
     constexpr int kLanes = kBnThreads / QUADS;
     BnGeom const t = bn_geometry<QUADS>(rows, C, splits);
     cudaGridDependencySynchronize();
+    cudaTriggerProgrammaticLaunchCompletion();
     {
         long long const goff = static_cast<long long>(blockIdx.z) * rows * C;
         int const soff = blockIdx.z * C;
@@ -315,7 +317,7 @@ inline BnPlan plan(int groups, int rows, int C) {
 }
 
 inline bool pdl_enabled() {
-    static int const on = [] { char const* v = std::getenv("GARFIELD_BN_PDL"); return v != nullptr && v[0] == '1' ? 1 : 0; }();
+    static int const on = [] { char const* v = std::getenv("GARFIELD_PDL"); return (v != nullptr && v[0] == '0') ? 0 : 1; }();
     return on != 0;
 }
 

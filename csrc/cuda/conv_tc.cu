@@ -202,6 +202,10 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
     ptx::tc_fence_after();
     uint32_t const tmem = sh.tmem_base;
     uint32_t const tap_mask = sh.tap_mask;
+    // Programmatic dependent launch: everything above (barriers, TMEM, descriptor prefetch) overlapped the tail of the kernel
+    // before us; from here on we touch its results. Let the kernel after us start ITS prologue right away.
+    cudaGridDependencySynchronize();
+    cudaTriggerProgrammaticLaunchCompletion();
     uint32_t const a_bytes = MODE < 2 ? static_cast<uint32_t>(g.bn * g.bh * g.bw) * 128u : kATile;
 
     if (warp == 0) {
@@ -373,6 +377,12 @@ bool make_pixel_map(CUtensorMap* map, const float* base, int C, int pitch, int W
     return make_map_nd(map, base, 5, dims, strides, box, estr, mn_major);
 }
 
+// GARFIELD_PDL=0 switches programmatic dependent launches off (plain stream order).
+bool pdl_enabled() {
+    static int const on = [] { char const* v = std::getenv("GARFIELD_PDL"); return (v != nullptr && v[0] == '0') ? 0 : 1; }();
+    return on != 0;
+}
+
 template <int BN, int MODE>
 cudaError_t launch_conv(CUtensorMap const& ma, CUtensorMap const& mb, ConvGeom& g, float* C, const float* bias, dim3 grid, cudaStream_t st) {
     auto kern = conv_tc_kernel<BN, MODE>;
@@ -393,8 +403,19 @@ cudaError_t launch_conv(CUtensorMap const& ma, CUtensorMap const& mb, ConvGeom& 
     if (stages > steps) stages = steps < 2 ? 2 : steps;
     g.stages = stages;
     size_t const smem = static_cast<size_t>(stages) * kStage + 1024;
-    kern<<<grid, kConvThreads, smem, st>>>(ma, mb, g, C, bias);
-    return cudaGetLastError();
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = grid;
+    cfg.blockDim = dim3(kConvThreads);
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    if (pdl_enabled()) {
+        attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+        attr[0].val.programmaticStreamSerializationAllowed = 1;
+        cfg.attrs = attr;
+        cfg.numAttrs = 1;
+    }
+    return cudaLaunchKernelEx(&cfg, kern, ma, mb, g, C, bias);
 }
 
 int map_fail(char const* what) {
