@@ -9,10 +9,14 @@ Counterpart of the reference's Quart demo (applications/LEARN/demo.py:95-446, RE
                                 epochs) and returns {"trainer_id": ...}
     GET  /status?trainer_id=ID  {"progress": percent} while running, then {"result": mean binary accuracy}
 
-The reference spawns n local processes talking over torch RPC; here the n nodes are role objects
-in one worker thread of this process (the local transport), reporting progress through a queue.
+Two ways of running the n nodes, as in the reference:
 
-    python applications/LEARN/demo.py --port 8080            # serve
+    --transport processes   n local processes named node:<rank> that talk over torch RPC on a fresh localhost port and report
+                            progress through a multiprocessing queue (what the reference does, demo.py:264-335);
+    --transport threads     the n nodes are role objects in one worker thread of this process (local transport; default —
+                            it needs no ports and starts in milliseconds).
+
+    python applications/LEARN/demo.py --port 8080            # serve (http://127.0.0.1:8080/ is the front-end)
     python applications/LEARN/demo.py --init_demo            # warm-up: build natives, load the dataset
 """
 import argparse
@@ -26,11 +30,17 @@ from http.server import BaseHTTPRequestHandler, ThreadingHTTPServer
 
 sys.path.insert(0, str(pathlib.Path(__file__).resolve().parents[2]))
 
-EPOCHS, BATCH, MAX_NODES = 15, 16, 10
-PAGE = """<!doctype html><title>garfield-b200 LEARN demo</title><h1>Decentralized Byzantine-resilient learning</h1>
-<form method=post>nodes n <input name=n value=5> Byzantine f <input name=f value=1>
-GAR <select name=gar><option>median<option>krum<option>average<option>brute<option>bulyan<option>trimmed_mean</select>
-<button>train</button></form><p>Poll <code>/status?trainer_id=ID</code> for progress.</p>"""
+import os
+
+EPOCHS, BATCH, MAX_NODES = int(os.environ.get("GARFIELD_DEMO_EPOCHS", "15")), 16, 10
+PAGE = (pathlib.Path(__file__).with_name("templates") / "index.html")
+TRANSPORT = ["threads"]
+
+
+def pima_source():
+    """Where the demo's table comes from: the real CSV, or the synthetic stand-in used when it is not installed."""
+    from garfield_b200.garfieldpp.datasets import PimaDiabetesDataset
+    return "pima_diabetes.csv" if getattr(PimaDiabetesDataset(train=False), "source", None) else "synthetic stand-in (pima_diabetes.csv not installed)"
 
 
 class Trainer:
@@ -46,7 +56,46 @@ class Trainer:
         self.thread.start()
         return self
 
+    def _train_processes(self):
+        """n processes over torch RPC; this thread only drains their progress queue."""
+        import socket
+        import torch.multiprocessing as mp
+        ctx = mp.get_context("spawn")
+        with socket.socket() as sock:
+            sock.bind(("127.0.0.1", 0))
+            port = sock.getsockname()[1]
+        events = ctx.Queue()
+        from garfield_b200.apps.learn_demo_node import node_process
+        procs = [ctx.Process(target=node_process, args=(r, self.n, self.f, self.gar, port, EPOCHS, BATCH, events), daemon=True) for r in range(self.n)]
+        progress, results, done = [0.0] * self.n, {}, 0
+        try:
+            for p in procs:
+                p.start()
+            while done < self.n:
+                try:
+                    msg = events.get(timeout=600)
+                except queue.Empty:
+                    raise TimeoutError("a node stopped reporting")
+                if "error" in msg:
+                    raise RuntimeError("node %d: %s" % (msg["rank"], msg["error"]))
+                progress[msg["rank"]] = msg["progress"]
+                self.progress = sum(progress) / self.n
+                if "result" in msg:
+                    done += 1
+                    if msg["result"] is not None:
+                        results[msg["rank"]] = msg["result"]
+            self.result = sum(results.values()) / max(1, len(results))
+        except Exception as err:
+            self.error = "%s: %s" % (type(err).__name__, err)
+        finally:
+            for p in procs:          # exactly the processes started above
+                p.join(timeout=30)
+                if p.is_alive():
+                    p.terminate()
+
     def _train(self):
+        if TRANSPORT[0] == "processes":
+            return self._train_processes()
         try:
             import torch
             import aggregators
@@ -83,11 +132,12 @@ class Trainer:
             self.error = "%s: %s" % (type(err).__name__, err)
 
     def status(self):
+        base = {"n": self.n, "f": self.f, "gar": self.gar, "transport": TRANSPORT[0], "dataset": pima_source()}
         if self.error:
-            return {"error": self.error}
+            return dict(base, error=self.error)
         if self.result is not None:
-            return {"result": self.result, "progress": 100.0}
-        return {"progress": round(self.progress, 2)}
+            return dict(base, result=self.result, progress=100.0)
+        return dict(base, progress=round(self.progress, 2))
 
 
 class Trainers:
@@ -132,8 +182,8 @@ class Handler(BaseHTTPRequestHandler):
 
     def do_GET(self):
         url = urllib.parse.urlparse(self.path)
-        if url.path == "/":
-            return self._send(200, PAGE, "text/html")
+        if url.path in ("/", "/index.html"):
+            return self._send(200, PAGE.read_text(), "text/html; charset=utf-8")
         if url.path == "/status":
             query = urllib.parse.parse_qs(url.query)
             try:
@@ -159,7 +209,7 @@ class Handler(BaseHTTPRequestHandler):
 def init_demo():
     """Pre-build the native libraries and touch the dataset (the reference's `quart init_demo`)."""
     import native
-    from garfieldpp.datasets import PimaDiabetesDataset
+    from garfield_b200.garfieldpp.datasets import PimaDiabetesDataset
     print("natives available:", native.available(), "| pima train rows:", len(PimaDiabetesDataset(train=True)))
 
 
@@ -168,7 +218,10 @@ def main(argv=None):
     ap.add_argument("--host", default="127.0.0.1")
     ap.add_argument("--port", type=int, default=8080)
     ap.add_argument("--init_demo", action="store_true")
+    ap.add_argument("--transport", default="threads", choices=["threads", "processes"],
+                    help="processes: n local processes over torch RPC (the reference's way); threads: in-process role objects")
     args = ap.parse_args(argv)
+    TRANSPORT[0] = args.transport
     if args.init_demo:
         return init_demo()
     server = ThreadingHTTPServer((args.host, args.port), Handler)

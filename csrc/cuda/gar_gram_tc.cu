@@ -32,6 +32,7 @@
 // remains the default for n <= 16 and the oracle in the tests.
 
 #include <cfloat>
+#include <cstdio>
 #include <cmath>
 
 #include "gar_common.cuh"
@@ -221,10 +222,10 @@ extern "C" GB_API int gb_gram_select_tc(float const* const* rows, int n, int64_t
     if (d < 1) return cuda_fail("gram_tc: empty rows");
     if (dist == nullptr || scratch == nullptr) return cuda_fail("gram_tc: missing output/scratch buffer");
     if (mode != kSelectNone && (W == nullptr || info == nullptr)) return cuda_fail("gram_tc: selection needs W and info buffers");
-    if (mode == kSelectMda) {
-        bool over = false;
-        unsigned long long const total = binomial(static_cast<unsigned>(n), static_cast<unsigned>(n - f), &over);
-        if (f < 1 || n < 2 * f + 1 || over || total > (1ull << 26)) return cuda_fail("gram_tc: invalid or too large MDA problem");
+    if (char const* bad = selection_error(mode, n, f, m, neighbors)) {
+        static thread_local char msg[160];
+        std::snprintf(msg, sizeof(msg), "gram_tc: %s", bad);
+        return cuda_fail(msg);
     }
     GramArgs a{};
     for (int i = 0; i < n; ++i) a.rows.p[i] = rows[i];

@@ -18,6 +18,7 @@
 //     deterministic distances.
 
 #include <cfloat>
+#include <cstdio>
 #include <cmath>
 #include <mutex>
 
@@ -281,26 +282,10 @@ extern "C" GB_API int gb_pairwise_select(float const* const* rows, int n, int64_
     if (d < 1) return cuda_fail("pairwise: empty rows");
     if (dist == nullptr || scratch == nullptr) return cuda_fail("pairwise: missing output/scratch buffer");
     if (mode != kSelectNone && (W == nullptr || info == nullptr)) return cuda_fail("pairwise: selection needs W and info buffers");
-    switch (mode) {
-        case kSelectNone: break;
-        case kSelectKrum:
-            if (f < 1 || n < 2 * f + 3 || m < 1 || m > n - f - 2 || neighbors < 1 || neighbors > n - 1) return cuda_fail("pairwise: invalid Krum parameters");
-            break;
-        case kSelectBulyanPython:
-        case kSelectBulyanNative:
-            if (f < 1 || n < 4 * f + 3 || m < 1 || m > n - f - 2) return cuda_fail("pairwise: invalid Bulyan parameters");
-            break;
-        case kSelectMda: {
-            if (f < 1 || n < 2 * f + 1) return cuda_fail("pairwise: invalid MDA parameters");
-            bool over = false;
-            unsigned long long const total = binomial(static_cast<unsigned>(n), static_cast<unsigned>(n - f), &over);
-            if (over || total > (1ull << 26)) return cuda_fail("pairwise: too many MDA subsets for the in-kernel search (limit 2^26)");
-            break;
-        }
-        case kSelectClosest:
-            if (n < 2 || m < 1 || m > n - 1) return cuda_fail("pairwise: invalid closest-to-last parameters");
-            break;
-        default: return cuda_fail("pairwise: unknown selection mode");
+    if (char const* bad = selection_error(mode, n, f, m, neighbors)) {
+        static thread_local char msg[160];
+        std::snprintf(msg, sizeof(msg), "pairwise: %s", bad);
+        return cuda_fail(msg);
     }
 
     PairwiseArgs a{};
@@ -364,10 +349,11 @@ extern "C" GB_API int gb_select_only(float* dist, int n, int mode, int f, int m,
     using namespace gb;
     if (n < 1 || n > kMaxRows) return cuda_fail("select_only: need 1 <= n <= 64 rows");
     if (dist == nullptr || W == nullptr || info == nullptr) return cuda_fail("select_only: missing buffers");
-    if (mode == kSelectMda) {
-        bool over = false;
-        unsigned long long const total = binomial(static_cast<unsigned>(n), static_cast<unsigned>(n - f), &over);
-        if (f < 1 || n < 2 * f + 1 || over || total > (1ull << 26)) return cuda_fail("select_only: invalid or too large MDA problem");
+    if (mode == kSelectNone) return cuda_fail("select_only: no selection mode given");
+    if (char const* bad = selection_error(mode, n, f, m, neighbors)) {
+        static thread_local char msg[160];
+        std::snprintf(msg, sizeof(msg), "select_only: %s", bad);
+        return cuda_fail(msg);
     }
     SelectOnlyArgs a{};
     a.n = n; a.dist = dist; a.W = W; a.info = info;
@@ -434,22 +420,10 @@ extern "C" GB_API int gb_pairwise_select_noalloc(float const* const* rows, int n
     if (d < 1) return cuda_fail("no-alloc pairwise: empty rows");
     if (dist == nullptr) return cuda_fail("no-alloc pairwise: missing distance output buffer");
     if (mode != kSelectNone && (W == nullptr || info == nullptr)) return cuda_fail("no-alloc pairwise: selection needs W and info buffers");
-    switch (mode) {
-        case kSelectNone: break;
-        case kSelectKrum:
-            if (f < 1 || n < 2 * f + 3 || m < 1 || m > n - f - 2 || neighbors < 1 || neighbors > n - 1) return cuda_fail("no-alloc pairwise: invalid Krum parameters");
-            break;
-        case kSelectBulyanPython:
-        case kSelectBulyanNative:
-            if (f < 1 || n < 4 * f + 3 || m < 1 || m > n - f - 2) return cuda_fail("no-alloc pairwise: invalid Bulyan parameters");
-            break;
-        case kSelectMda:
-            if (f < 1 || n < 2 * f + 1) return cuda_fail("no-alloc pairwise: invalid MDA parameters");
-            break;  // C(16, k) <= 12870 subsets: always within the in-kernel search limit
-        case kSelectClosest:
-            if (n < 2 || m < 1 || m > n - 1) return cuda_fail("no-alloc pairwise: invalid closest-to-last parameters");
-            break;
-        default: return cuda_fail("no-alloc pairwise: unknown selection mode");
+    if (char const* bad = selection_error(mode, n, f, m, neighbors)) {
+        static thread_local char msg[160];
+        std::snprintf(msg, sizeof(msg), "no-alloc pairwise: %s", bad);
+        return cuda_fail(msg);
     }
     void* scratch = nullptr;
     if (static_scratch_for_current_device(&scratch)) return 1;

@@ -11,6 +11,28 @@
 
 namespace gb {
 
+// Host-side validation shared by every entry point that runs the selection (gb_pairwise_select, gb_pairwise_select_noalloc,
+// gb_select_only, gb_gram_select_tc): out-of-range (n, f, m, neighbors) would index the score order and the weight matrix
+// out of bounds on the device. Returns nullptr when the parameters are valid, else what is wrong.
+inline char const* selection_error(int mode, int n, int f, int m, int neighbors) {
+    switch (mode) {
+        case kSelectNone: return nullptr;
+        case kSelectKrum:
+            return (f < 1 || n < 2 * f + 3 || m < 1 || m > n - f - 2 || neighbors < 1 || neighbors > n - 1) ? "invalid Krum parameters" : nullptr;
+        case kSelectBulyanPython:
+        case kSelectBulyanNative:
+            return (f < 1 || n < 4 * f + 3 || m < 1 || m > n - f - 2) ? "invalid Bulyan parameters" : nullptr;
+        case kSelectMda: {
+            if (f < 1 || n < 2 * f + 1) return "invalid MDA parameters";
+            bool over = false;
+            unsigned long long const total = binomial(static_cast<unsigned>(n), static_cast<unsigned>(n - f), &over);
+            return (over || total > (1ull << 26)) ? "too many MDA subsets for the in-kernel search (limit 2^26)" : nullptr;
+        }
+        case kSelectClosest: return (n < 2 || m < 1 || m > n - 1) ? "invalid closest-to-last parameters" : nullptr;
+        default: return "unknown selection mode";
+    }
+}
+
 // ------------------------------------------------------------------------ selection ---
 
 struct SelectScratch {      // lives in dynamic shared memory of the last CTA (ring is idle by then)

@@ -71,18 +71,28 @@ class PimaDiabetesDataset(torch.utils.data.Dataset):
 
     def __init__(self, train, train_size=None):
         rows = self._load()
+        self.source = self._source          # path of the CSV that was read, or None for the synthetic stand-in
         split = self.TRAIN_SPLIT if train_size is None or train_size >= self.TRAIN_SPLIT else train_size
         rows = rows[:split] if train else rows[-self.TEST_SPLIT:]
         feats, labels = rows[:, :-1], rows[:, -1:]
         feats = (feats - feats.mean(dim=0)) / feats.std(dim=0)
         self.data, self.targets = feats.float(), labels.float()
 
-    @staticmethod
-    def _load():
+    _source = None
+    _warned = False
+
+    @classmethod
+    def _load(cls):
         for candidate in _PIMA_CANDIDATES:
             if candidate.is_file():
                 import pandas as pd
+                cls._source = str(candidate)
                 return torch.tensor(pd.read_csv(candidate).values, dtype=torch.float64)
+        cls._source = None
+        if not cls._warned:      # never silently: the numbers of a run on the stand-in are not Pima numbers
+            cls._warned = True
+            logger.warning("pima_diabetes.csv not found (looked in %s): using a SYNTHETIC stand-in of the same shape",
+                           ", ".join(str(c) for c in _PIMA_CANDIDATES[:3]))
         gen = torch.Generator().manual_seed(768)
         feats = torch.randn(768, 8, generator=gen, dtype=torch.float64) * 3 + 5
         weights = torch.tensor([0.4, 1.1, -0.2, 0.1, 0.3, 0.9, 0.5, 0.6], dtype=torch.float64)

@@ -115,7 +115,12 @@ def coordwise(gradients, rule, f=0, beta=0, upper=False, p=0.9, seed=0, W=None, 
     return out
 
 
-TENSOR_CORE_MIN_ROWS = [17]  # `engine="auto"` uses the tcgen05 Gram kernel from this many rows (<= 32)
+# `engine="auto"` is the EXACT direct-difference kernel for every n: the registry rules promise the reference's selections, and
+# TF32 Gram distances (error ~1e-3·(‖x_i‖² + ‖x_j‖²) after the G_ii + G_jj − 2 G_ij cancellation) can reorder scores when honest
+# gradients sit close together relative to their norm — or when an adversary aims a row into that error band. The tcgen05
+# Gram kernel is opt-in: `engine="tc"` per call, or GARFIELD_GRAM_TC=<min rows> to route n >= that many rows (<= 32) to it.
+import os as _os
+TENSOR_CORE_MIN_ROWS = [int(_os.environ.get("GARFIELD_GRAM_TC", "0")) or 10 ** 9]
 
 
 def select(gradients, mode, f=0, m=0, neighbors=0, squared=True, engine="auto", workspace_tag=0):
@@ -123,7 +128,7 @@ def select(gradients, mode, f=0, m=0, neighbors=0, squared=True, engine="auto", 
     `dist` (n×n), `W` (n×n buffer, first θ rows valid) and `info`.
 
     engine: "simt" = exact direct-difference kernel, "tc" = tcgen05 TF32 Gram kernel (2..32
-    aligned rows), "auto" = tc for TENSOR_CORE_MIN_ROWS <= n <= 32 when the rows qualify."""
+    aligned rows), "auto" = exact unless GARFIELD_GRAM_TC opts n >= TENSOR_CORE_MIN_ROWS rows into the Gram kernel."""
     rows, n, d, device = _prep(gradients)
     lib = _lib.require()
     ws = _Workspace.get(device, n, workspace_tag)

@@ -794,6 +794,12 @@ class SSMWEngine:
         shard, its workers' BatchNorm buffers, the step counter and the RNG state."""
         self.wait_published()
         torch.cuda.synchronize(self.device)
+        # BatchNorm's per-layer `num_batches_tracked += 1` kernels are skipped on the hot path (_skip_bn_counters); the counter is
+        # a pure function of the number of training passes, so it is written here — checkpoints equal what torch would hold
+        for w in self.workers:
+            for name, buf in w.replica.module.named_buffers():
+                if name.endswith("num_batches_tracked"):
+                    buf.fill_(self.steps_done)
         payload = {"format": 1, "step": self.steps_done, "lo": self.lo, "hi": self.hi, "world": self.world,
                    "model": {k: v.detach().cpu().contiguous() for k, v in self.master.module.state_dict().items()},
                    "optimizer": self.optimizer.state_dict() if self.optimizer is not None else None,

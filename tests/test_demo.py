@@ -43,6 +43,28 @@ def test_demo_http_roundtrip():
         server.shutdown()
 
 
+def test_demo_runs_its_nodes_as_processes_over_rpc():
+    """--transport processes: n local processes named node:<rank> over torch RPC on a fresh localhost port, progress through
+    a multiprocessing queue (the reference's demo.py:264-335); /status names the transport and where the table came from."""
+    import os
+    os.environ["GARFIELD_DEMO_EPOCHS"] = "1"
+    spec = importlib.util.spec_from_file_location("learn_demo_mp", ROOT / "applications" / "LEARN" / "demo.py")
+    demo = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(demo)
+    demo.EPOCHS = 1
+    demo.TRANSPORT[0] = "processes"
+    try:
+        trainer = demo.Trainer(1, 3, 1, "median").start()
+        trainer.thread.join(timeout=400)
+        status = trainer.status()
+        assert "error" not in status, status
+        assert status["transport"] == "processes" and "dataset" in status
+        assert 0.0 <= status.get("result", -1) <= 100.0, status
+    finally:
+        demo.TRANSPORT[0] = "threads"
+        os.environ.pop("GARFIELD_DEMO_EPOCHS", None)
+
+
 def test_playground_scripts_run(tmp_path):
     """rsrcs/playgrounds counterparts: the random-attack Aggregathor variant and the centralized tutorial loop."""
     import os

@@ -660,3 +660,43 @@ def test_pull_median_operand_matches_torch():
         want = torch.stack([r[:cout * k] for r in rows]).median(0)[0]
         assert torch.equal(flat, want)
         assert torch.equal(operand[:, :k], want.view(cout, k)) and (operand[:, k:] == 0).all()
+
+
+def test_registry_rules_stay_exact_on_tightly_clustered_gradients():
+    """Honest gradients that differ by 1e-3 of their norm on top of a large common offset (late training, large batches) plus f
+    outliers: the default engine is the exact direct-difference kernel for every n, so the selected set equals the fp64
+    reference; TF32 Gram distances cannot resolve these rows, which is why that kernel is opt-in."""
+    cuda_lib()
+    from garfield_b200.ops import gar
+    torch.manual_seed(77)
+    n, f, d = 20, 3, 200_000
+    common = torch.randn(d, dtype=torch.float64) * 10
+    rows64 = [common + 1e-3 * torch.randn(d, dtype=torch.float64) * (1 + 0.05 * i) for i in range(n - f)]
+    rows64 += [common + 0.5 * torch.randn(d, dtype=torch.float64) for _ in range(f)]
+    rows = [r.float().cuda() for r in rows64]
+    ws = gar.select(rows, "krum", f=f, m=n - f - 2, neighbors=n - f - 2, squared=True)          # engine="auto"
+    torch.cuda.synchronize()
+    picked = sorted(ws["info"][1:1 + n - f - 2].tolist())
+    stack = torch.stack([r.double() for r in rows]).cpu()
+    dist = torch.cdist(stack, stack).pow(2)
+    dist.fill_diagonal_(float("inf"))
+    scores = dist.sort(1)[0][:, :n - f - 2].sum(1)
+    want = sorted(scores.argsort()[:n - f - 2].tolist())
+    assert picked == want
+    assert all(i < n - f for i in picked)                         # no outlier selected
+    exact = gar.pairwise_sqdist(rows, engine="simt").cpu().double()
+    off = ~torch.eye(n, dtype=torch.bool)
+    assert ((exact - dist)[off].abs() / dist[off]).max().item() < 1e-4
+    tc = gar.pairwise_sqdist(rows, engine="tc").cpu().double()
+    honest = off.clone(); honest[n - f:] = False; honest[:, n - f:] = False
+    assert ((tc - dist)[honest].abs() / dist[honest]).max().item() > 1e-2      # what the TF32 Gram form does to such rows
+
+
+def test_select_only_rejects_out_of_range_parameters():
+    cuda_lib()
+    from garfield_b200.ops import gar
+    ws = gar.select([torch.randn(1000, device="cuda") for _ in range(7)], "none")
+    for kwargs in (dict(mode="krum", f=1, m=9, neighbors=5), dict(mode="krum", f=1, m=3, neighbors=9), dict(mode="bulyan_native", f=2, m=1),
+                   dict(mode="closest", m=12), dict(mode="mda", f=4)):
+        with pytest.raises(RuntimeError):
+            gar.select_only(ws, 7, torch.device("cuda"), **kwargs)
