@@ -103,7 +103,7 @@ __device__ void run_selection(Args const& a, SelectScratch& S) {
     if (sel.mode == kSelectNone) return;
 
     for (int e = tid; e < n * n; e += blockDim.x) {
-        float const v = a.dist[e];
+        auto const v = a.dist[e];      // float (fp32 kernels) or double (fp64 kernels)
         double dv = sel.squared ? static_cast<double>(v) : sqrt(static_cast<double>(v));
         // native MDA counts a non-finite distance as the largest finite one instead of skipping the subset
         if (sel.mode == kSelectMda && sel.squared && !isfinite(dv) && (e / n) != (e % n)) dv = DBL_MAX;

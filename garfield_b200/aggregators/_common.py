@@ -37,8 +37,10 @@ def on_device(gradients):
     g0 = gradients[0]
     if not (isinstance(g0, torch.Tensor) and g0.is_cuda):
         return False
-    if g0.dtype not in (torch.float32,) or len(gradients) > 64:
-        return False  # fp64 inputs and more than 64 rows take the (device-resident) torch path
+    if g0.dtype not in (torch.float32, torch.float64) or len(gradients) > 64:
+        return False  # more than 64 rows (and other dtypes) take the (device-resident) torch path
+    if any(g.dtype != g0.dtype for g in gradients):
+        return False
     return device_ops() is not None
 
 

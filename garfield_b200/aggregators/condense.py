@@ -18,7 +18,7 @@ _calls = [0]
 
 def aggregate(gradients, f, p=0.9, seed=None, **kwargs):
     """Bernoulli(p) mix of the coordinate-wise median and gradients[0]."""
-    if on_device(gradients):
+    if on_device(gradients) and gradients[0].dtype == __import__("torch").float32:
         if seed is None:
             _calls[0] += 1
             seed = (torch.initial_seed() * 0x9E3779B97F4A7C15 + _calls[0]) & 0x7FFFFFFFFFFFFFFF

@@ -32,6 +32,10 @@ def _declare(h):
     h.gb_pairwise_scratch_bytes.restype = i64
     h.gb_pairwise_scratch_bytes.argtypes = [i32]
     h.gb_pairwise_select.argtypes = [pp, i32, i64, i32, i32, i32, i32, i32, vp, i64, vp, vp, vp, vp]
+    h.gb_pairwise_scratch_bytes_f64.restype = i64
+    h.gb_pairwise_scratch_bytes_f64.argtypes = [i32]
+    h.gb_pairwise_select_f64.argtypes = [pp, i32, i64, i32, i32, i32, i32, i32, vp, i64, vp, vp, vp, vp]
+    h.gb_coordwise_f64.argtypes = [pp, i32, i64, i32, i32, i32, vp, i32, vp, vp]
     h.gb_gram_scratch_bytes.restype = i64
     h.gb_gram_scratch_bytes.argtypes = [i32]
     h.gb_gram_select_tc.argtypes = [pp, i32, i64, i32, i32, i32, i32, i32, vp, i64, vp, vp, vp, vp]

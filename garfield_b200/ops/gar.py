@@ -39,18 +39,18 @@ class _Workspace:
     _cache = {}
 
     @classmethod
-    def get(cls, device, n, tag=0):
+    def get(cls, device, n, tag=0, dtype=torch.float32):
         """`tag` separates workspaces that are in flight at the same time (e.g. distances of one coordinate range
         computed on a side stream while another call runs)."""
-        key = (device.index if device.index is not None else torch.cuda.current_device(), n, tag)
+        key = (device.index if device.index is not None else torch.cuda.current_device(), n, tag, dtype)
         ws = cls._cache.get(key)
         if ws is None:
             lib = _lib.require()
             with torch.cuda.device(device):
-                nbytes = int(lib.gb_pairwise_scratch_bytes(n))
+                nbytes = int(lib.gb_pairwise_scratch_bytes(n) if dtype == torch.float32 else lib.gb_pairwise_scratch_bytes_f64(n))
             ws = dict(
                 scratch=torch.zeros(nbytes, dtype=torch.uint8, device=device),
-                dist=torch.empty(n, n, dtype=torch.float32, device=device),
+                dist=torch.empty(n, n, dtype=dtype, device=device),
                 W=torch.zeros(n, n, dtype=torch.float32, device=device),
                 info=torch.zeros(1 + n, dtype=torch.int32, device=device),
             )
@@ -65,8 +65,8 @@ def _prep(gradients):
     g0 = gradients[0]
     rows = []
     for g in gradients:
-        if g.dtype != torch.float32 or not g.is_cuda or g.dim() != 1 or g.shape != g0.shape:
-            raise ValueError("expected 1-D float32 CUDA tensors of equal length")
+        if g.dtype not in (torch.float32, torch.float64) or g.dtype != g0.dtype or not g.is_cuda or g.dim() != 1 or g.shape != g0.shape:
+            raise ValueError("expected 1-D float32 (or float64) CUDA tensors of equal length and dtype")
         rows.append(g if g.is_contiguous() else g.contiguous())
     return rows, n, g0.numel(), g0.device
 
@@ -102,6 +102,16 @@ def coordwise(gradients, rule, f=0, beta=0, upper=False, p=0.9, seed=0, W=None, 
     lib = _lib.require()
     code = RULES[rule]
     rank = f if rule == "trimmed_mean" else beta
+    if rows[0].dtype == torch.float64:      # double-precision inputs: SIMT fp64 kernel (csrc/cuda/gar_f64.cu)
+        if update is not None or rule == "condense":
+            raise ValueError("float64 rows: no fused update / condense on the device path")
+        if out is None:
+            out = torch.empty(d, dtype=torch.float64, device=device)
+        with torch.cuda.device(device):
+            _lib.check(lib.gb_coordwise_f64(_lib.row_table(rows), n, d, code, int(rank), int(bool(upper)), W.data_ptr() if W is not None else None,
+                                            int(theta), out.data_ptr(), _lib.stream_ptr(device)))
+        _lib.count()
+        return out
     if out is None and want_out:
         out = torch.empty(d, dtype=torch.float32, device=device)
     upd = update.struct() if update is not None else None
@@ -131,6 +141,15 @@ def select(gradients, mode, f=0, m=0, neighbors=0, squared=True, engine="auto", 
     aligned rows), "auto" = exact unless GARFIELD_GRAM_TC opts n >= TENSOR_CORE_MIN_ROWS rows into the Gram kernel."""
     rows, n, d, device = _prep(gradients)
     lib = _lib.require()
+    if rows[0].dtype == torch.float64:
+        ws = _Workspace.get(device, n, workspace_tag, torch.float64)
+        with torch.cuda.device(device):
+            _lib.check(lib.gb_pairwise_select_f64(
+                _lib.row_table(rows), n, d, MODES[mode], int(f), int(m), int(neighbors), int(bool(squared)),
+                ws["scratch"].data_ptr(), ws["scratch"].numel(), ws["dist"].data_ptr(), ws["W"].data_ptr(),
+                ws["info"].data_ptr(), _lib.stream_ptr(device)))
+        _lib.count()
+        return ws
     ws = _Workspace.get(device, n, workspace_tag)
     aligned = all(r.data_ptr() % 16 == 0 for r in rows)
     use_tc = engine == "tc" or (engine == "auto" and TENSOR_CORE_MIN_ROWS[0] <= n <= 32 and aligned and d >= 4096)

@@ -154,6 +154,14 @@ GB_API int gb_gram_select_tc(float const* const* rows, int n, int64_t d, int mod
 GB_API int gb_pairwise_select_noalloc(float const* const* rows, int n, int64_t d, int mode, int f, int m, int neighbors,
                                       int squared, float* dist, float* W, int* info, void* stream);
 
+/* Double-precision variants for CUDA float64 rows (SIMT; same selection code and semantics; `dist` is n*n doubles, W / info as
+ * above; coordwise rules 0-4). ref: aggregate_gpu_double dispatch, native/include/aggregator.hpp:123-133. */
+GB_API int64_t gb_pairwise_scratch_bytes_f64(int n);
+GB_API int gb_pairwise_select_f64(double const* const* rows, int n, int64_t d, int mode, int f, int m, int neighbors, int squared,
+                                  void* scratch, int64_t scratch_bytes, double* dist, float* W, int* info, void* stream);
+GB_API int gb_coordwise_f64(double const* const* rows, int n, int64_t d, int rule, int rank, int upper, float const* W, int theta,
+                            double* out, void* stream);
+
 /* C[M,N] (fp32, row stride ldc) = A[M,K] · B[N,K]^T (+ bias[N]) (ReLU) on tcgen05 tensor cores with TMA
  * tiled loads and a TMEM accumulator. dtype 0: fp32 operands read as TF32; 1: bf16 operands.
  * Operands K-major, 16-byte aligned, row strides (in elements) multiples of 16 bytes.

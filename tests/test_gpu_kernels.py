@@ -700,3 +700,25 @@ def test_select_only_rejects_out_of_range_parameters():
                    dict(mode="closest", m=12), dict(mode="mda", f=4)):
         with pytest.raises(RuntimeError):
             gar.select_only(ws, 7, torch.device("cuda"), **kwargs)
+
+
+@pytest.mark.parametrize("name,n,f", [("average", 5, 0), ("median", 7, 1), ("native-median", 6, 1), ("trimmed_mean", 9, 2), ("averaged_median", 8, 2),
+                                      ("krum", 9, 2), ("native-krum", 9, 2), ("bulyan", 11, 2), ("native-bulyan", 11, 2), ("brute", 7, 2),
+                                      ("native-brute", 7, 2), ("aksel", 7, 2)])
+def test_float64_rows_run_on_the_fp64_device_kernels(name, n, f):
+    """CUDA float64 inputs (the reference natives' gpu_double dispatch): same registry call, fp64 SIMT kernels, results equal
+    the CPU registry on the same doubles to double precision."""
+    cuda_lib()
+    from garfield_b200.ops import _lib
+    torch.manual_seed(n * 7 + f)
+    d = 10_007
+    rows = [torch.randn(d, dtype=torch.float64) for _ in range(n)]
+    if name.startswith("native-median"):
+        rows[2][5] = float("nan"); rows[3][9] = float("inf")
+    want = aggregators.gars[name](gradients=[r.clone() for r in rows], f=f)
+    before = _lib.launches[0]
+    got = aggregators.gars[name](gradients=[r.cuda() for r in rows], f=f)
+    assert _lib.launches[0] > before, "the fp64 device kernels must have run"
+    assert got.dtype == torch.float64 and got.is_cuda
+    # sums run in a different order than on the host: a few ulps of double
+    assert torch.allclose(got.cpu(), want, rtol=1e-11, atol=1e-12, equal_nan=True), (got.cpu() - want).abs().max()
