@@ -58,6 +58,7 @@ struct ConvGeom {
     int stages;               // depth of the TMA -> MMA shared-memory ring (2..8)
     int mn_lbo, mn_sbo, mn_layout, mn_kstep;   // MN-major operand descriptors (bytes; see mn_descriptor_defaults)
     long long ldc, c_group_stride;
+    const float* addend;      // optional tensor of the output's shape and pitch added in the epilogue (gradient of a skip connection)
     signed char dh[kMaxTaps], dw[kMaxTaps];
 };
 
@@ -96,7 +97,8 @@ __device__ __forceinline__ bool tap_in_range(ConvGeom const& g, int t, int h0, i
 // through shared memory → 128-byte row segments.
 template <int BN>
 __device__ __forceinline__ void store_quadrant(uint32_t acc, float* stage, float* __restrict__ C, long long ldc, int row0, int rows_end, int col0,
-                                               int cols_end, const float* __restrict__ bias, int relu, bool zero, int lane) {
+                                               int cols_end, const float* __restrict__ bias, int relu, bool zero, int lane,
+                                               const float* __restrict__ addend = nullptr) {
     bool const vec_ok = (reinterpret_cast<uintptr_t>(C) & 15u) == 0 && (ldc & 3) == 0 && (col0 & 3) == 0;
 #pragma unroll 1
     for (int c0 = 0; c0 < BN; c0 += 32) {
@@ -128,12 +130,18 @@ __device__ __forceinline__ void store_quadrant(uint32_t acc, float* stage, float
             if (grow < rows_end && gcol < cols_end) {
                 float* out = C + static_cast<long long>(grow) * ldc + gcol;
                 if (vec_ok && gcol + 3 < cols_end) {
-                    *reinterpret_cast<float4*>(out) = o;
+                    float4 v = o;
+                    if (addend != nullptr) {
+                        float4 const t = *reinterpret_cast<float4 const*>(addend + static_cast<long long>(grow) * ldc + gcol);
+                        v.x += t.x; v.y += t.y; v.z += t.z; v.w += t.w;
+                    }
+                    *reinterpret_cast<float4*>(out) = v;
                 } else {
-                    out[0] = o.x;
-                    if (gcol + 1 < cols_end) out[1] = o.y;
-                    if (gcol + 2 < cols_end) out[2] = o.z;
-                    if (gcol + 3 < cols_end) out[3] = o.w;
+                    const float* t = addend != nullptr ? addend + static_cast<long long>(grow) * ldc + gcol : nullptr;
+                    out[0] = o.x + (t ? t[0] : 0.f);
+                    if (gcol + 1 < cols_end) out[1] = o.y + (t ? t[1] : 0.f);
+                    if (gcol + 2 < cols_end) out[2] = o.z + (t ? t[2] : 0.f);
+                    if (gcol + 3 < cols_end) out[3] = o.w + (t ? t[3] : 0.f);
                 }
             }
         }
@@ -287,7 +295,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
             cols_end = g.n_store;
         }
         store_quadrant<BN>(acc, stage, out, g.ldc, m0 + quad * 32, m0 + rows_valid, col0, cols_end, MODE == 0 ? bias : nullptr, g.relu, nothing,
-                           lane);
+                           lane, MODE == 1 ? g.addend : nullptr);
     }
     ptx::tc_fence_before();
     __syncthreads();
@@ -491,8 +499,9 @@ extern "C" GB_API int gb_conv_fprop_tc(float const* x, float const* w, float con
 }
 
 // dx[n, h, w, :cin] (pixel pitch dx_pitch) = Σ_taps dy[n, h + pad − r, w + pad − s, :cout] · w[cout, r, s, cin]   (stride-1 convolution)
+// (+ addend[n, h, w, :cin], same pitch: the gradient arriving over a skip connection, summed in the epilogue)
 extern "C" GB_API int gb_conv_dgrad_tc(float const* dy, float const* w, float* dx, int n, int h, int wd, int cin, int dx_pitch, int cout,
-                                       int dy_pitch, int kh, int kw, int pad_h, int pad_w, void* stream) {
+                                       int dy_pitch, int kh, int kw, int pad_h, int pad_w, float const* addend, void* stream) {
     if (n < 1 || h < 1 || wd < 1 || cin < 1 || cout < 1 || kh < 1 || kw < 1 || pad_h < 0 || pad_w < 0) return cuda_fail("conv_dgrad_tc: bad geometry");
     if ((kh * kw * cin) % 4 || dy_pitch % 4 || dy_pitch < cout || dx_pitch < cin || !aligned16(dy) || !aligned16(w))
         return cuda_fail("conv_dgrad_tc: kh*kw*cin and the gradient pixel pitch must be multiples of 4 floats, pointers 16-byte aligned");
@@ -502,7 +511,7 @@ extern "C" GB_API int gb_conv_dgrad_tc(float const* dy, float const* w, float* d
     if (fill_taps(g, kh, kw, pad_h, pad_w, true)) return cuda_fail("conv_dgrad_tc: more than 32 filter taps");
     if (pick_pixel_tile(g, n, h, wd)) return cuda_fail("conv_dgrad_tc: input width must be 1..128");
     g.k_extent = cout; g.kchunks = (cout + 31) / 32; g.n_total = cin; g.m_total = n * h * wd;
-    g.sh = 1; g.sw = 1; g.hin = ho; g.win = wo; g.relu = 0; g.ldc = dx_pitch;
+    g.sh = 1; g.sw = 1; g.hin = ho; g.win = wo; g.relu = 0; g.ldc = dx_pitch; g.addend = addend;
     int const tiles_m = g.tiles_h == 1 ? (n + g.bn - 1) / g.bn : n * g.tiles_h;
     int const bn_tile = (cin > 64 && static_cast<long long>(tiles_m) * ((cin + 127) / 128) >= device_sm_count()) ? 128 : 64;
     CUtensorMap ma, mb;

@@ -12,19 +12,36 @@ from ..ops.nn import fused_batch_norm
 
 __all__ = ["fuse_resnet_blocks"]
 
+import os
+
+# GARFIELD_FORK_SKIP=1: sum the skip-connection gradient inside conv1's data-gradient epilogue (one add kernel less per block).
+# Off by default: measured SLOWER on the flagship (2.40 vs 2.32 ms per step at 8 workers on one B200) although it removes 12
+# launches — the data-gradient kernel then waits for the skip gradient's producer as well, which shortens the overlap window of the
+# side-stream weight gradients. Numerically identical to the separate add (tests/test_grouped.py).
+FORK_SKIP = [os.environ.get("GARFIELD_FORK_SKIP", "0") != "0"]
+
+
+def _first_conv(block, x):
+    """(conv1(x), identity). Without a downsample branch the identity leaves through conv1's autograd node when the worker-fusion
+    layer offers that (`_gb_fork`): the skip gradient is then added inside conv1's data-gradient kernel, not by an add kernel."""
+    fork = getattr(block.conv1, "_gb_fork", None)
+    if block.downsample is None and fork is not None and FORK_SKIP[0]:
+        return fork(x)
+    return block.conv1(x), x
+
 
 def _bottleneck_forward(self, x):
-    out = fused_batch_norm(self.conv1(x), self.bn1, relu=True)
+    y1, identity = _first_conv(self, x)
+    out = fused_batch_norm(y1, self.bn1, relu=True)
     out = fused_batch_norm(self.conv2(out), self.bn2, relu=True)
-    identity = x
     if self.downsample is not None:
         identity = fused_batch_norm(self.downsample[0](x), self.downsample[1], relu=False)
     return fused_batch_norm(self.conv3(out), self.bn3, residual=identity, relu=True)
 
 
 def _basic_forward(self, x):
-    out = fused_batch_norm(self.conv1(x), self.bn1, relu=True)
-    identity = x
+    y1, identity = _first_conv(self, x)
+    out = fused_batch_norm(y1, self.bn1, relu=True)
     if self.downsample is not None:
         identity = fused_batch_norm(self.downsample[0](x), self.downsample[1], relu=False)
     return fused_batch_norm(self.conv2(out), self.bn2, residual=identity, relu=True)

@@ -42,7 +42,7 @@ def _declare(h):
     h.gb_select_only.argtypes = [vp, i32, i32, i32, i32, i32, i32, vp, vp, vp]
     h.gb_gemm_nt.argtypes = [vp, vp, vp, vp, i32, i32, i32, i64, i64, i64, i32, i32, vp]
     h.gb_conv_fprop_tc.argtypes = [vp, vp, vp, vp] + [i32] * 14 + [vp]
-    h.gb_conv_dgrad_tc.argtypes = [vp, vp, vp] + [i32] * 11 + [vp]
+    h.gb_conv_dgrad_tc.argtypes = [vp, vp, vp] + [i32] * 11 + [vp, vp]
     h.gb_conv_wgrad_tc.argtypes = [vp, vp, vp] + [i32] * 15 + [i64, i64, vp]
     h.gb_im2col_pad_nhwc.argtypes = [vp, vp] + [i32] * 12 + [vp]
     h.gb_pad_rows.argtypes = [vp, vp, i64, i32, i64, i32, vp]

@@ -153,8 +153,9 @@ def upsample_zero(t, stride, out_hw):
     return out
 
 
-def conv_dgrad(dy, w, in_hw, stride=1, padding=0):
-    """dx [N, H, W, Cin] of y = conv(x, w); dy [N, Ho, Wo, Cout], w [Cout, kh, kw, Cin]."""
+def conv_dgrad(dy, w, in_hw, stride=1, padding=0, addend=None):
+    """dx [N, H, W, Cin] of y = conv(x, w); dy [N, Ho, Wo, Cout], w [Cout, kh, kw, Cin]. `addend` (dx's shape, contiguous): a
+    second gradient of the same tensor (skip connection), summed in the kernel's epilogue where the path allows it."""
     lib = _lib.require()
     dy, w = _prep(dy), w if w.is_contiguous() else w.contiguous()
     n, ho, wo, cout = dy.shape
@@ -162,12 +163,20 @@ def conv_dgrad(dy, w, in_hw, stride=1, padding=0):
     (sh, sw), (ph, pw) = _pair(stride), _pair(padding)
     h, wd = in_hw
     dx = torch.empty((n, h, wd, cin), device=dy.device)
+    fused_add = addend is not None and (sh, sw) == (1, 1) and addend.is_contiguous() and tuple(addend.shape) == tuple(dx.shape)
+    result = _conv_dgrad(lib, dy, w, dx, n, ho, wo, cout, kh, kw, cin, sh, sw, ph, pw, h, wd, addend if fused_add else None)
+    if addend is not None and not fused_add:
+        result = result + addend
+    return result
+
+
+def _conv_dgrad(lib, dy, w, dx, n, ho, wo, cout, kh, kw, cin, sh, sw, ph, pw, h, wd, addend):
     with torch.cuda.device(dy.device):
         if (kh * kw * cin) % 4 == 0 and kh * kw <= 32 and wd <= 128 and w.data_ptr() % 16 == 0 and (sh == sw == 1 or cout % 4 == 0):
             if (kh, kw) == (1, 1) and (ph, pw) == (0, 0) and (sh, sw) != (1, 1):
                 # strided 1×1: the GEMM at output resolution, scattered onto the sampled pixels
                 small = torch.empty((n, ho, wo, cin), device=dy.device)
-                _lib.check(lib.gb_conv_dgrad_tc(dy.data_ptr(), w.data_ptr(), small.data_ptr(), n, ho, wo, cin, cin, cout, _pitch(dy), 1, 1, 0, 0, _st(dy)))
+                _lib.check(lib.gb_conv_dgrad_tc(dy.data_ptr(), w.data_ptr(), small.data_ptr(), n, ho, wo, cin, cin, cout, _pitch(dy), 1, 1, 0, 0, None, _st(dy)))
                 _lib.count()
                 if cin % 4 == 0:
                     return upsample_zero(small, (sh, sw), (h, wd))
@@ -178,8 +187,10 @@ def conv_dgrad(dy, w, in_hw, stride=1, padding=0):
                 # strided k×k: stride-1 data gradient of the zero-upsampled output gradient
                 full_h, full_w = h + 2 * ph - kh + 1, wd + 2 * pw - kw + 1
                 dy = upsample_zero(dy if dy.is_contiguous() else dy.contiguous(), (sh, sw), (full_h, full_w))
-            _lib.check(lib.gb_conv_dgrad_tc(dy.data_ptr(), w.data_ptr(), dx.data_ptr(), n, h, wd, cin, cin, cout, _pitch(dy), kh, kw, ph, pw, _st(dy)))
+            _lib.check(lib.gb_conv_dgrad_tc(dy.data_ptr(), w.data_ptr(), dx.data_ptr(), n, h, wd, cin, cin, cout, _pitch(dy), kh, kw, ph, pw,
+                                            addend.data_ptr() if addend is not None else None, _st(dy)))
             _lib.count()
+            addend = None
         else:
             # explicit: dcols[pix, (kh, kw, c)] = dy · W2d (a 1×1 data-gradient GEMM on zero-padded weights), then col2im
             k = kh * kw * cin
@@ -187,10 +198,10 @@ def conv_dgrad(dy, w, in_hw, stride=1, padding=0):
             w2 = _pad_weight(w.view(cout, k), kpad)
             m = n * ho * wo
             dcols = torch.empty((m, kpad), device=dy.device)
-            _lib.check(lib.gb_conv_dgrad_tc(dy.data_ptr(), w2.data_ptr(), dcols.data_ptr(), m, 1, 1, kpad, kpad, cout, _pitch(dy), 1, 1, 0, 0, _st(dy)))
+            _lib.check(lib.gb_conv_dgrad_tc(dy.data_ptr(), w2.data_ptr(), dcols.data_ptr(), m, 1, 1, kpad, kpad, cout, _pitch(dy), 1, 1, 0, 0, None, _st(dy)))
             _lib.check(lib.gb_col2im_nhwc(dcols.data_ptr(), dx.data_ptr(), n, h, wd, cin, cin, kh, kw, sh, sw, ph, pw, kpad, _st(dy)))
             _lib.count(2)
-    return dx
+    return dx if addend is None else dx + addend
 
 
 def _wgrad_implicit_ok(ho, wo):

@@ -395,11 +395,15 @@ class _TcConv(torch.autograd.Function):
     batch) and the G per-worker weight gradients (one launch, written straight into the workers' gradient rows)."""
 
     @staticmethod
-    def forward(ctx, x, w, b, owner, conv, widx, bidx):
+    def forward(ctx, x, w, b, owner, conv, widx, bidx, fork=False):
+        """`fork`: also return the input itself (the identity branch of a residual block) — its gradient then arrives here and is
+        summed inside the data-gradient kernel's epilogue instead of by a separate add kernel."""
+        skip = x.view_as(x) if fork else None
         if not x.is_contiguous(memory_format=torch.channels_last):
             x = x.contiguous(memory_format=torch.channels_last)
         ctx.save_for_backward(x, w)
         ctx.cfg = (owner, conv, widx, bidx)
+        ctx.fork = fork
         cache = {"w2": getattr(conv, "_gb_w2", None)}
         ho, wo = convops.out_size(x.shape[2], x.shape[3], conv.kernel_size, conv.stride, conv.padding)
         # the output is allocated here in its logical NCHW shape (channels-last strides) so that autograd sees a fresh tensor,
@@ -407,10 +411,10 @@ class _TcConv(torch.autograd.Function):
         y = torch.empty((x.shape[0], w.shape[0], ho, wo), device=x.device, memory_format=torch.channels_last)
         convops.conv_fprop(x.permute(0, 2, 3, 1), w.permute(0, 2, 3, 1), b, conv.stride, conv.padding, out=y.permute(0, 2, 3, 1), cache=cache)
         ctx.cols = cache.get("cols")       # explicit patch matrix (RGB stem): reused by the weight gradient
-        return y
+        return (y, skip) if fork else y
 
     @staticmethod
-    def backward(ctx, gy):
+    def backward(ctx, gy, gskip=None):
         x, w = ctx.saved_tensors
         owner, conv, widx, bidx = ctx.cfg
         G = owner.groups
@@ -433,8 +437,13 @@ class _TcConv(torch.autograd.Function):
                 owner.sink.put(bidx, convops.colsum_grouped(gyn.reshape(-1, cout), G))
         gx = None
         if ctx.needs_input_grad[0]:
-            gx = convops.conv_dgrad(gyn, wn, (x.shape[2], x.shape[3]), conv.stride, conv.padding).permute(0, 3, 1, 2)
-        return gx, None, None, None, None, None, None
+            addend = None
+            if gskip is not None:
+                if not gskip.is_contiguous(memory_format=torch.channels_last):
+                    gskip = gskip.contiguous(memory_format=torch.channels_last)
+                addend = gskip.permute(0, 2, 3, 1)
+            gx = convops.conv_dgrad(gyn, wn, (x.shape[2], x.shape[3]), conv.stride, conv.padding, addend=addend).permute(0, 3, 1, 2)
+        return gx, None, None, None, None, None, None, None
 
 
 class _TcLinear(torch.autograd.Function):
@@ -550,7 +559,9 @@ class GroupedWorkers:
         self.running_tables = {}
         for name, m in self.module.named_modules():
             if isinstance(m, torch.nn.Conv2d):
-                m.forward = types.MethodType(self._conv_forward(index[id(m.weight)], None if m.bias is None else index[id(m.bias)]), m)
+                fwd = self._conv_forward(index[id(m.weight)], None if m.bias is None else index[id(m.bias)], m)
+                m.forward = types.MethodType(fwd, m)
+                m._gb_fork = fwd.fork
             elif isinstance(m, torch.nn.Linear):
                 m.forward = types.MethodType(self._linear_forward(index[id(m.weight)], None if m.bias is None else index[id(m.bias)]), m)
             elif isinstance(m, self._BATCHNORM):
@@ -601,13 +612,20 @@ class GroupedWorkers:
         return None
 
     # -- patched layer forwards -----------------------------------------------------------------------------------
-    def _conv_forward(self, widx, bidx):
+    def _conv_forward(self, widx, bidx, conv_module=None):
         owner = self
 
         def forward(conv, x):
             if owner.own_kernels(x) and conv.groups == 1 and conv.dilation == (1, 1) and x.dim() == 4:
                 return _TcConv.apply(x, conv.weight, conv.bias, owner, conv, widx, bidx)
             return _GroupedConv.apply(x, conv.weight, conv.bias, owner, conv, widx, bidx)
+
+        def fork(x):
+            """(conv(x), x): the block's identity branch leaves through the convolution's autograd node (see _TcConv.forward)."""
+            if owner.own_kernels(x) and conv_module.groups == 1 and conv_module.dilation == (1, 1) and x.dim() == 4 and x.requires_grad:
+                return _TcConv.apply(x, conv_module.weight, conv_module.bias, owner, conv_module, widx, bidx, True)
+            return conv_module(x), x
+        forward.fork = fork
         return forward
 
     def _linear_forward(self, widx, bidx):

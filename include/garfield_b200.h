@@ -177,9 +177,10 @@ GB_API int gb_gemm_nt(void const* A, void const* B, float* C, float const* bias,
  * garfieldpp/worker.py:85-91). */
 GB_API int gb_conv_fprop_tc(float const* x, float const* w, float const* bias, float* y, int n, int h, int wd, int cin, int x_pitch, int cout,
                             int y_pitch, int kh, int kw, int stride_h, int stride_w, int pad_h, int pad_w, int relu, void* stream);
-/* dx of a stride-1 convolution (strided layers: zero-upsample dy first, gb_upsample_zero_nhwc). */
+/* dx of a stride-1 convolution (strided layers: zero-upsample dy first, gb_upsample_zero_nhwc); `addend` (optional, dx's shape
+ * and pitch) is summed in the epilogue - the gradient of a residual skip connection joins without a separate add kernel. */
 GB_API int gb_conv_dgrad_tc(float const* dy, float const* w, float* dx, int n, int h, int wd, int cin, int dx_pitch, int cout, int dy_pitch,
-                            int kh, int kw, int pad_h, int pad_w, void* stream);
+                            int kh, int kw, int pad_h, int pad_w, float const* addend, void* stream);
 /* Per-worker weight gradients: images g*b ... g*b+b-1 belong to worker g; matrix g is written at dw + g*dw_group_stride
  * ([cout][kh*kw*dw_cols], row stride dw_ld) — straight into the workers' gradient rows. */
 GB_API int gb_conv_wgrad_tc(float const* x, float const* dy, float* dw, int groups, int b, int h, int wd, int cin, int x_pitch, int cout,
