@@ -114,6 +114,11 @@ __device__ __forceinline__ void flush(float (&acc)[kG][kG], int bi, int bj, int 
         }
 }
 
+// Upper bound on the CTAs of the next gb_pairwise_select launches of this thread (0 = fill the GPU). A distance pass that runs
+// in the BACKGROUND of other work (the tail coordinates' distances during the backward pass) must not take every SM, or the
+// work it hides behind stalls.
+thread_local int g_pairwise_cta_limit = 0;
+
 // ------------------------------------------------------------------------- kernel ---
 
 __global__ void __launch_bounds__(kThreads) pairwise_kernel(const __grid_constant__ PairwiseArgs a) {
@@ -302,6 +307,7 @@ extern "C" GB_API int gb_pairwise_select(float const* const* rows, int n, int64_
     long long const tiles = (d + a.tile - 1) / a.tile;
     int const ctas_per_sm = smem <= 100 * 1024 ? 2 : 1;
     long long grid = static_cast<long long>(device_sm_count()) * ctas_per_sm;
+    if (g_pairwise_cta_limit > 0 && grid > g_pairwise_cta_limit) grid = g_pairwise_cta_limit;   // background launch: leave SMs to others
     if (grid > tiles) grid = tiles;
     if (grid < 1) grid = 1;
     int64_t const need = 256 + grid * nn * static_cast<int64_t>(sizeof(float));
@@ -315,6 +321,12 @@ extern "C" GB_API int gb_pairwise_select(float const* const* rows, int n, int64_
     return cuda_check(cudaGetLastError(), "pairwise launch");
 }
 
+
+extern "C" GB_API int gb_pairwise_cta_limit(int max_ctas) {
+    int const previous = gb::g_pairwise_cta_limit;
+    gb::g_pairwise_cta_limit = max_ctas < 0 ? 0 : max_ctas;
+    return previous;
+}
 
 // ------------------------------------------------------------------ selection only ---
 //

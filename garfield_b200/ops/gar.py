@@ -133,7 +133,7 @@ import os as _os
 TENSOR_CORE_MIN_ROWS = [int(_os.environ.get("GARFIELD_GRAM_TC", "0")) or 10 ** 9]
 
 
-def select(gradients, mode, f=0, m=0, neighbors=0, squared=True, engine="auto", workspace_tag=0):
+def select(gradients, mode, f=0, m=0, neighbors=0, squared=True, engine="auto", workspace_tag=0, max_ctas=0):
     """Distances + selection in one launch. Returns the device workspace dict with
     `dist` (n×n), `W` (n×n buffer, first θ rows valid) and `info`.
 
@@ -162,10 +162,15 @@ def select(gradients, mode, f=0, m=0, neighbors=0, squared=True, engine="auto", 
         _lib.count()
         return ws
     with torch.cuda.device(device):
-        _lib.check(lib.gb_pairwise_select(
-            _lib.row_table(rows), n, d, MODES[mode], int(f), int(m), int(neighbors), int(bool(squared)),
-            ws["scratch"].data_ptr(), ws["scratch"].numel(), ws["dist"].data_ptr(), ws["W"].data_ptr(),
-            ws["info"].data_ptr(), _lib.stream_ptr(device)))
+        previous = lib.gb_pairwise_cta_limit(int(max_ctas)) if max_ctas else None      # background launch: a bounded share of the SMs
+        try:
+            _lib.check(lib.gb_pairwise_select(
+                _lib.row_table(rows), n, d, MODES[mode], int(f), int(m), int(neighbors), int(bool(squared)),
+                ws["scratch"].data_ptr(), ws["scratch"].numel(), ws["dist"].data_ptr(), ws["W"].data_ptr(),
+                ws["info"].data_ptr(), _lib.stream_ptr(device)))
+        finally:
+            if previous is not None:
+                lib.gb_pairwise_cta_limit(previous)
     _lib.count()
     return ws
 

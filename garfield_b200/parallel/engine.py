@@ -252,7 +252,7 @@ class SSMWEngine:
         self._tail_at = None
         # opt-in: measured +0.6 % on the flagship (75.3 vs 74.8 k images/s) — the persistent pairwise kernel takes every SM
         # while it runs, so the backward pass it overlaps with stalls; it needs an SM-limited launch to pay off
-        want_overlap = bool(overlap_distances)
+        want_overlap = bool(overlap_distances) or (overlap_distances is None and os.environ.get("GARFIELD_OVERLAP_DISTANCES", "0") != "0")
         if (want_overlap and self.fused is not None and self.world == 1 and len(self._chains) == 1 and not self.byzantine
                 and gar in gar_ops.distance_rules()):
             self._setup_distance_overlap()
@@ -324,6 +324,8 @@ class SSMWEngine:
         if chosen is None:
             return
         self._early_stream = torch.cuda.Stream(device=self.device)
+        import os
+        self._early_ctas = int(os.environ.get("GARFIELD_EARLY_DISTANCE_CTAS", "37"))
         start = self.fused.add_milestone(chosen, self._early_distances)
         self._tail_at = (start + 63) // 64 * 64                     # 256-byte aligned split of every row
         self._early_ws = None
@@ -335,7 +337,8 @@ class SSMWEngine:
         self._early_stream.wait_stream(main)
         self.fused.join_side_streams(self._early_stream)
         with torch.cuda.stream(self._early_stream):
-            self._early_ws = gar_ops.select([w.row[self._tail_at:] for w in self.workers], "none", workspace_tag=1)
+            # a quarter of the SMs: the backward pass this hides behind keeps the rest
+            self._early_ws = gar_ops.select([w.row[self._tail_at:] for w in self.workers], "none", workspace_tag=1, max_ctas=self._early_ctas)
 
     def _bounds(self, rank):
         lo = min(self.d, rank * self.per)
