@@ -56,6 +56,7 @@ struct ConvGeom {
     int n_store;              // wgrad: columns stored per tap (<= n_total; a zero-padded reduction matrix has fewer real ones)
     int relu;
     int stages;               // depth of the TMA -> MMA shared-memory ring (2..8)
+    int split;                // split-K: CTAs of a cluster (along grid.z) that share one output tile (1 = none; fprop / dgrad only)
     int mn_lbo, mn_sbo, mn_layout, mn_kstep;   // MN-major operand descriptors (bytes; see mn_descriptor_defaults)
     long long ldc, c_group_stride;
     const float* addend;      // optional tensor of the output's shape and pitch added in the epilogue (gradient of a skip connection)
@@ -84,6 +85,18 @@ __device__ __forceinline__ void tma_load_5d(void* dst, const void* map, int c0, 
             ptx::smem_u32(dst)),
         "l"(map), "r"(c0), "r"(c1), "r"(c2), "r"(c3), "r"(c4), "r"(ptx::smem_u32(bar))
         : "memory");
+}
+
+// ---- thread-block cluster helpers (split-K reduction through distributed shared memory) ----
+__device__ __forceinline__ void cluster_sync_all() {
+    asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+__device__ __forceinline__ float4 ld_dsmem_f4(const float* local_ptr, uint32_t cta_rank) {
+    uint32_t remote;
+    asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(remote) : "r"(ptx::smem_u32(local_ptr)), "r"(cta_rank));
+    float4 v;
+    asm volatile("ld.shared::cluster.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(remote) : "memory");
+    return v;
 }
 
 // Does filter tap t touch any in-bounds pixel for rows h0 … h0+rows-1 of the pixel grid? (interval test: conservative)
@@ -150,7 +163,9 @@ __device__ __forceinline__ void store_quadrant(uint32_t acc, float* stage, float
 }
 
 // MODE 0: fprop (B = weights, K-major)   MODE 1: dgrad (B = weights, MN-major)   MODE 2: wgrad (A = dY, B = X, both MN-major)
-template <int BN, int MODE>
+// SPLIT: the K loop of one output tile is shared by the g.split CTAs of a cluster (grid.z); their TMEM partials meet in shared
+// memory and every CTA reduces one row slab over DSMEM in CTA order (deterministic) before storing it.
+template <int BN, int MODE, bool SPLIT = false>
 __global__ void __launch_bounds__(kConvThreads)
 conv_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b, const __grid_constant__ ConvGeom g,
                float* __restrict__ C, const float* __restrict__ bias) {
@@ -215,6 +230,11 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
     cudaGridDependencySynchronize();
     cudaTriggerProgrammaticLaunchCompletion();
     uint32_t const a_bytes = MODE < 2 ? static_cast<uint32_t>(g.bn * g.bh * g.bw) * 128u : kATile;
+    // this CTA's share [step_lo, step_hi) of the flattened (valid tap, K chunk) sequence
+    int const steps_total = MODE < 2 ? __popc(tap_mask) * g.kchunks : (tap_mask ? g.kchunks : 0);
+    int const zr = SPLIT ? static_cast<int>(blockIdx.z) : 0;
+    int const step_lo = SPLIT ? static_cast<int>(static_cast<long long>(steps_total) * zr / g.split) : 0;
+    int const step_hi = SPLIT ? static_cast<int>(static_cast<long long>(steps_total) * (zr + 1) / g.split) : steps_total;
 
     if (warp == 0) {
         if (ptx::elect_one()) {
@@ -222,9 +242,12 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
             uint32_t phase = 0;
             auto advance = [&] { if (++s == STAGES) { s = 0; phase ^= 1u; } };
             if (MODE < 2) {
+                int step = 0;
                 for (int t = 0; t < g.taps; ++t) {
                     if (!((tap_mask >> t) & 1u)) continue;
-                    for (int kc = 0; kc < g.kchunks; ++kc, advance()) {
+                    if (SPLIT && (step + g.kchunks <= step_lo || step >= step_hi)) { step += g.kchunks; continue; }
+                    for (int kc = 0; kc < g.kchunks; ++kc, ++step) {
+                        if (SPLIT && (step < step_lo || step >= step_hi)) continue;
                         ptx::mbar_wait(&sh.empty[s], phase ^ 1u);
                         ptx::mbar_arrive_expect_tx(&sh.full[s], a_bytes + kBBytes);
                         unsigned char* dst = smem_raw + static_cast<size_t>(s) * kStageBytes;
@@ -236,6 +259,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
                             for (int j = 0; j < BN / 32; ++j)
                                 ptx::tma_load_2d(dst + kATile + j * 4096, &map_b, t * g.n_total + tile_n * BN + 32 * j, kc * 32, &sh.full[s]);
                         }
+                        advance();
                     }
                 }
             } else if (tap_mask) {
@@ -259,7 +283,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
     } else if (warp == 1) {
         if (ptx::elect_one()) {
             uint32_t const idesc = ptx::make_idesc(2u, 2u, 128, BN, MODE == 2 ? 1u : 0u, MODE >= 1 ? 1u : 0u);
-            int const steps = MODE < 2 ? __popc(tap_mask) * g.kchunks : (tap_mask ? g.kchunks : 0);
+            int const steps = step_hi - step_lo;
             int s = 0;
             uint32_t phase = 0;
             for (int it = 0; it < steps; ++it) {
@@ -283,10 +307,27 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
         }
     } else {
         int const quad = warp & 3;
-        bool const nothing = MODE < 2 ? tap_mask == 0u : (tap_mask == 0u || g.kchunks == 0);
+        bool const nothing = step_hi <= step_lo;         // no MMA was issued: the accumulator is undefined, the tile is zero
         ptx::mbar_wait(&sh.acc_full, 0u);
         ptx::tc_fence_after();
         uint32_t const acc = tmem + (static_cast<uint32_t>(quad * 32) << 16);
+        if constexpr (SPLIT) {
+            // partial tile -> shared memory [128][BN + 4]; the reduction follows the cluster barrier below
+            float* const red = reinterpret_cast<float*>(smem_raw);
+#pragma unroll 1
+            for (int c0 = 0; c0 < BN; c0 += 32) {
+                uint32_t v[32];
+                ptx::tmem_ld_32x32b_x16(acc + static_cast<uint32_t>(c0), reinterpret_cast<uint32_t(&)[16]>(v[0]));
+                ptx::tmem_ld_32x32b_x16(acc + static_cast<uint32_t>(c0 + 16), reinterpret_cast<uint32_t(&)[16]>(v[16]));
+                ptx::tmem_ld_wait();
+                float* row = red + (quad * 32 + lane) * (BN + 4) + c0;
+#pragma unroll
+                for (int q = 0; q < 8; ++q)
+                    *reinterpret_cast<float4*>(row + 4 * q) = nothing ? make_float4(0.f, 0.f, 0.f, 0.f)
+                                                                      : make_float4(__uint_as_float(v[4 * q]), __uint_as_float(v[4 * q + 1]),
+                                                                                    __uint_as_float(v[4 * q + 2]), __uint_as_float(v[4 * q + 3]));
+            }
+        } else {
         float* const stage = reinterpret_cast<float*>(smem_raw) + quad * 32 * kStagePitch;   // the pipeline's smem is idle by now
         float* out = C;
         int col0 = tile_n * BN, cols_end = g.n_total;
@@ -296,6 +337,43 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
         }
         store_quadrant<BN>(acc, stage, out, g.ldc, m0 + quad * 32, m0 + rows_valid, col0, cols_end, MODE == 0 ? bias : nullptr, g.relu, nothing,
                            lane, MODE == 1 ? g.addend : nullptr);
+        }
+    }
+    if constexpr (SPLIT) {
+        __syncthreads();
+        cluster_sync_all();                               // every CTA's partial tile is in its shared memory
+        if (warp >= 2) {
+            float const* const red = reinterpret_cast<float const*>(smem_raw);
+            int const rows_per = 128 / g.split;
+            int const et = threadIdx.x - 64;                  // 0..127
+            int const col0 = tile_n * BN, cols_end = g.n_total;
+            bool const vec_ok = (reinterpret_cast<uintptr_t>(C) & 15u) == 0 && (g.ldc & 3) == 0;
+            for (int e = et; e < rows_per * (BN / 4); e += 128) {
+                int const r = zr * rows_per + e / (BN / 4), c = (e % (BN / 4)) * 4;
+                float4 sum = make_float4(0.f, 0.f, 0.f, 0.f);
+                for (int src = 0; src < g.split; ++src) {     // fixed order: bitwise reproducible
+                    float4 const v = ld_dsmem_f4(red + r * (BN + 4) + c, static_cast<uint32_t>(src));
+                    sum.x += v.x; sum.y += v.y; sum.z += v.z; sum.w += v.w;
+                }
+                int const grow = m0 + r, gcol = col0 + c;
+                if (r >= rows_valid || gcol >= cols_end) continue;
+                float o[4] = {sum.x, sum.y, sum.z, sum.w};
+#pragma unroll
+                for (int k = 0; k < 4; ++k) {
+                    if (gcol + k >= cols_end) break;
+                    if (MODE == 0 && bias != nullptr) o[k] += bias[gcol + k];
+                    if (MODE == 1 && g.addend != nullptr) o[k] += g.addend[static_cast<long long>(grow) * g.ldc + gcol + k];
+                    if (g.relu) o[k] = fmaxf(o[k], 0.f);
+                }
+                float* out = C + static_cast<long long>(grow) * g.ldc + gcol;
+                if (vec_ok && gcol + 3 < cols_end) {
+                    *reinterpret_cast<float4*>(out) = make_float4(o[0], o[1], o[2], o[3]);
+                } else {
+                    for (int k = 0; k < 4 && gcol + k < cols_end; ++k) out[k] = o[k];
+                }
+            }
+        }
+        cluster_sync_all();                               // nobody leaves while a peer may still read its tile
     }
     ptx::tc_fence_before();
     __syncthreads();
@@ -391,38 +469,78 @@ bool pdl_enabled() {
     return on != 0;
 }
 
+// GARFIELD_SPLIT_K=0 switches the cluster split-K of small-grid, deep-K problems off.
+bool split_k_enabled() {
+    static int const on = [] { char const* v = std::getenv("GARFIELD_SPLIT_K"); return (v != nullptr && v[0] == '0') ? 0 : 1; }();
+    return on != 0;
+}
+
+int env_int(char const* name, int fallback) {
+    char const* v = std::getenv(name);
+    return v != nullptr && v[0] != 0 ? std::atoi(v) : fallback;
+}
+// Largest cluster (2, 4 or 8 CTAs per output tile) and the fewest K steps a CTA must keep for the split to pay for its cluster
+// barriers and the DSMEM reduction (tuned on B200: profiles/README.md).
+int split_k_max() { static int const v = env_int("GARFIELD_SPLIT_MAX", 4); return v; }
+int split_k_min_steps() { static int const v = env_int("GARFIELD_SPLIT_MIN_STEPS", 12); return v; }
+
 template <int BN, int MODE>
 cudaError_t launch_conv(CUtensorMap const& ma, CUtensorMap const& mb, ConvGeom& g, float* C, const float* bias, dim3 grid, cudaStream_t st) {
-    auto kern = conv_tc_kernel<BN, MODE>;
     constexpr size_t kStage = kATile + BN * 128;
     constexpr int kDeep = static_cast<int>((200u * 1024u) / kStage) > kMaxStages ? kMaxStages : static_cast<int>((200u * 1024u) / kStage);
+    constexpr bool kCanSplit = MODE < 2 && BN == 64;
+    auto kern = conv_tc_kernel<BN, MODE, false>;
+    auto kern_split = conv_tc_kernel<BN, MODE, kCanSplit>;
     static bool configured = false;      // per instantiation
     if (!configured) {
         cudaError_t err = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(kDeep * kStage + 1024));
+        if (err == cudaSuccess && kCanSplit)
+            err = cudaFuncSetAttribute(kern_split, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(kDeep * kStage + 1024));
         if (err != cudaSuccess) return err;
         configured = true;
     }
+    long long const ctas = static_cast<long long>(grid.x) * grid.y * grid.z;
+    int steps = MODE < 2 ? g.taps * g.kchunks : g.kchunks;
+    // Split-K: a small grid with a long reduction loop leaves most SMs idle while a few CTAs walk K serially. Up to 8 CTAs (one
+    // cluster) share an output tile; their partials are reduced through distributed shared memory in CTA order.
+    int split = 1;
+    if (kCanSplit && split_k_enabled())
+        for (int s2 = split_k_max(); s2 >= 2; s2 >>= 1)
+            if (ctas * s2 <= device_sm_count() && steps / s2 >= split_k_min_steps()) { split = s2; break; }
+    g.split = split;
+    if (split > 1) {
+        grid.z = static_cast<unsigned>(split);
+        steps = (steps + split - 1) / split;
+    }
     // Latency-bound shapes (at most one CTA per SM, long reduction loops) get the deepest ring that fits: the bytes in flight per
     // SM set the rate. Larger grids keep two CTAs per SM so that one CTA's prologue / epilogue overlaps the other's main loop.
-    long long const ctas = static_cast<long long>(grid.x) * grid.y * grid.z;
-    int const steps = MODE < 2 ? g.taps * g.kchunks : g.kchunks;
-    int stages = ctas <= device_sm_count() ? kDeep : 4;
+    int stages = ctas * split <= device_sm_count() ? kDeep : 4;
     if (BN == 128 && stages == 4) stages = 3;
     if (stages > steps) stages = steps < 2 ? 2 : steps;
     g.stages = stages;
-    size_t const smem = static_cast<size_t>(stages) * kStage + 1024;
+    size_t const smem = static_cast<size_t>(stages) * kStage + 1024;      // >= the split-K reduction tile (128 x 68 floats) for stages >= 2
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = grid;
     cfg.blockDim = dim3(kConvThreads);
     cfg.dynamicSmemBytes = smem;
     cfg.stream = st;
-    cudaLaunchAttribute attr[1];
+    cudaLaunchAttribute attr[2];
+    int count = 0;
     if (pdl_enabled()) {
-        attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
-        attr[0].val.programmaticStreamSerializationAllowed = 1;
-        cfg.attrs = attr;
-        cfg.numAttrs = 1;
+        attr[count].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+        attr[count].val.programmaticStreamSerializationAllowed = 1;
+        ++count;
     }
+    if (split > 1) {
+        attr[count].id = cudaLaunchAttributeClusterDimension;
+        attr[count].val.clusterDim.x = 1;
+        attr[count].val.clusterDim.y = 1;
+        attr[count].val.clusterDim.z = static_cast<unsigned>(split);
+        ++count;
+    }
+    cfg.attrs = attr;
+    cfg.numAttrs = count;
+    if (split > 1) return cudaLaunchKernelEx(&cfg, kern_split, ma, mb, g, C, bias);
     return cudaLaunchKernelEx(&cfg, kern, ma, mb, g, C, bias);
 }
 
