@@ -58,3 +58,15 @@ def test_grouped_batchnorm_latency():
     rm, rv = torch.zeros(groups, 256, device="cuda"), torch.ones(groups, 256, device="cuda")
     ms = _median_ms(lambda: gnn.grouped_batch_norm(x, gamma, beta, rm, rv, groups, 1e-5, 0.1, None, True))
     assert ms < 0.15, "grouped BN forward took %.1f us (measured 13-17 us on the device; the bound leaves room for host launch overhead)" % (ms * 1e3)
+
+
+def test_tcgen05_convolution_latency():
+    """ResNet-50 layer shapes at the flagship batch (8 workers × 25): coarse bounds ≈3× above the measured device times
+    (profiles/r2/conv_check_b200.log: 3×3 64→64 on 8×8: 7.6 / 7.3 / 20.1 µs; these eager timings include host launch overhead)."""
+    from garfield_b200.ops import conv as C
+    x = torch.randn(200, 8, 8, 64, device="cuda")
+    w = torch.randn(64, 3, 3, 64, device="cuda") / 24
+    dy = torch.randn(200, 8, 8, 64, device="cuda")
+    assert _median_ms(lambda: C.conv_fprop(x, w, None, 1, 1)) < 0.08
+    assert _median_ms(lambda: C.conv_dgrad(dy, w, (8, 8), 1, 1)) < 0.08
+    assert _median_ms(lambda: C.conv_wgrad(x, dy, 8, 3, 1, 1)) < 0.10
