@@ -200,6 +200,74 @@ __global__ void __launch_bounds__(256) colsum_grouped_kernel(const float* __rest
     }
 }
 
+// ReLU on a flat tensor (forward) and its gradient mask from the OUTPUT (backward): y > 0 ⇔ x > 0.
+__global__ void __launch_bounds__(256) relu_fwd_kernel(const float* __restrict__ x, float* __restrict__ y, long long total) {
+    long long const n4 = total / 4;
+    for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < n4; i += static_cast<long long>(gridDim.x) * blockDim.x) {
+        float4 v = reinterpret_cast<const float4*>(x)[i];
+        v.x = fmaxf(v.x, 0.f); v.y = fmaxf(v.y, 0.f); v.z = fmaxf(v.z, 0.f); v.w = fmaxf(v.w, 0.f);
+        reinterpret_cast<float4*>(y)[i] = v;
+    }
+    for (long long i = n4 * 4 + blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < total; i += static_cast<long long>(gridDim.x) * blockDim.x)
+        y[i] = fmaxf(x[i], 0.f);
+}
+__global__ void __launch_bounds__(256) relu_bwd_kernel(const float* __restrict__ dy, const float* __restrict__ y, float* __restrict__ dx, long long total) {
+    for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < total; i += static_cast<long long>(gridDim.x) * blockDim.x)
+        dx[i] = y[i] > 0.f ? dy[i] : 0.f;
+}
+
+// Max pooling for any channel count (scalar lanes): the float4 kernels above need C % 4 == 0.
+__global__ void __launch_bounds__(256) maxpool_fwd_scalar_kernel(const float* __restrict__ x, float* __restrict__ y, unsigned char* __restrict__ arg, int H,
+                                                                  int W, int C, int K, int s, int p, int Ho, int Wo, long long total) {
+    for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < total; i += static_cast<long long>(gridDim.x) * blockDim.x) {
+        int const c = static_cast<int>(i % C);
+        long long r = i / C;
+        int const wo = static_cast<int>(r % Wo); r /= Wo;
+        int const ho = static_cast<int>(r % Ho);
+        long long const n = r / Ho;
+        float best = -FLT_MAX;
+        unsigned char at = 255;
+        for (int kh = 0; kh < K; ++kh) {
+            int const h = ho * s - p + kh;
+            if (h < 0 || h >= H) continue;
+            for (int kw = 0; kw < K; ++kw) {
+                int const w = wo * s - p + kw;
+                if (w < 0 || w >= W) continue;
+                float const v = x[((n * H + h) * W + w) * C + c];
+                if (v > best || v != v || at == 255) { best = v; at = static_cast<unsigned char>(kh * K + kw); }
+            }
+        }
+        y[i] = best;
+        arg[i] = at;
+    }
+}
+__global__ void __launch_bounds__(256) maxpool_bwd_scalar_kernel(const float* __restrict__ dy, const unsigned char* __restrict__ arg, float* __restrict__ dx,
+                                                                  int H, int W, int C, int K, int s, int p, int Ho, int Wo, long long total) {
+    for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < total; i += static_cast<long long>(gridDim.x) * blockDim.x) {
+        int const c = static_cast<int>(i % C);
+        long long r = i / C;
+        int const w = static_cast<int>(r % W); r /= W;
+        int const h = static_cast<int>(r % H);
+        long long const n = r / H;
+        float acc = 0.f;
+        for (int kh = 0; kh < K; ++kh) {
+            int const hn = h + p - kh;
+            if (hn < 0 || hn % s) continue;
+            int const ho = hn / s;
+            if (ho >= Ho) continue;
+            for (int kw = 0; kw < K; ++kw) {
+                int const wn = w + p - kw;
+                if (wn < 0 || wn % s) continue;
+                int const wo = wn / s;
+                if (wo >= Wo) continue;
+                long long const o = ((n * Ho + ho) * Wo + wo) * C + c;
+                if (arg[o] == static_cast<unsigned char>(kh * K + kw)) acc += dy[o];
+            }
+        }
+        dx[i] = acc;
+    }
+}
+
 __global__ void __launch_bounds__(256) avgpool_fwd_kernel(const float* __restrict__ x, float* __restrict__ y, int hw, int C, long long total) {
     for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < total; i += static_cast<long long>(gridDim.x) * blockDim.x) {
         int const c = static_cast<int>(i % C);
@@ -263,8 +331,13 @@ extern "C" GB_API int gb_upsample_zero_nhwc(float const* in, float* out, int N, 
 
 extern "C" GB_API int gb_maxpool_nhwc_forward(float const* x, float* y, unsigned char* arg, int N, int H, int W, int C, int k, int stride, int pad,
                                               void* stream) {
-    if (N < 1 || H < 1 || W < 1 || C < 4 || C % 4 || k < 1 || k > 15 || stride < 1 || pad < 0 || 2 * pad > k) return cuda_fail("maxpool_nhwc: bad geometry");
+    if (N < 1 || H < 1 || W < 1 || C < 1 || k < 1 || k > 15 || stride < 1 || pad < 0 || 2 * pad > k) return cuda_fail("maxpool_nhwc: bad geometry");
     int const Ho = (H + 2 * pad - k) / stride + 1, Wo = (W + 2 * pad - k) / stride + 1;
+    if (C % 4) {
+        long long const all = static_cast<long long>(N) * Ho * Wo * C;
+        maxpool_fwd_scalar_kernel<<<grid_for(all), 256, 0, static_cast<cudaStream_t>(stream)>>>(x, y, arg, H, W, C, k, stride, pad, Ho, Wo, all);
+        return cuda_check(cudaGetLastError(), "maxpool_nhwc_forward");
+    }
     long long const total = static_cast<long long>(N) * Ho * Wo * (C / 4);
     maxpool_fwd_kernel<<<grid_for(total), 256, 0, static_cast<cudaStream_t>(stream)>>>(reinterpret_cast<const float4*>(x), reinterpret_cast<float4*>(y),
                                                                                        reinterpret_cast<uchar4*>(arg), H, W, C / 4, k, stride, pad, Ho, Wo,
@@ -274,8 +347,13 @@ extern "C" GB_API int gb_maxpool_nhwc_forward(float const* x, float* y, unsigned
 
 extern "C" GB_API int gb_maxpool_nhwc_backward(float const* dy, unsigned char const* arg, float* dx, int N, int H, int W, int C, int k, int stride,
                                                int pad, void* stream) {
-    if (N < 1 || H < 1 || W < 1 || C < 4 || C % 4 || k < 1 || k > 15 || stride < 1 || pad < 0) return cuda_fail("maxpool_nhwc: bad geometry");
+    if (N < 1 || H < 1 || W < 1 || C < 1 || k < 1 || k > 15 || stride < 1 || pad < 0) return cuda_fail("maxpool_nhwc: bad geometry");
     int const Ho = (H + 2 * pad - k) / stride + 1, Wo = (W + 2 * pad - k) / stride + 1;
+    if (C % 4) {
+        long long const all = static_cast<long long>(N) * H * W * C;
+        maxpool_bwd_scalar_kernel<<<grid_for(all), 256, 0, static_cast<cudaStream_t>(stream)>>>(dy, arg, dx, H, W, C, k, stride, pad, Ho, Wo, all);
+        return cuda_check(cudaGetLastError(), "maxpool_nhwc_backward");
+    }
     long long const total = static_cast<long long>(N) * H * W * (C / 4);
     maxpool_bwd_kernel<<<grid_for(total), 256, 0, static_cast<cudaStream_t>(stream)>>>(reinterpret_cast<const float4*>(dy),
                                                                                        reinterpret_cast<const uchar4*>(arg), reinterpret_cast<float4*>(dx),
@@ -297,6 +375,18 @@ extern "C" GB_API int gb_colsum_grouped(float const* in, int64_t ld, float* out,
     dim3 const grid(static_cast<unsigned>((cols + 31) / 32), static_cast<unsigned>(groups));
     colsum_grouped_kernel<<<grid, 256, 0, static_cast<cudaStream_t>(stream)>>>(in, ld, out, rows_per_group, cols, scale);
     return cuda_check(cudaGetLastError(), "colsum_grouped");
+}
+
+extern "C" GB_API int gb_relu_forward(float const* x, float* y, int64_t total, void* stream) {
+    if (total < 1) return cuda_fail("relu: empty tensor");
+    if ((reinterpret_cast<uintptr_t>(x) | reinterpret_cast<uintptr_t>(y)) & 15u) return cuda_fail("relu: tensors must be 16-byte aligned");
+    relu_fwd_kernel<<<grid_for(total / 4 + 1), 256, 0, static_cast<cudaStream_t>(stream)>>>(x, y, total);
+    return cuda_check(cudaGetLastError(), "relu_forward");
+}
+extern "C" GB_API int gb_relu_backward(float const* dy, float const* y, float* dx, int64_t total, void* stream) {
+    if (total < 1) return cuda_fail("relu: empty tensor");
+    relu_bwd_kernel<<<grid_for(total), 256, 0, static_cast<cudaStream_t>(stream)>>>(dy, y, dx, total);
+    return cuda_check(cudaGetLastError(), "relu_backward");
 }
 
 extern "C" GB_API int gb_avgpool_nhwc_forward(float const* x, float* y, int64_t n, int hw, int C, void* stream) {

@@ -23,11 +23,13 @@ class Net(nn.Module):
         self.conv2_drop = nn.Dropout2d()
         self.fc1 = nn.Linear(320, 50)
         self.fc2 = nn.Linear(50, num_classes)
+        # parameter-free layers as modules (no state_dict keys): the device engines route modules to this library's kernels
+        self.pool, self.relu = nn.MaxPool2d(2), nn.ReLU()
 
     def forward(self, x):
-        x = F.relu(F.max_pool2d(self.conv1(x), 2))
-        x = F.relu(F.max_pool2d(self.conv2_drop(self.conv2(x)), 2))
-        x = F.relu(self.fc1(x.flatten(1)))
+        x = self.relu(self.pool(self.conv1(x)))
+        x = self.relu(self.pool(self.conv2_drop(self.conv2(x))))
+        x = self.relu(self.fc1(x.flatten(1)))
         x = F.dropout(x, training=self.training)
         return F.log_softmax(self.fc2(x), dim=1)
 
@@ -43,12 +45,13 @@ class Cifarnet(nn.Module):
         self.fc1 = nn.Linear(16 * 5 * 5, 120)
         self.fc2 = nn.Linear(120, 84)
         self.fc3 = nn.Linear(84, num_classes)
+        self.relu = nn.ReLU()          # a module, so that the device engines can route it to this library's kernel
 
     def forward(self, x):
-        x = self.pool(F.relu(self.conv1(x)))
-        x = self.pool(F.relu(self.conv2(x)))
-        x = F.relu(self.fc1(x.flatten(1)))
-        x = F.relu(self.fc2(x))
+        x = self.pool(self.relu(self.conv1(x)))
+        x = self.pool(self.relu(self.conv2(x)))
+        x = self.relu(self.fc1(x.flatten(1)))
+        x = self.relu(self.fc2(x))
         return self.fc3(x)
 
 
@@ -101,10 +104,11 @@ class LeNet(nn.Module):
         self.fc1 = nn.Linear(16 * 5 * 5, 120)
         self.fc2 = nn.Linear(120, 84)
         self.fc3 = nn.Linear(84, num_classes)
+        self.pool, self.relu = nn.MaxPool2d(2), nn.ReLU()
 
     def forward(self, x):
-        x = F.max_pool2d(F.relu(self.conv1(x)), 2)
-        x = F.max_pool2d(F.relu(self.conv2(x)), 2)
-        x = F.relu(self.fc1(x.flatten(1)))
-        x = F.relu(self.fc2(x))
+        x = self.pool(self.relu(self.conv1(x)))
+        x = self.pool(self.relu(self.conv2(x)))
+        x = self.relu(self.fc1(x.flatten(1)))
+        x = self.relu(self.fc2(x))
         return self.fc3(x)

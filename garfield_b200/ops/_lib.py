@@ -53,6 +53,8 @@ def _declare(h):
     h.gb_maxpool_nhwc_backward.argtypes = [vp, vp, vp] + [i32] * 7 + [vp]
     h.gb_softmax_ce_grouped.argtypes = [vp, i32, vp, vp, vp, i32, i32, i32, i32, vp]
     h.gb_colsum_grouped.argtypes = [vp, i64, vp, i32, i32, i32, f32, vp]
+    h.gb_relu_forward.argtypes = [vp, vp, i64, vp]
+    h.gb_relu_backward.argtypes = [vp, vp, vp, i64, vp]
     h.gb_avgpool_nhwc_forward.argtypes = [vp, vp, i64, i32, i32, vp]
     h.gb_avgpool_nhwc_backward.argtypes = [vp, vp, i64, i32, i32, vp]
     h.gb_conv2d_forward.argtypes = [vp, vp, vp, vp] + [i32] * 10 + [vp]

@@ -22,7 +22,7 @@ import torch
 
 from . import _lib
 
-__all__ = ["conv_fprop", "conv_dgrad", "conv_wgrad", "upsample_zero", "max_pool_nhwc", "max_pool_nhwc_backward", "softmax_ce_grouped",
+__all__ = ["conv_fprop", "conv_dgrad", "conv_wgrad", "upsample_zero", "relu", "relu_backward", "max_pool_nhwc", "max_pool_nhwc_backward", "softmax_ce_grouped",
            "colsum_grouped", "avg_pool_nhwc", "avg_pool_nhwc_backward", "out_size"]
 
 
@@ -244,6 +244,22 @@ def conv_wgrad(x, dy, groups, ksize, stride=1, padding=0, out=None, cols=None):
 
 
 # ----------------------------------------------------------------------------------------------------- non-GEMM layers ---
+
+def relu(x):
+    """max(x, 0) on a dense tensor of any shape (same strides in, same strides out)."""
+    y = torch.empty_like(x)
+    _lib.check(_lib.require().gb_relu_forward(x.data_ptr(), y.data_ptr(), x.numel(), _st(x)))
+    _lib.count()
+    return y
+
+
+def relu_backward(dy, y):
+    """dy where y > 0, else 0; `dy` must have y's element order."""
+    dx = torch.empty_like(y)
+    _lib.check(_lib.require().gb_relu_backward(dy.data_ptr(), y.data_ptr(), dx.data_ptr(), y.numel(), _st(y)))
+    _lib.count()
+    return dx
+
 
 def max_pool_nhwc(x, kernel, stride, padding, out=None):
     n, h, w, c = x.shape

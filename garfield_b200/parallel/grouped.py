@@ -475,6 +475,28 @@ class _TcLinear(torch.autograd.Function):
         return gx, None, None, None, None, None
 
 
+class _TcReLU(torch.autograd.Function):
+    """ReLU modules of the fused pass (networks without BatchNorm to fuse it into: CifarNet, VGG, the MLPs)."""
+
+    @staticmethod
+    def forward(ctx, x):
+        dense = x.is_contiguous() or (x.dim() == 4 and x.is_contiguous(memory_format=torch.channels_last))
+        if not dense:
+            x = x.contiguous()
+        y = convops.relu(x)
+        ctx.save_for_backward(y)
+        return y
+
+    @staticmethod
+    def backward(ctx, gy):
+        y, = ctx.saved_tensors
+        if gy.stride() != y.stride():
+            gy = gy.contiguous(memory_format=torch.channels_last) if (y.dim() == 4 and not y.is_contiguous()) else gy.contiguous()
+            if gy.stride() != y.stride():
+                return torch.where(y > 0, gy, torch.zeros_like(gy))
+        return convops.relu_backward(gy, y)
+
+
 class _TcMaxPool(torch.autograd.Function):
     @staticmethod
     def forward(ctx, x, k, s, p):
@@ -575,6 +597,8 @@ class GroupedWorkers:
             elif (isinstance(m, torch.nn.MaxPool2d) and isinstance(m.kernel_size, int) and isinstance(m.padding, int) and m.dilation == 1
                   and not m.ceil_mode and not m.return_indices and isinstance(m.stride if m.stride is not None else m.kernel_size, int)):
                 m.forward = types.MethodType(self._maxpool_forward(type(m).forward), m)
+            elif isinstance(m, torch.nn.ReLU):
+                m.forward = types.MethodType(self._relu_forward(type(m).forward), m)
             elif isinstance(m, torch.nn.AdaptiveAvgPool2d) and m.output_size in (1, (1, 1)):
                 m.forward = types.MethodType(self._avgpool_forward(type(m).forward), m)
 
@@ -644,11 +668,20 @@ class GroupedWorkers:
         return (OWN_KERNELS[0] and x.is_cuda and x.dtype == torch.float32 and getattr(self.replica, "channels_last", False)
                 and _lib.available())
 
+    def _relu_forward(self, stock):
+        owner = self
+
+        def forward(act, x):
+            if owner.own_kernels(x) and x.data_ptr() % 16 == 0 and x.requires_grad:
+                return _TcReLU.apply(x)
+            return stock(act, x)
+        return forward
+
     def _maxpool_forward(self, stock):
         owner = self
 
         def forward(pool, x):
-            if owner.own_kernels(x) and x.dim() == 4 and x.shape[1] % 4 == 0:
+            if owner.own_kernels(x) and x.dim() == 4:
                 return _TcMaxPool.apply(x, pool.kernel_size, pool.stride if pool.stride is not None else pool.kernel_size, pool.padding)
             return stock(pool, x)
         return forward

@@ -125,3 +125,56 @@ def test_avgpool_nhwc():
     assert torch.allclose(y.cpu(), x.mean((1, 2)), atol=1e-6)
     dx = C.avg_pool_nhwc_backward(y, (3, 3))
     assert torch.allclose(dx.cpu(), (y.cpu() / 9)[:, None, None, :].expand(5, 3, 3, 12), atol=1e-7)
+
+
+def test_relu_and_scalar_maxpool_kernels():
+    """ReLU forward / backward and max pooling on a channel count that is not a multiple of 4 (CifarNet: 6 channels)."""
+    from garfield_b200.ops import conv as C
+    torch.manual_seed(21)
+    x = torch.randn(5, 7, 3, 6)
+    y = C.relu(x.cuda())
+    assert torch.equal(y.cpu(), torch.relu(x))
+    dy = torch.randn_like(x)
+    assert torch.equal(C.relu_backward(dy.cuda(), y).cpu(), dy * (x > 0))
+    xp = torch.randn(4, 6, 14, 14, requires_grad=True)
+    yr = F.max_pool2d(xp, 2, 2)
+    g = torch.randn_like(yr)
+    gx, = torch.autograd.grad(yr, xp, g)
+    yk, arg = C.max_pool_nhwc(xp.detach().permute(0, 2, 3, 1).contiguous().cuda(), 2, 2, 0)
+    assert torch.equal(yk.cpu(), yr.detach().permute(0, 2, 3, 1))
+    dx = C.max_pool_nhwc_backward(g.permute(0, 2, 3, 1).contiguous().cuda(), arg, (4, 14, 14, 6), 2, 2, 0)
+    assert torch.allclose(dx.cpu(), gx.permute(0, 2, 3, 1), atol=1e-6)
+
+
+def test_cifarnet_pass_runs_on_own_kernels_only():
+    """Config 2's network through the fused pass: every convolution, Linear layer, ReLU, pooling and the loss is one of this
+    library's kernels (counted launches), and the gradients match separate fp32 replicas within TF32 tolerance."""
+    import copy
+    from garfield_b200.models.small import Cifarnet
+    from garfield_b200.ops import _lib
+    from garfield_b200.parallel.arena import FlatModel
+    from garfield_b200.parallel.grouped import GroupedWorkers
+    torch.manual_seed(8)
+    dev = torch.device("cuda")
+    module = Cifarnet().to(dev)
+    G, B = 3, 8
+    xs = [torch.randn(B, 3, 32, 32, device=dev) for _ in range(G)]
+    ys = [torch.randint(0, 10, (B,), device=dev) for _ in range(G)]
+    loss_fn = torch.nn.CrossEntropyLoss()
+    want = []
+    for x, y in zip(xs, ys):
+        m = copy.deepcopy(module)
+        loss_fn(m(x), y).backward()
+        want.append(torch.cat([p.grad.reshape(-1) for p in m.parameters()]))
+    flat = FlatModel(copy.deepcopy(module), dev, channels_last=True)
+    rows = torch.zeros(G, flat.numel, device=dev)
+    group = GroupedWorkers(flat, [rows[g] for g in range(G)], loss_fn, side_streams=2)
+    losses = torch.zeros(G, device=dev)
+    data = torch.cat(xs).contiguous(memory_format=torch.channels_last)
+    before = _lib.launches[0]
+    group.forward_backward(data, torch.cat(ys), losses)
+    torch.cuda.synchronize()
+    assert _lib.launches[0] - before >= 2 * 3 + 5 * 3 + 4 + 2 + 2      # convs, linears (fwd/dgrad/wgrad), ReLUs, pools, loss
+    for g in range(G):
+        got = torch.cat([flat._view(rows[g], off, n, shape).reshape(-1) for off, n, shape in flat.slices])
+        assert (got - want[g]).norm() <= 3e-2 * want[g].norm(), float((got - want[g]).norm() / want[g].norm())
