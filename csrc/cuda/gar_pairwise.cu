@@ -19,6 +19,7 @@
 
 #include <cfloat>
 #include <cstdio>
+#include <cstdlib>
 #include <cmath>
 #include <mutex>
 
@@ -31,7 +32,9 @@
 namespace gb {
 namespace {
 
-constexpr int kG = 4;  // rows per block
+// Rows per register block: warps own KG×KG row-block pairs. Per lane and 128 coordinates a block pair costs 2·KG LDS.128 and
+// 2·KG² FADD/FFMA pairs: at KG = 4 shared-memory reads and FP32 issue are balanced (both ≈50 % of the SM), at KG = 8 the
+// shared-memory traffic per FMA halves and the kernel is FP32-bound — used from 13 rows on (fewer rows leave most of an 8×8 block empty).
 
 __device__ __forceinline__ void block_pair_of(int item, int B, int& bi, int& bj) {
     // enumerate (bi <= bj) row-block pairs in row-major order
@@ -54,7 +57,7 @@ __device__ __forceinline__ float sq4_acc(float acc, float4 a, float4 b) {
 // Accumulate the 128-coordinate chunks first, first+stride, ... (lane = 4 coordinates) of the
 // row-block pair whose rows start at `pa` / `pb` in shared memory (row pitch `tile` floats).
 // FULL: all 4 rows of both blocks exist (no predicates). DIAG: bi == bj (upper triangle only).
-template <bool FULL, bool DIAG>
+template <int kG, bool FULL, bool DIAG>
 __device__ __forceinline__ void accumulate_block(float (&acc)[kG][kG], float const* pa, float const* pb, int tile, int rows_a, int rows_b,
                                                  int first, int stride, int chunks) {
     for (int ch = first; ch < chunks; ch += stride) {
@@ -79,6 +82,7 @@ __device__ __forceinline__ void accumulate_block(float (&acc)[kG][kG], float con
 }
 
 // Dispatch on (all rows present, diagonal block). `src` = stage base with the lane offset added.
+template <int kG>
 __device__ __forceinline__ void accumulate_pair(float (&acc)[kG][kG], float const* src, int tile, int n, int bi, int bj, int first,
                                                 int stride, int chunks) {
     float const* pa = src + bi * kG * tile;
@@ -86,11 +90,11 @@ __device__ __forceinline__ void accumulate_pair(float (&acc)[kG][kG], float cons
     int const rows_a = min(kG, n - bi * kG), rows_b = min(kG, n - bj * kG);
     bool const full = rows_a == kG && rows_b == kG;
     if (bi == bj) {
-        if (full) accumulate_block<true, true>(acc, pa, pb, tile, rows_a, rows_b, first, stride, chunks);
-        else accumulate_block<false, true>(acc, pa, pb, tile, rows_a, rows_b, first, stride, chunks);
+        if (full) accumulate_block<kG, true, true>(acc, pa, pb, tile, rows_a, rows_b, first, stride, chunks);
+        else accumulate_block<kG, false, true>(acc, pa, pb, tile, rows_a, rows_b, first, stride, chunks);
     } else {
-        if (full) accumulate_block<true, false>(acc, pa, pb, tile, rows_a, rows_b, first, stride, chunks);
-        else accumulate_block<false, false>(acc, pa, pb, tile, rows_a, rows_b, first, stride, chunks);
+        if (full) accumulate_block<kG, true, false>(acc, pa, pb, tile, rows_a, rows_b, first, stride, chunks);
+        else accumulate_block<kG, false, false>(acc, pa, pb, tile, rows_a, rows_b, first, stride, chunks);
     }
 }
 
@@ -101,6 +105,7 @@ __device__ __forceinline__ float warp_sum(float v) {
 }
 
 // Add this warp's register accumulators of block pair (bi, bj) into its private n×n slot.
+template <int kG>
 __device__ __forceinline__ void flush(float (&acc)[kG][kG], int bi, int bj, int n, float* slot) {
     int const lane = threadIdx.x & 31;
 #pragma unroll
@@ -119,8 +124,15 @@ __device__ __forceinline__ void flush(float (&acc)[kG][kG], int bi, int bj, int 
 // work it hides behind stalls.
 thread_local int g_pairwise_cta_limit = 0;
 
+// GARFIELD_PAIRWISE_WIDE=0 keeps 4-row register blocks for every n (A/B measurements).
+bool wide_blocks_enabled() {
+    static int const on = [] { char const* v = std::getenv("GARFIELD_PAIRWISE_WIDE"); return (v != nullptr && v[0] == '0') ? 0 : 1; }();
+    return on != 0;
+}
+
 // ------------------------------------------------------------------------- kernel ---
 
+template <int kG>
 __global__ void __launch_bounds__(kThreads) pairwise_kernel(const __grid_constant__ PairwiseArgs a) {
     extern __shared__ __align__(128) unsigned char smem_raw[];
     __shared__ TileRing ring;
@@ -169,7 +181,7 @@ __global__ void __launch_bounds__(kThreads) pairwise_kernel(const __grid_constan
                 for (int p = 0; p < BP; ++p) {
                     int bi, bj;
                     block_pair_of(p, B, bi, bj);
-                    float const load = count[p] == 0 ? 1e9f : (bi == bj ? 6.0f : 16.0f) / count[p];
+                    float const load = count[p] == 0 ? 1e9f : (bi == bj ? 0.5f * kG * (kG - 1) : 1.0f * kG * kG) / count[p];
                     if (load > worst) {
                         worst = load;
                         pick = p;
@@ -191,19 +203,19 @@ __global__ void __launch_bounds__(kThreads) pairwise_kernel(const __grid_constan
             ptx::mbar_wait(&ring.full[s], phase);
             float const* src = stages + s * stage_floats + lane * 4;
             if (fixed) {
-                accumulate_pair(acc, src, tile, n, my_bi, my_bj, my_first, my_stride, chunks);
+                accumulate_pair<kG>(acc, src, tile, n, my_bi, my_bj, my_first, my_stride, chunks);
             } else {
                 for (int p = cw; p < BP; p += kConsumerWarps) {
                     int bi, bj;
                     block_pair_of(p, B, bi, bj);
-                    accumulate_pair(acc, src, tile, n, bi, bj, 0, 1, chunks);
-                    flush(acc, bi, bj, n, slot);
+                    accumulate_pair<kG>(acc, src, tile, n, bi, bj, 0, 1, chunks);
+                    flush<kG>(acc, bi, bj, n, slot);
                 }
             }
             __syncwarp();
             if (lane == 0) ptx::mbar_arrive(&ring.empty[s]);
         }
-        if (fixed) flush(acc, my_bi, my_bj, n, slot);
+        if (fixed) flush<kG>(acc, my_bi, my_bj, n, slot);
 
         // remainder / unaligned rows: direct global loads, one coordinate per lane
         long long const done = full_tiles * tile;
@@ -232,7 +244,7 @@ __global__ void __launch_bounds__(kThreads) pairwise_kernel(const __grid_constan
                                 acc[r][c] = fmaf(df, df, acc[r][c]);
                             }
                 }
-                flush(acc, bi, bj, n, slot);
+                flush<kG>(acc, bi, bj, n, slot);
             }
         }
     }
@@ -315,7 +327,9 @@ extern "C" GB_API int gb_pairwise_select(float const* const* rows, int n, int64_
     a.counter = static_cast<unsigned int*>(scratch);
     a.partials = reinterpret_cast<float*>(static_cast<unsigned char*>(scratch) + 256);
 
-    auto kern = pairwise_kernel;
+    // 8-row blocks pay only when every block is full: measured at d = 23.5 M, n = 24 (aksel's 23 rows + median) 2.88 -> 2.19 ms, but
+    // n = 23 (a 7-row last block takes the predicated path) 2.16 -> 2.22 ms
+    auto kern = n > 12 && n % 8 == 0 && wide_blocks_enabled() ? pairwise_kernel<8> : pairwise_kernel<4>;
     if (cuda_check(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)), "pairwise smem attribute")) return 1;
     kern<<<static_cast<int>(grid), kThreads, smem, static_cast<cudaStream_t>(stream)>>>(a);
     return cuda_check(cudaGetLastError(), "pairwise launch");
@@ -464,7 +478,7 @@ extern "C" GB_API int gb_pairwise_select_noalloc(float const* const* rows, int n
     cudaStream_t const st = static_cast<cudaStream_t>(stream);
     // the completion counter must be zero when the kernel starts, whatever an earlier call left behind
     if (cuda_check(cudaMemsetAsync(scratch, 0, 256, st), "no-alloc pairwise: clearing the counter")) return 1;
-    auto kern = pairwise_kernel;
+    auto kern = pairwise_kernel<4>;   // n <= 16 here: the fixed scratch array is sized for it
     if (cuda_check(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)), "no-alloc pairwise: smem attribute")) return 1;
     kern<<<static_cast<int>(grid), kThreads, smem, st>>>(a);
     return cuda_check(cudaGetLastError(), "no-alloc pairwise: launch");
