@@ -29,23 +29,39 @@ inline unsigned grid_for(long long total, int block = 256) {
     return static_cast<unsigned>(blocks < 1 ? 1 : blocks);
 }
 
+// One block = kIm2colPixels consecutive output pixels × all kpad columns. The pixel → (image, row, column) decomposition is done
+// once per pixel (first warp, shared memory), the column → (kh, kw, c) decomposition once per thread and column; the inner loop
+// is one predicated load and one coalesced store per element (the first version redid both decompositions per element and
+// ran at 0.46 TB/s on the stem's 30 MB patch matrix).
+constexpr int kIm2colPixels = 32;
 __global__ void __launch_bounds__(256) im2col_pad_kernel(const float* __restrict__ x, float* __restrict__ cols, int H, int W, int C, int pitch, int KH,
-                                                          int KW, int sh, int sw, int ph, int pw, int Ho, int Wo, int kpad, long long total) {
-    int const k_real = KH * KW * C;
-    for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < total; i += static_cast<long long>(gridDim.x) * blockDim.x) {
-        int const k = static_cast<int>(i % kpad);
-        long long r = i / kpad;
-        float v = 0.f;
-        if (k < k_real) {
-            int const c = k % C, kw = (k / C) % KW, kh = k / (C * KW);
+                                                          int KW, int sh, int sw, int ph, int pw, int Ho, int Wo, int kpad, long long pixels) {
+    __shared__ long long base[kIm2colPixels];     // offset of pixel (n, 0, 0) ... in floats: n·H·W·pitch
+    __shared__ int hb[kIm2colPixels], wb[kIm2colPixels];
+    long long const pix0 = static_cast<long long>(blockIdx.x) * kIm2colPixels;
+    if (threadIdx.x < kIm2colPixels) {
+        long long const r = pix0 + threadIdx.x;
+        if (r < pixels) {
             int const wo = static_cast<int>(r % Wo);
             long long const t = r / Wo;
             int const ho = static_cast<int>(t % Ho);
-            long long const n = t / Ho;
-            int const h = ho * sh - ph + kh, w = wo * sw - pw + kw;
-            if (h >= 0 && h < H && w >= 0 && w < W) v = x[((n * H + h) * W + w) * pitch + c];
+            base[threadIdx.x] = (t / Ho) * H * W * pitch;
+            hb[threadIdx.x] = ho * sh - ph;
+            wb[threadIdx.x] = wo * sw - pw;
         }
-        cols[i] = v;
+    }
+    __syncthreads();
+    int const k_real = KH * KW * C;
+    int const count = static_cast<int>(min(static_cast<long long>(kIm2colPixels), pixels - pix0));
+    for (int k = threadIdx.x; k < kpad; k += blockDim.x) {
+        bool const real = k < k_real;
+        int const c = k % C, kw = (k / C) % KW, kh = k / (C * KW);
+        for (int p = 0; p < count; ++p) {
+            int const h = hb[p] + kh, w = wb[p] + kw;
+            float v = 0.f;
+            if (real && h >= 0 && h < H && w >= 0 && w < W) v = x[base[p] + (static_cast<long long>(h) * W + w) * pitch + c];
+            cols[(pix0 + p) * kpad + k] = v;
+        }
     }
 }
 
@@ -296,9 +312,11 @@ extern "C" GB_API int gb_im2col_pad_nhwc(float const* x, float* cols, int N, int
         return cuda_fail("im2col_pad_nhwc: bad geometry");
     int const Ho = (H + 2 * pad_h - KH) / stride_h + 1, Wo = (W + 2 * pad_w - KW) / stride_w + 1;
     if (Ho < 1 || Wo < 1) return cuda_fail("im2col_pad_nhwc: empty output");
-    long long const total = static_cast<long long>(N) * Ho * Wo * kpad;
-    im2col_pad_kernel<<<grid_for(total), 256, 0, static_cast<cudaStream_t>(stream)>>>(x, cols, H, W, C, pitch, KH, KW, stride_h, stride_w, pad_h, pad_w,
-                                                                                      Ho, Wo, kpad, total);
+    long long const pixels = static_cast<long long>(N) * Ho * Wo;
+    long long const blocks = (pixels + kIm2colPixels - 1) / kIm2colPixels;
+    if (blocks > 2147483647LL) return cuda_fail("im2col_pad_nhwc: too many output pixels");
+    im2col_pad_kernel<<<static_cast<unsigned>(blocks), 256, 0, static_cast<cudaStream_t>(stream)>>>(x, cols, H, W, C, pitch, KH, KW, stride_h, stride_w,
+                                                                                                   pad_h, pad_w, Ho, Wo, kpad, pixels);
     return cuda_check(cudaGetLastError(), "im2col_pad_nhwc");
 }
 
