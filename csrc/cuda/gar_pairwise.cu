@@ -34,7 +34,8 @@ namespace {
 
 // Rows per register block: warps own KG×KG row-block pairs. Per lane and 128 coordinates a block pair costs 2·KG LDS.128 and
 // 2·KG² FADD/FFMA pairs: at KG = 4 shared-memory reads and FP32 issue are balanced (both ≈50 % of the SM), at KG = 8 the
-// shared-memory traffic per FMA halves and the kernel is FP32-bound — used from 13 rows on (fewer rows leave most of an 8×8 block empty).
+// shared-memory traffic per FMA halves and the kernel is FP32-bound — used at n = 16 (3 full block pairs for 8 warps); other row
+// counts above 12 take pairwise_multi_kernel below.
 
 __device__ __forceinline__ void block_pair_of(int item, int B, int& bi, int& bj) {
     // enumerate (bi <= bj) row-block pairs in row-major order
@@ -117,6 +118,80 @@ __device__ __forceinline__ void flush(float (&acc)[kG][kG], int bi, int bj, int 
             if (lane == 0 && i < n && j < n && i < j) slot[i * n + j] += total;
             acc[r][c] = 0.0f;
         }
+}
+
+// Coordinates that do not fill a tile (and rows the bulk copies cannot take: unaligned) — direct global loads, one coordinate
+// per lane, every block pair flushed into the warp's slot.
+template <int kG>
+__device__ __forceinline__ void remainder_pass(PairwiseArgs const& a, long long done, int cw, int lane, int B, int BP, float* slot) {
+    long long const rest = a.d - done;
+    if (rest <= 0) return;
+    int const n = a.n;
+    long long const per_cta = (rest + gridDim.x - 1) / gridDim.x;
+    long long const lo = done + per_cta * blockIdx.x;
+    long long const hi = min(a.d, lo + per_cta);
+    float acc[kG][kG];
+#pragma unroll
+    for (int r = 0; r < kG; ++r)
+#pragma unroll
+        for (int c = 0; c < kG; ++c) acc[r][c] = 0.0f;
+    for (int p = cw; p < BP; p += kConsumerWarps) {
+        int bi, bj;
+        block_pair_of(p, B, bi, bj);
+        for (long long x = lo + lane; x < hi; x += 32) {
+            float va[kG], vb[kG];
+#pragma unroll
+            for (int r = 0; r < kG; ++r) {
+                int const ra = bi * kG + r, rb = bj * kG + r;
+                va[r] = ra < n ? a.rows.p[ra][x] : 0.0f;
+                vb[r] = rb < n ? a.rows.p[rb][x] : 0.0f;
+            }
+#pragma unroll
+            for (int r = 0; r < kG; ++r)
+#pragma unroll
+                for (int c = 0; c < kG; ++c)
+                    if (bi != bj || c > r) {
+                        float const df = va[r] - vb[c];
+                        acc[r][c] = fmaf(df, df, acc[r][c]);
+                    }
+        }
+        flush<kG>(acc, bi, bj, n, slot);
+    }
+}
+
+// After the streaming loop: CTA partial = Σ over warps in fixed order → global scratch; the last CTA to finish reduces the
+// partials in CTA order (double), symmetrises, maps non-finite values to +inf and runs the selection.
+__device__ __forceinline__ void finish_cta(PairwiseArgs const& a, float* slots, unsigned char* smem_raw, unsigned int& is_last) {
+    int const n = a.n, nn = n * n;
+    __syncthreads();
+    float* mine = a.partials + static_cast<size_t>(blockIdx.x) * nn;
+    for (int e = threadIdx.x; e < nn; e += blockDim.x) {
+        float s = 0.0f;
+#pragma unroll
+        for (int w = 0; w < kConsumerWarps; ++w) s += slots[w * nn + e];
+        mine[e] = s;
+    }
+    __threadfence();
+    __syncthreads();
+    if (threadIdx.x == 0) is_last = (atomicAdd(a.counter, 1u) == gridDim.x - 1) ? 1u : 0u;
+    __syncthreads();
+    if (!is_last) return;
+    __threadfence();
+    for (int e = threadIdx.x; e < nn; e += blockDim.x) {
+        int const i = e / n, j = e % n;
+        float out = INFINITY;
+        if (i != j) {
+            int const src = i < j ? i * n + j : j * n + i;
+            double total = 0.0;
+            for (unsigned b = 0; b < gridDim.x; ++b) total += static_cast<double>(__ldcg(a.partials + static_cast<size_t>(b) * nn + src));
+            float const f = static_cast<float>(total);
+            out = (fabsf(f) <= FLT_MAX) ? f : INFINITY;
+        }
+        a.dist[e] = out;
+    }
+    if (threadIdx.x == 0) *a.counter = 0u;  // ready for the next launch
+    __syncthreads();
+    run_selection(a, *reinterpret_cast<SelectScratch*>(smem_raw));
 }
 
 // Upper bound on the CTAs of the next gb_pairwise_select launches of this thread (0 = fill the GPU). A distance pass that runs
@@ -217,70 +292,177 @@ __global__ void __launch_bounds__(kThreads) pairwise_kernel(const __grid_constan
         }
         if (fixed) flush<kG>(acc, my_bi, my_bj, n, slot);
 
-        // remainder / unaligned rows: direct global loads, one coordinate per lane
-        long long const done = full_tiles * tile;
-        long long const rest = a.d - done;
-        if (rest > 0) {
-            long long const per_cta = (rest + gridDim.x - 1) / gridDim.x;
-            long long const lo = done + per_cta * blockIdx.x;
-            long long const hi = min(a.d, lo + per_cta);
-            for (int p = cw; p < BP; p += kConsumerWarps) {
+        remainder_pass<kG>(a, full_tiles * tile, cw, lane, B, BP, slot);
+    }
+    finish_cta(a, slots, smem_raw, is_last);
+}
+
+// ---------------------------------------------------- 13..32 rows: register-resident sums ---
+//
+// With more block pairs than warps the kernel above flushes a warp's 16 sums after every (tile, block pair) — 80 shuffles
+// against the 16 LDS.128 + 256 FP32 instructions of a 256-coordinate tile, and one lane issuing n one-kilobyte copies per
+// stage. This variant (4-row blocks, B <= 8 → at most 36 block pairs) instead
+//   * gives every warp up to QO off-diagonal and QD diagonal block pairs for the whole kernel (longest-processing-time
+//     assignment: 16 against 6 row pairs) and keeps all their sums in registers — one flush per kernel. The slots are typed
+//     so that the unrolled loop holds QO + QD copies of the block code, not 2·(QO + QD): measured at n = 23, ten copies ran
+//     at 0.75 ms and twelve at 0.89 ms — the loop has to stay inside the instruction cache;
+//   * pads each stage to 4·B rows whose phantom rows are zeroed once, so every block takes the predicate-free path;
+//   * sizes the tile for one CTA per SM (≈200 KB of shared memory: 640 coordinates at n = 23) and lets lane i of the
+//     producer warp issue row i's copy.
+constexpr int kMultiRows = 32;
+constexpr int kMultiPairs = kMultiRows / 4 * (kMultiRows / 4 + 1) / 2;
+
+template <int QO, int QD>
+__global__ void __launch_bounds__(kThreads, 1) pairwise_multi_kernel(const __grid_constant__ PairwiseArgs a) {
+    constexpr int kG = 4;
+    extern __shared__ __align__(128) unsigned char smem_raw[];
+    __shared__ TileRing ring;
+    __shared__ unsigned int is_last;
+    __shared__ unsigned char owner[kMultiPairs];
+    int const n = a.n;
+    int const nn = n * n;
+    float* slots = reinterpret_cast<float*>(smem_raw);
+    int const slot_floats = ((kConsumerWarps * nn + 31) / 32) * 32;
+    float* stages = slots + slot_floats;
+    int const warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    int const tile = a.tile;
+    long long const full_tiles = a.use_tma ? a.d / tile : 0;
+    int const B = (n + kG - 1) / kG;
+    int const BP = B * (B + 1) / 2;
+    int const padded = B * kG;
+    size_t const stage_floats = static_cast<size_t>(padded) * tile;
+
+    for (int i = threadIdx.x; i < kConsumerWarps * nn; i += blockDim.x) slots[i] = 0.0f;
+    for (int s = 0; s < kStages; ++s)
+        for (int i = threadIdx.x; i < (padded - n) * tile; i += blockDim.x) stages[s * stage_floats + static_cast<size_t>(n) * tile + i] = 0.0f;
+    if (threadIdx.x == 32) {
+        float load[kConsumerWarps];
+        int held_off[kConsumerWarps], held_diag[kConsumerWarps];
+        for (int w = 0; w < kConsumerWarps; ++w) { load[w] = 0.0f; held_off[w] = held_diag[w] = 0; }
+        for (int pass = 0; pass < 2; ++pass)          // the expensive (off-diagonal) pairs first
+            for (int p = 0; p < BP; ++p) {
                 int bi, bj;
                 block_pair_of(p, B, bi, bj);
-                for (long long x = lo + lane; x < hi; x += 32) {
-                    float va[kG], vb[kG];
-#pragma unroll
-                    for (int r = 0; r < kG; ++r) {
-                        int const ra = bi * kG + r, rb = bj * kG + r;
-                        va[r] = ra < n ? a.rows.p[ra][x] : 0.0f;
-                        vb[r] = rb < n ? a.rows.p[rb][x] : 0.0f;
-                    }
-#pragma unroll
-                    for (int r = 0; r < kG; ++r)
-#pragma unroll
-                        for (int c = 0; c < kG; ++c)
-                            if (bi != bj || c > r) {
-                                float const df = va[r] - vb[c];
-                                acc[r][c] = fmaf(df, df, acc[r][c]);
-                            }
+                bool const diag = bi == bj;
+                if (diag != (pass == 1)) continue;
+                int best = -1;
+                for (int w = 0; w < kConsumerWarps; ++w) {
+                    bool const room = diag ? held_diag[w] < QD : held_off[w] < QO;
+                    if (room && (best < 0 || load[w] < load[best])) best = w;
                 }
-                flush<kG>(acc, bi, bj, n, slot);
+                owner[p] = static_cast<unsigned char>(best);     // the host picks (QO, QD) so that a warp with room exists
+                load[best] += diag ? 0.5f * kG * (kG - 1) : 1.0f * kG * kG;
+                ++(diag ? held_diag[best] : held_off[best]);
             }
-        }
     }
-    __syncthreads();
+    ring_init(ring);
 
-    // CTA partial = Σ over warps in fixed order → global scratch
-    float* mine = a.partials + static_cast<size_t>(blockIdx.x) * nn;
-    for (int e = threadIdx.x; e < nn; e += blockDim.x) {
-        float s = 0.0f;
+    if (warp == 0) {
+        uint32_t const row_bytes = static_cast<uint32_t>(tile) * 4u;
+        float const* const row = lane < n ? a.rows.p[lane] : nullptr;
+        long long it = 0;
+        for (long long t = blockIdx.x; t < full_tiles; t += gridDim.x, ++it) {
+            int const s = static_cast<int>(it % kStages);
+            uint32_t const phase = static_cast<uint32_t>((it / kStages) & 1);
+            ptx::mbar_wait(&ring.empty[s], phase ^ 1u);
+            if (lane == 0) ptx::mbar_arrive_expect_tx(&ring.full[s], row_bytes * static_cast<uint32_t>(n));
+            __syncwarp();
+            if (lane < n) ptx::bulk_g2s(stages + s * stage_floats + static_cast<size_t>(lane) * tile, row + t * tile, row_bytes, &ring.full[s]);
+        }
+    } else {
+        int const cw = warp - 1;
+        float* slot = slots + cw * nn;
+        float acc_off[QO][kG][kG], acc_diag[QD][kG][kG];
+        int off_a[QO], off_b[QO], diag_a[QD];
 #pragma unroll
-        for (int w = 0; w < kConsumerWarps; ++w) s += slots[w * nn + e];
-        mine[e] = s;
-    }
-    __threadfence();
-    __syncthreads();
-    if (threadIdx.x == 0) is_last = (atomicAdd(a.counter, 1u) == gridDim.x - 1) ? 1u : 0u;
-    __syncthreads();
-    if (!is_last) return;
-    __threadfence();
-
-    // last CTA: fixed-order reduction over CTAs (double), symmetrise, non-finite → +inf
-    for (int e = threadIdx.x; e < nn; e += blockDim.x) {
-        int const i = e / n, j = e % n;
-        float out = INFINITY;
-        if (i != j) {
-            int const src = i < j ? i * n + j : j * n + i;
-            double total = 0.0;
-            for (unsigned b = 0; b < gridDim.x; ++b) total += static_cast<double>(__ldcg(a.partials + static_cast<size_t>(b) * nn + src));
-            float const f = static_cast<float>(total);
-            out = (fabsf(f) <= FLT_MAX) ? f : INFINITY;
+        for (int q = 0; q < QO; ++q) {
+            off_a[q] = off_b[q] = 0;
+#pragma unroll
+            for (int r = 0; r < kG; ++r)
+#pragma unroll
+                for (int c = 0; c < kG; ++c) acc_off[q][r][c] = 0.0f;
         }
-        a.dist[e] = out;
+#pragma unroll
+        for (int q = 0; q < QD; ++q) {
+            diag_a[q] = 0;
+#pragma unroll
+            for (int r = 0; r < kG; ++r)
+#pragma unroll
+                for (int c = 0; c < kG; ++c) acc_diag[q][r][c] = 0.0f;
+        }
+        int n_off = 0, n_diag = 0;
+        for (int p = 0; p < BP; ++p)
+            if (owner[p] == cw) {
+                int x, y;
+                block_pair_of(p, B, x, y);
+                if (x == y) {
+#pragma unroll
+                    for (int q = 0; q < QD; ++q)
+                        if (q == n_diag) diag_a[q] = x;
+                    ++n_diag;
+                } else {
+#pragma unroll
+                    for (int q = 0; q < QO; ++q)
+                        if (q == n_off) { off_a[q] = x; off_b[q] = y; }
+                    ++n_off;
+                }
+            }
+        int const chunks = tile / 128;
+        long long it = 0;
+        for (long long t = blockIdx.x; t < full_tiles; t += gridDim.x, ++it) {
+            int const s = static_cast<int>(it % kStages);
+            uint32_t const phase = static_cast<uint32_t>((it / kStages) & 1);
+            ptx::mbar_wait(&ring.full[s], phase);
+            float const* src = stages + s * stage_floats + lane * 4;
+#pragma unroll
+            for (int q = 0; q < QO; ++q)
+                if (q < n_off)
+                    accumulate_block<kG, true, false>(acc_off[q], src + off_a[q] * kG * tile, src + off_b[q] * kG * tile, tile, kG, kG, 0, 1, chunks);
+#pragma unroll
+            for (int q = 0; q < QD; ++q)
+                if (q < n_diag) {
+                    float const* pa = src + diag_a[q] * kG * tile;
+                    accumulate_block<kG, true, true>(acc_diag[q], pa, pa, tile, kG, kG, 0, 1, chunks);
+                }
+            __syncwarp();
+            if (lane == 0) ptx::mbar_arrive(&ring.empty[s]);
+        }
+#pragma unroll
+        for (int q = 0; q < QO; ++q)
+            if (q < n_off) flush<kG>(acc_off[q], off_a[q], off_b[q], n, slot);
+#pragma unroll
+        for (int q = 0; q < QD; ++q)
+            if (q < n_diag) flush<kG>(acc_diag[q], diag_a[q], diag_a[q], n, slot);
+        remainder_pass<kG>(a, full_tiles * tile, cw, lane, B, BP, slot);
     }
-    if (threadIdx.x == 0) *a.counter = 0u;  // ready for the next launch
-    __syncthreads();
-    run_selection(a, *reinterpret_cast<SelectScratch*>(smem_raw));
+    finish_cta(a, slots, smem_raw, is_last);
+}
+
+// GARFIELD_PAIRWISE_MULTI=0 sends 13..32 rows through the general kernel again (A/B measurements).
+bool multi_enabled() {
+    static int const on = [] { char const* v = std::getenv("GARFIELD_PAIRWISE_MULTI"); return (v != nullptr && v[0] == '0') ? 0 : 1; }();
+    return on != 0;
+}
+
+// Tile of the register-resident variant: the largest multiple of 128 coordinates whose three padded stages fit ≈200 KB.
+int multi_tile(int n) {
+    int const padded = (n + 3) / 4 * 4;
+    int const slot_bytes = ((kConsumerWarps * n * n + 31) / 32) * 32 * 4;
+    int tile = (200 * 1024 - slot_bytes) / (kStages * padded * 4) / 128 * 128;
+    if (tile < 128) tile = 128;
+    if (tile > 1024) tile = 1024;
+    return tile;
+}
+
+// Slot counts per block count B = ⌈n/4⌉ (B(B−1)/2 off-diagonal and B diagonal pairs on 8 warps):
+//   B = 4: 6 + 4 → (1, 2);  B = 5: 10 + 5 → (2, 1);  B = 6: 15 + 6 → (2, 1);  B = 7: 21 + 7 → (3, 1);  B = 8: 28 + 8 → (4, 1)
+using MultiKernel = void (*)(PairwiseArgs);
+MultiKernel multi_kernel_for(int n) {
+    int const B = (n + 3) / 4;
+    if (B <= 4) return pairwise_multi_kernel<1, 2>;
+    if (B <= 6) return pairwise_multi_kernel<2, 1>;
+    if (B == 7) return pairwise_multi_kernel<3, 1>;
+    return pairwise_multi_kernel<4, 1>;
 }
 
 }  // namespace
@@ -309,15 +491,21 @@ extern "C" GB_API int gb_pairwise_select(float const* const* rows, int n, int64_
     for (int i = 0; i < n; ++i) a.rows.p[i] = rows[i];
     a.n = n; a.d = d; a.dist = dist; a.W = W; a.info = info;
     a.sel.mode = mode; a.sel.f = f; a.sel.m = m; a.sel.neighbors = neighbors; a.sel.squared = squared;
-    a.tile = pick_tile(n);
     a.use_tma = rows_aligned(a.rows, n) ? 1 : 0;
+    // 13..32 rows: register-resident sums. Measured at d = 23.5 M (general kernel -> this one): n = 13 0.61 -> 0.34 ms, 20 1.09 -> 0.52,
+    // 23 1.58 -> 0.74, 24 0.86 (8-row blocks) -> 0.74, 28 2.61 -> 1.02, 32 5.79 -> 1.26. n = 16 keeps the general kernel with 8-row
+    // blocks (3 block pairs, sums already register-resident there: 0.331 against 0.338 ms).
+    bool const wide = n == 16 && wide_blocks_enabled();
+    bool const multi = n > 12 && n <= kMultiRows && multi_enabled() && !wide;
+    a.tile = multi ? multi_tile(n) : pick_tile(n);
 
     int const nn = n * n;
     int const slot_floats = ((kConsumerWarps * nn + 31) / 32) * 32;
-    size_t smem = sizeof(float) * (static_cast<size_t>(slot_floats) + static_cast<size_t>(kStages) * n * a.tile);
+    int const stage_rows = multi ? (n + 3) / 4 * 4 : n;
+    size_t smem = sizeof(float) * (static_cast<size_t>(slot_floats) + static_cast<size_t>(kStages) * stage_rows * a.tile);
     if (smem < sizeof(SelectScratch)) smem = sizeof(SelectScratch);
     long long const tiles = (d + a.tile - 1) / a.tile;
-    int const ctas_per_sm = smem <= 100 * 1024 ? 2 : 1;
+    int const ctas_per_sm = (smem <= 100 * 1024 && !multi) ? 2 : 1;
     long long grid = static_cast<long long>(device_sm_count()) * ctas_per_sm;
     if (g_pairwise_cta_limit > 0 && grid > g_pairwise_cta_limit) grid = g_pairwise_cta_limit;   // background launch: leave SMs to others
     if (grid > tiles) grid = tiles;
@@ -327,9 +515,7 @@ extern "C" GB_API int gb_pairwise_select(float const* const* rows, int n, int64_
     a.counter = static_cast<unsigned int*>(scratch);
     a.partials = reinterpret_cast<float*>(static_cast<unsigned char*>(scratch) + 256);
 
-    // 8-row blocks pay only when every block is full: measured at d = 23.5 M, n = 24 (aksel's 23 rows + median) 2.88 -> 2.19 ms, but
-    // n = 23 (a 7-row last block takes the predicated path) 2.16 -> 2.22 ms
-    auto kern = n > 12 && n % 8 == 0 && wide_blocks_enabled() ? pairwise_kernel<8> : pairwise_kernel<4>;
+    auto kern = multi ? multi_kernel_for(n) : (wide ? pairwise_kernel<8> : pairwise_kernel<4>);
     if (cuda_check(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)), "pairwise smem attribute")) return 1;
     kern<<<static_cast<int>(grid), kThreads, smem, static_cast<cudaStream_t>(stream)>>>(a);
     return cuda_check(cudaGetLastError(), "pairwise launch");
