@@ -16,6 +16,8 @@
 //     in registers from the weight matrix W (θ×n) right before the network;
 //   * the optimizer update and the model publication are fused in the epilogue.
 
+#include <cstdlib>
+
 #include "gar_coordwise.cuh"
 #include "garfield_b200.h"
 #include "launch.cuh"
@@ -73,7 +75,17 @@ extern "C" GB_API int gb_coordwise(float const* const* rows, int n, int64_t d, i
 
     // register-array size of the sorting network: the next bucket >= cnt (pruned Batcher networks)
     int const np = rule == kRuleLinear ? 1 : cnt <= 4 ? 4 : cnt <= 32 ? (cnt + 3) / 4 * 4 : cnt <= 48 ? 48 : 64;
-    int const w_floats = theta > 0 ? ((np * n + 31) / 32) * 32 : 0;
+    // transposed weights, rows padded to 4 (gar_coordwise.cuh); the weighted sum keeps one weight per input
+    int const w_floats = theta > 0 ? (((np == 1 ? 1 : (np + 3) / 4 * 4) * ((n + 3) / 4 * 4) + 31) / 32) * 32 : 0;
+    // Weighted sums and W·x mixes of more than 16 rows: the 32 KB stages leave tiles of 256-384 coordinates, i.e. 64-96 of the 256
+    // consumer threads busy at 4 coordinates each. One CTA per SM with ≈220 KB of stages instead (n = 23, d = 23.5 M: weighted sum
+    // 0.61 -> 0.43 ms, Bulyan's second pass 2.54 -> 1.96 ms); the sorting rules without a mix keep two CTAs per SM (median 0.70
+    // against 0.90 ms).
+    if ((rule == kRuleLinear || theta > 0) && a.tile < 512) {
+        int tile = (220 * 1024 - w_floats * 4) / (kStages * n * 4) / 128 * 128;
+        if (tile > 1024) tile = 1024;
+        if (tile > a.tile) a.tile = tile;
+    }
     size_t const smem = sizeof(float) * (static_cast<size_t>(w_floats) + static_cast<size_t>(kStages) * n * a.tile);
     long long const tiles = (d + a.tile - 1) / a.tile;
     int const ctas_per_sm = smem <= 100 * 1024 ? 2 : 1;

@@ -110,18 +110,18 @@ __device__ __forceinline__ float reduce_column(float (&v)[NP], int cnt, int rank
                 else v[i] = (live && !isnan_) ? val : INFINITY;
             }
         }
-        sort_regs<NP>(v);
+        if constexpr (RULE != kRuleMedianLower && RULE != kRuleCondense && RULE != kRuleMedianFiniteUpper) sort_regs<NP>(v);
 
         float result = 0.0f;
         if constexpr (RULE == kRuleMedianLower || RULE == kRuleCondense) {
-            result = pick_reg<NP>(v, (cnt - 1) >> 1);
+            result = select_rank<NP>(v, (cnt - 1) >> 1);
             if (has_nan) result = NAN;
             if constexpr (RULE == kRuleCondense) {
                 uint4 const r = philox4x32(seed, static_cast<unsigned long long>(x), 0u);
                 result = (u01(r.x) < p) ? result : first_row_value;
             }
         } else if constexpr (RULE == kRuleMedianFiniteUpper) {
-            result = pick_reg<NP>(v, finite >> 1);
+            result = select_rank<NP>(v, finite >> 1);
             if (finite == 0) result = 0.0f;
         } else if constexpr (RULE == kRuleTrimmedMean) {
             int const lo = rank, hi = cnt - rank;
@@ -157,15 +157,46 @@ __device__ __forceinline__ void columns(CoordArgs const& a, float const* Ws, uns
         for (int k = 0; k < NP; ++k)
 #pragma unroll
             for (int e = 0; e < V; ++e) v[k][e] = 0.0f;
+        if constexpr (NP == 1) {   // weighted sum: the weights of 4 inputs per broadcast LDS.128; zero weight = input not read
+            for (int i0 = 0; i0 < a.n; i0 += 4) {
+                float4 const w4 = *reinterpret_cast<float4 const*>(Ws + i0);
+                float const w[4] = {w4.x, w4.y, w4.z, w4.w};
+#pragma unroll
+                for (int j = 0; j < 4; ++j)
+                    if (w[j] != 0.0f) {  // warp-uniform; entries beyond n are zero
+                        float xi[V];
+                        loadv(i0 + j, xi);
+#pragma unroll
+                        for (int e = 0; e < V; ++e) v[0][e] = fmaf(w[j], xi[e], v[0][e]);
+                    }
+            }
+        } else
         for (int i = 0; i < a.n; ++i) {
             if (!((used_mask >> i) & 1ull)) continue;  // warp-uniform
             float xi[V];
             loadv(i, xi);
+            // Ws is stored row-of-W-per-input (n × NPW, NPW = NP rounded up to 4): the NP weights of input i are NPW/4 broadcast
+            // LDS.128 instead of NP scalar loads (θ = 13, n = 23: 92 instead of 299 shared-memory wavefronts per coordinate)
+            constexpr int NPW = NP == 1 ? 1 : (NP + 3) / 4 * 4;
+            if constexpr (NP >= 4) {
 #pragma unroll
-            for (int k = 0; k < NP; ++k) {
-                float const w = Ws[k * a.n + i];
+                for (int k4 = 0; k4 < NP / 4; ++k4) {
+                    float4 const w = *reinterpret_cast<float4 const*>(Ws + i * NPW + k4 * 4);
 #pragma unroll
-                for (int e = 0; e < V; ++e) v[k][e] = fmaf(w, xi[e], v[k][e]);
+                    for (int e = 0; e < V; ++e) {
+                        v[k4 * 4 + 0][e] = fmaf(w.x, xi[e], v[k4 * 4 + 0][e]);
+                        v[k4 * 4 + 1][e] = fmaf(w.y, xi[e], v[k4 * 4 + 1][e]);
+                        v[k4 * 4 + 2][e] = fmaf(w.z, xi[e], v[k4 * 4 + 2][e]);
+                        v[k4 * 4 + 3][e] = fmaf(w.w, xi[e], v[k4 * 4 + 3][e]);
+                    }
+                }
+            } else {
+#pragma unroll
+                for (int k = 0; k < NP; ++k) {
+                    float const w = Ws[i * NPW + k];
+#pragma unroll
+                    for (int e = 0; e < V; ++e) v[k][e] = fmaf(w, xi[e], v[k][e]);
+                }
             }
         }
 #pragma unroll
@@ -203,29 +234,37 @@ template <int NP, int RULE, bool MIX, int V>
 __global__ void __launch_bounds__(kThreads) coordwise_kernel(const __grid_constant__ CoordArgs a) {
     extern __shared__ __align__(128) unsigned char smem_raw[];
     __shared__ TileRing ring;
-    float* Ws = reinterpret_cast<float*>(smem_raw);  // NP × n weights (MIX only), zero padded
-    int const w_floats = MIX ? ((NP * a.n + 31) / 32) * 32 : 0;
+    constexpr int NPW = NP == 1 ? 1 : (NP + 3) / 4 * 4;
+    int const n4 = (a.n + 3) / 4 * 4;
+    float* Ws = reinterpret_cast<float*>(smem_raw);  // n4 × NPW weights (MIX only): Ws[i][k] = W[k][i], zero beyond theta and n
+    int const w_floats = MIX ? ((NPW * n4 + 31) / 32) * 32 : 0;
     float* stages = Ws + w_floats;  // kStages × n × tile
     int const warp = threadIdx.x >> 5;
     int const tile = a.tile;
     long long const full_tiles = a.use_tma ? a.d / tile : 0;
 
     if constexpr (MIX)
-        for (int i = threadIdx.x; i < NP * a.n; i += blockDim.x) Ws[i] = (i < a.theta * a.n) ? a.W[i] : 0.0f;
+        for (int e = threadIdx.x; e < NPW * n4; e += blockDim.x) {
+            int const i = e / NPW, k = e % NPW;
+            Ws[e] = (k < a.theta && i < a.n) ? a.W[k * a.n + i] : 0.0f;
+        }
     ring_init(ring);  // contains the __syncthreads that also publishes Ws
     unsigned long long used_mask = ~0ull;  // rows with at least one non-zero weight
     if constexpr (MIX) {
         used_mask = 0ull;
         for (int i = 0; i < a.n; ++i) {
             bool used = false;
-            for (int k = 0; k < a.theta; ++k) used |= (Ws[k * a.n + i] != 0.0f);
+            for (int k = 0; k < a.theta; ++k) used |= (Ws[i * NPW + k] != 0.0f);
             used_mask |= used ? (1ull << i) : 0ull;
         }
     }
 
     if (warp == 0) {
-        if (full_tiles > 0 && ptx::elect_one())
-            ring_produce(ring, stages, a.rows, a.n, tile, full_tiles, [&](int i) { return ((used_mask >> i) & 1ull) != 0ull; });
+        auto const want = [&](int i) { return ((used_mask >> i) & 1ull) != 0ull; };
+        if (full_tiles > 0) {
+            if (a.warp_producer) ring_produce_warp(ring, stages, a.rows, a.n, tile, full_tiles, want);
+            else if (ptx::elect_one()) ring_produce(ring, stages, a.rows, a.n, tile, full_tiles, want);
+        }
     } else {
         int const ctid = threadIdx.x - 32;
         constexpr int kConsumers = 32 * kConsumerWarps;
@@ -269,7 +308,7 @@ cudaError_t launch_coordwise(CoordArgs const& a, int grid, size_t smem, cudaStre
 template <int NP>
 cudaError_t dispatch_coordwise(CoordArgs const& a, int grid, size_t smem, cudaStream_t stream);
 
-#define GB_DEFINE_COORDWISE_DISPATCH(NP, V)                                                                            \
+#define GB_DEFINE_COORDWISE_DISPATCH(NP, V, VMIX)                                                                          \
     template <>                                                                                                        \
     cudaError_t dispatch_coordwise<NP>(CoordArgs const& a, int grid, size_t smem, cudaStream_t stream) {               \
         bool const mix = a.theta > 0;                                                                                  \
@@ -279,7 +318,7 @@ cudaError_t dispatch_coordwise(CoordArgs const& a, int grid, size_t smem, cudaSt
             case kRuleTrimmedMean: return launch_coordwise<NP, kRuleTrimmedMean, false, V>(a, grid, smem, stream);     \
             case kRuleCondense: return launch_coordwise<NP, kRuleCondense, false, V>(a, grid, smem, stream);           \
             case kRuleAveragedMedian:                                                                                  \
-                return mix ? launch_coordwise<NP, kRuleAveragedMedian, true, V>(a, grid, smem, stream)                 \
+                return mix ? launch_coordwise<NP, kRuleAveragedMedian, true, VMIX>(a, grid, smem, stream)              \
                            : launch_coordwise<NP, kRuleAveragedMedian, false, V>(a, grid, smem, stream);               \
             default: return cudaErrorInvalidValue;                                                                     \
         }                                                                                                              \

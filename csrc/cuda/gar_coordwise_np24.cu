@@ -1,4 +1,4 @@
 #include "gar_coordwise.cuh"
 namespace gb {
-GB_DEFINE_COORDWISE_DISPATCH(24, 2)
+GB_DEFINE_COORDWISE_DISPATCH(24, 1, 2)
 }

@@ -1,4 +1,4 @@
 #include "gar_coordwise.cuh"
 namespace gb {
-GB_DEFINE_COORDWISE_DISPATCH(4, 4)
+GB_DEFINE_COORDWISE_DISPATCH(4, 4, 4)
 }

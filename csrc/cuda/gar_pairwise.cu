@@ -22,6 +22,7 @@
 #include <cstdlib>
 #include <cmath>
 #include <mutex>
+#include <type_traits>
 
 #include "../cpu/combinations.hpp"
 #include "gar_common.cuh"
@@ -33,9 +34,9 @@ namespace gb {
 namespace {
 
 // Rows per register block: warps own KG×KG row-block pairs. Per lane and 128 coordinates a block pair costs 2·KG LDS.128 and
-// 2·KG² FADD/FFMA pairs: at KG = 4 shared-memory reads and FP32 issue are balanced (both ≈50 % of the SM), at KG = 8 the
-// shared-memory traffic per FMA halves and the kernel is FP32-bound — used at n = 16 (3 full block pairs for 8 warps); other row
-// counts above 12 take pairwise_multi_kernel below.
+// 2·KG² FADD/FFMA pairs: at KG = 4 shared-memory reads and FP32 issue are balanced (both ≈50 % of the SM). (8-row blocks halve
+// the shared-memory traffic per FMA but were slower than pairwise_multi_kernel with packed FP32 at every n — 0.33 against
+// 0.26 ms at n = 16 — and are no longer instantiated.)
 
 __device__ __forceinline__ void block_pair_of(int item, int B, int& bi, int& bj) {
     // enumerate (bi <= bj) row-block pairs in row-major order
@@ -82,6 +83,76 @@ __device__ __forceinline__ void accumulate_block(float (&acc)[kG][kG], float con
     }
 }
 
+// Packed FP32 (sm_100 FADD2 / FFMA2: two lanes of a 64-bit register pair per instruction) for the register-resident kernel: half
+// the issue slots per squared difference, and the operands are register PAIRS — the scalar form subtracts .x from .x, .y from .y
+// of two LDS.128 results, i.e. always two registers of equal index modulo 4. A sum is kept as (even coordinates, odd coordinates)
+// and folded when it is flushed.
+using pair2 = unsigned long long;
+__device__ __forceinline__ pair2 pack2(float lo, float hi) {
+    pair2 r;
+    asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi));
+    return r;
+}
+__device__ __forceinline__ pair2 sub2(pair2 a, pair2 b) {
+    pair2 r;
+    asm("sub.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
+    return r;
+}
+__device__ __forceinline__ pair2 square_acc2(pair2 d, pair2 acc) {
+    pair2 r;
+    asm("fma.rn.f32x2 %0, %1, %1, %2;" : "=l"(r) : "l"(d), "l"(acc));
+    return r;
+}
+__device__ __forceinline__ float fold2(pair2 v) {
+    float lo, hi;
+    asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v));
+    return lo + hi;
+}
+template <bool FULL, bool DIAG>
+__device__ __forceinline__ void accumulate_block_packed(pair2 (&acc)[4][4], float const* pa, float const* pb, int tile, int rows_a, int rows_b,
+                                                        int first, int stride, int chunks) {
+    for (int ch = first; ch < chunks; ch += stride) {
+        pair2 a01[4], a23[4], b01[4], b23[4];
+#pragma unroll
+        for (int r = 0; r < 4; ++r) {
+            float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (FULL || r < rows_a) v = *reinterpret_cast<float4 const*>(pa + r * tile + ch * 128);
+            a01[r] = pack2(v.x, v.y);
+            a23[r] = pack2(v.z, v.w);
+            if constexpr (DIAG) {
+                b01[r] = a01[r];
+                b23[r] = a23[r];
+            } else {
+                float4 w = make_float4(0.f, 0.f, 0.f, 0.f);
+                if (FULL || r < rows_b) w = *reinterpret_cast<float4 const*>(pb + r * tile + ch * 128);
+                b01[r] = pack2(w.x, w.y);
+                b23[r] = pack2(w.z, w.w);
+            }
+        }
+#pragma unroll
+        for (int r = 0; r < 4; ++r)
+#pragma unroll
+            for (int c = 0; c < 4; ++c)
+                if (!DIAG || c > r) {
+                    acc[r][c] = square_acc2(sub2(a01[r], b01[c]), acc[r][c]);
+                    acc[r][c] = square_acc2(sub2(a23[r], b23[c]), acc[r][c]);
+                }
+    }
+}
+template <int kG>
+__device__ __forceinline__ void flush(float (&acc)[kG][kG], int bi, int bj, int n, float* slot);
+__device__ __forceinline__ void flush_packed(pair2 (&acc)[4][4], int bi, int bj, int n, float* slot) {
+    float folded[4][4];
+#pragma unroll
+    for (int r = 0; r < 4; ++r)
+#pragma unroll
+        for (int c = 0; c < 4; ++c) {
+            folded[r][c] = fold2(acc[r][c]);
+            acc[r][c] = 0ull;
+        }
+    flush<4>(folded, bi, bj, n, slot);
+}
+
 // Dispatch on (all rows present, diagonal block). `src` = stage base with the lane offset added.
 template <int kG>
 __device__ __forceinline__ void accumulate_pair(float (&acc)[kG][kG], float const* src, int tile, int n, int bi, int bj, int first,
@@ -96,6 +167,21 @@ __device__ __forceinline__ void accumulate_pair(float (&acc)[kG][kG], float cons
     } else {
         if (full) accumulate_block<kG, true, false>(acc, pa, pb, tile, rows_a, rows_b, first, stride, chunks);
         else accumulate_block<kG, false, false>(acc, pa, pb, tile, rows_a, rows_b, first, stride, chunks);
+    }
+}
+
+__device__ __forceinline__ void accumulate_pair_packed(pair2 (&acc)[4][4], float const* src, int tile, int n, int bi, int bj, int first, int stride,
+                                                       int chunks) {
+    float const* pa = src + bi * 4 * tile;
+    float const* pb = src + bj * 4 * tile;
+    int const rows_a = min(4, n - bi * 4), rows_b = min(4, n - bj * 4);
+    bool const full = rows_a == 4 && rows_b == 4;
+    if (bi == bj) {
+        if (full) accumulate_block_packed<true, true>(acc, pa, pb, tile, rows_a, rows_b, first, stride, chunks);
+        else accumulate_block_packed<false, true>(acc, pa, pb, tile, rows_a, rows_b, first, stride, chunks);
+    } else {
+        if (full) accumulate_block_packed<true, false>(acc, pa, pb, tile, rows_a, rows_b, first, stride, chunks);
+        else accumulate_block_packed<false, false>(acc, pa, pb, tile, rows_a, rows_b, first, stride, chunks);
     }
 }
 
@@ -199,16 +285,11 @@ __device__ __forceinline__ void finish_cta(PairwiseArgs const& a, float* slots, 
 // work it hides behind stalls.
 thread_local int g_pairwise_cta_limit = 0;
 
-// GARFIELD_PAIRWISE_WIDE=0 keeps 4-row register blocks for every n (A/B measurements).
-bool wide_blocks_enabled() {
-    static int const on = [] { char const* v = std::getenv("GARFIELD_PAIRWISE_WIDE"); return (v != nullptr && v[0] == '0') ? 0 : 1; }();
-    return on != 0;
-}
-
 // ------------------------------------------------------------------------- kernel ---
 
-template <int kG>
+template <int kG, bool PACKED = false>
 __global__ void __launch_bounds__(kThreads) pairwise_kernel(const __grid_constant__ PairwiseArgs a) {
+    static_assert(!PACKED || kG == 4, "packed FP32 accumulation is written for 4-row blocks");
     extern __shared__ __align__(128) unsigned char smem_raw[];
     __shared__ TileRing ring;
     __shared__ unsigned int is_last;
@@ -232,11 +313,12 @@ __global__ void __launch_bounds__(kThreads) pairwise_kernel(const __grid_constan
     } else {
         int const cw = warp - 1;  // consumer warp id
         float* slot = slots + cw * nn;
-        float acc[kG][kG];
+        using Acc = std::conditional_t<PACKED, pair2, float>;
+        Acc acc[kG][kG];
 #pragma unroll
         for (int r = 0; r < kG; ++r)
 #pragma unroll
-            for (int c = 0; c < kG; ++c) acc[r][c] = 0.0f;
+            for (int c = 0; c < kG; ++c) acc[r][c] = Acc(0);
         size_t const stage_floats = static_cast<size_t>(n) * tile;
         int const chunks = tile / 128;
 
@@ -278,19 +360,28 @@ __global__ void __launch_bounds__(kThreads) pairwise_kernel(const __grid_constan
             ptx::mbar_wait(&ring.full[s], phase);
             float const* src = stages + s * stage_floats + lane * 4;
             if (fixed) {
-                accumulate_pair<kG>(acc, src, tile, n, my_bi, my_bj, my_first, my_stride, chunks);
+                if constexpr (PACKED) accumulate_pair_packed(acc, src, tile, n, my_bi, my_bj, my_first, my_stride, chunks);
+                else accumulate_pair<kG>(acc, src, tile, n, my_bi, my_bj, my_first, my_stride, chunks);
             } else {
                 for (int p = cw; p < BP; p += kConsumerWarps) {
                     int bi, bj;
                     block_pair_of(p, B, bi, bj);
-                    accumulate_pair<kG>(acc, src, tile, n, bi, bj, 0, 1, chunks);
-                    flush<kG>(acc, bi, bj, n, slot);
+                    if constexpr (PACKED) {
+                        accumulate_pair_packed(acc, src, tile, n, bi, bj, 0, 1, chunks);
+                        flush_packed(acc, bi, bj, n, slot);
+                    } else {
+                        accumulate_pair<kG>(acc, src, tile, n, bi, bj, 0, 1, chunks);
+                        flush<kG>(acc, bi, bj, n, slot);
+                    }
                 }
             }
             __syncwarp();
             if (lane == 0) ptx::mbar_arrive(&ring.empty[s]);
         }
-        if (fixed) flush<kG>(acc, my_bi, my_bj, n, slot);
+        if (fixed) {
+            if constexpr (PACKED) flush_packed(acc, my_bi, my_bj, n, slot);
+            else flush<kG>(acc, my_bi, my_bj, n, slot);
+        }
 
         remainder_pass<kG>(a, full_tiles * tile, cw, lane, B, BP, slot);
     }
@@ -312,7 +403,7 @@ __global__ void __launch_bounds__(kThreads) pairwise_kernel(const __grid_constan
 constexpr int kMultiRows = 32;
 constexpr int kMultiPairs = kMultiRows / 4 * (kMultiRows / 4 + 1) / 2;
 
-template <int QO, int QD>
+template <int QO, int QD, bool PACKED>
 __global__ void __launch_bounds__(kThreads, 1) pairwise_multi_kernel(const __grid_constant__ PairwiseArgs a) {
     constexpr int kG = 4;
     extern __shared__ __align__(128) unsigned char smem_raw[];
@@ -372,7 +463,8 @@ __global__ void __launch_bounds__(kThreads, 1) pairwise_multi_kernel(const __gri
     } else {
         int const cw = warp - 1;
         float* slot = slots + cw * nn;
-        float acc_off[QO][kG][kG], acc_diag[QD][kG][kG];
+        using Acc = std::conditional_t<PACKED, pair2, float>;
+        Acc acc_off[QO][kG][kG], acc_diag[QD][kG][kG];
         int off_a[QO], off_b[QO], diag_a[QD];
 #pragma unroll
         for (int q = 0; q < QO; ++q) {
@@ -380,7 +472,7 @@ __global__ void __launch_bounds__(kThreads, 1) pairwise_multi_kernel(const __gri
 #pragma unroll
             for (int r = 0; r < kG; ++r)
 #pragma unroll
-                for (int c = 0; c < kG; ++c) acc_off[q][r][c] = 0.0f;
+                for (int c = 0; c < kG; ++c) acc_off[q][r][c] = Acc(0);
         }
 #pragma unroll
         for (int q = 0; q < QD; ++q) {
@@ -388,7 +480,7 @@ __global__ void __launch_bounds__(kThreads, 1) pairwise_multi_kernel(const __gri
 #pragma unroll
             for (int r = 0; r < kG; ++r)
 #pragma unroll
-                for (int c = 0; c < kG; ++c) acc_diag[q][r][c] = 0.0f;
+                for (int c = 0; c < kG; ++c) acc_diag[q][r][c] = Acc(0);
         }
         int n_off = 0, n_diag = 0;
         for (int p = 0; p < BP; ++p)
@@ -417,22 +509,34 @@ __global__ void __launch_bounds__(kThreads, 1) pairwise_multi_kernel(const __gri
 #pragma unroll
             for (int q = 0; q < QO; ++q)
                 if (q < n_off)
-                    accumulate_block<kG, true, false>(acc_off[q], src + off_a[q] * kG * tile, src + off_b[q] * kG * tile, tile, kG, kG, 0, 1, chunks);
+                {
+                    float const* pa = src + off_a[q] * kG * tile;
+                    float const* pb = src + off_b[q] * kG * tile;
+                    if constexpr (PACKED) accumulate_block_packed<true, false>(acc_off[q], pa, pb, tile, 4, 4, 0, 1, chunks);
+                    else accumulate_block<kG, true, false>(acc_off[q], pa, pb, tile, kG, kG, 0, 1, chunks);
+                }
 #pragma unroll
             for (int q = 0; q < QD; ++q)
                 if (q < n_diag) {
                     float const* pa = src + diag_a[q] * kG * tile;
-                    accumulate_block<kG, true, true>(acc_diag[q], pa, pa, tile, kG, kG, 0, 1, chunks);
+                    if constexpr (PACKED) accumulate_block_packed<true, true>(acc_diag[q], pa, pa, tile, 4, 4, 0, 1, chunks);
+                    else accumulate_block<kG, true, true>(acc_diag[q], pa, pa, tile, kG, kG, 0, 1, chunks);
                 }
             __syncwarp();
             if (lane == 0) ptx::mbar_arrive(&ring.empty[s]);
         }
 #pragma unroll
         for (int q = 0; q < QO; ++q)
-            if (q < n_off) flush<kG>(acc_off[q], off_a[q], off_b[q], n, slot);
+            if (q < n_off) {
+                if constexpr (PACKED) flush_packed(acc_off[q], off_a[q], off_b[q], n, slot);
+                else flush<kG>(acc_off[q], off_a[q], off_b[q], n, slot);
+            }
 #pragma unroll
         for (int q = 0; q < QD; ++q)
-            if (q < n_diag) flush<kG>(acc_diag[q], diag_a[q], diag_a[q], n, slot);
+            if (q < n_diag) {
+                if constexpr (PACKED) flush_packed(acc_diag[q], diag_a[q], diag_a[q], n, slot);
+                else flush<kG>(acc_diag[q], diag_a[q], diag_a[q], n, slot);
+            }
         remainder_pass<kG>(a, full_tiles * tile, cw, lane, B, BP, slot);
     }
     finish_cta(a, slots, smem_raw, is_last);
@@ -457,12 +561,23 @@ int multi_tile(int n) {
 // Slot counts per block count B = ⌈n/4⌉ (B(B−1)/2 off-diagonal and B diagonal pairs on 8 warps):
 //   B = 4: 6 + 4 → (1, 2);  B = 5: 10 + 5 → (2, 1);  B = 6: 15 + 6 → (2, 1);  B = 7: 21 + 7 → (3, 1);  B = 8: 28 + 8 → (4, 1)
 using MultiKernel = void (*)(PairwiseArgs);
+// (two CTAs per SM with 256-coordinate tiles were measured too: no faster, 0.74 against 0.72 ms at n = 23)
+// GARFIELD_PW_PACKED=0: scalar FADD / FFMA everywhere (A/B measurements).
+bool packed_enabled() {
+    static int const on = [] { char const* v = std::getenv("GARFIELD_PW_PACKED"); return (v != nullptr && v[0] == '0') ? 0 : 1; }();
+    return on != 0;
+}
 MultiKernel multi_kernel_for(int n) {
     int const B = (n + 3) / 4;
-    if (B <= 4) return pairwise_multi_kernel<1, 2>;
-    if (B <= 6) return pairwise_multi_kernel<2, 1>;
-    if (B == 7) return pairwise_multi_kernel<3, 1>;
-    return pairwise_multi_kernel<4, 1>;
+    if (packed_enabled()) {
+        if (B <= 4) return pairwise_multi_kernel<1, 2, true>;
+        if (B <= 6) return pairwise_multi_kernel<2, 1, true>;
+        if (B == 7) return pairwise_multi_kernel<3, 1, true>;
+    }
+    if (B <= 4) return pairwise_multi_kernel<1, 2, false>;
+    if (B <= 6) return pairwise_multi_kernel<2, 1, false>;
+    if (B == 7) return pairwise_multi_kernel<3, 1, false>;
+    return pairwise_multi_kernel<4, 1, false>;
 }
 
 }  // namespace
@@ -492,11 +607,11 @@ extern "C" GB_API int gb_pairwise_select(float const* const* rows, int n, int64_
     a.n = n; a.d = d; a.dist = dist; a.W = W; a.info = info;
     a.sel.mode = mode; a.sel.f = f; a.sel.m = m; a.sel.neighbors = neighbors; a.sel.squared = squared;
     a.use_tma = rows_aligned(a.rows, n) ? 1 : 0;
-    // 13..32 rows: register-resident sums. Measured at d = 23.5 M (general kernel -> this one): n = 13 0.61 -> 0.34 ms, 20 1.09 -> 0.52,
-    // 23 1.58 -> 0.74, 24 0.86 (8-row blocks) -> 0.74, 28 2.61 -> 1.02, 32 5.79 -> 1.26. n = 16 keeps the general kernel with 8-row
-    // blocks (3 block pairs, sums already register-resident there: 0.331 against 0.338 ms).
-    bool const wide = n == 16 && wide_blocks_enabled();
-    bool const multi = n > 12 && n <= kMultiRows && multi_enabled() && !wide;
+    // 13..32 rows: register-resident sums. Measured at d = 23.5 M (general kernel -> this one): n = 13 0.61 -> 0.26 ms, 16 0.33 -> 0.26,
+    // 20 1.09 -> 0.42, 23 1.58 -> 0.58, 24 0.86 -> 0.59, 28 2.61 -> 0.92, 32 5.79 -> 1.22.
+    bool const multi = n > 12 && n <= kMultiRows && multi_enabled();
+    // packed FP32 in the general kernel pays from 9 rows on (n = 10 0.256 -> 0.214 ms, 12 0.223 -> 0.207; n = 8 0.136 -> 0.142)
+    bool const packed = n > 8 && packed_enabled();
     a.tile = multi ? multi_tile(n) : pick_tile(n);
 
     int const nn = n * n;
@@ -515,7 +630,7 @@ extern "C" GB_API int gb_pairwise_select(float const* const* rows, int n, int64_
     a.counter = static_cast<unsigned int*>(scratch);
     a.partials = reinterpret_cast<float*>(static_cast<unsigned char*>(scratch) + 256);
 
-    auto kern = multi ? multi_kernel_for(n) : (wide ? pairwise_kernel<8> : pairwise_kernel<4>);
+    auto kern = multi ? multi_kernel_for(n) : (packed ? pairwise_kernel<4, true> : pairwise_kernel<4, false>);
     if (cuda_check(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)), "pairwise smem attribute")) return 1;
     kern<<<static_cast<int>(grid), kThreads, smem, static_cast<cudaStream_t>(stream)>>>(a);
     return cuda_check(cudaGetLastError(), "pairwise launch");
@@ -664,7 +779,7 @@ extern "C" GB_API int gb_pairwise_select_noalloc(float const* const* rows, int n
     cudaStream_t const st = static_cast<cudaStream_t>(stream);
     // the completion counter must be zero when the kernel starts, whatever an earlier call left behind
     if (cuda_check(cudaMemsetAsync(scratch, 0, 256, st), "no-alloc pairwise: clearing the counter")) return 1;
-    auto kern = pairwise_kernel<4>;   // n <= 16 here: the fixed scratch array is sized for it
+    auto kern = pairwise_kernel<4, false>;   // n <= 16 here: the fixed scratch array is sized for it
     if (cuda_check(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)), "no-alloc pairwise: smem attribute")) return 1;
     kern<<<static_cast<int>(grid), kThreads, smem, st>>>(a);
     return cuda_check(cudaGetLastError(), "no-alloc pairwise: launch");

@@ -47,7 +47,7 @@ for n in args.rows:
     ms = start.elapsed_time(stop) / 20
     floor = n * d * 4 / 6.5e12 * 1e3
     rec = {"n": n, "d": d, "ms": round(ms, 4), "hbm_floor_ms": round(floor, 4), "max_rel_err_vs_fp64": rel,
-           "multi": os.environ.get("GARFIELD_PAIRWISE_MULTI", "1"), "wide": os.environ.get("GARFIELD_PAIRWISE_WIDE", "1")}
+           "multi": os.environ.get("GARFIELD_PAIRWISE_MULTI", "1"), "packed": os.environ.get("GARFIELD_PW_PACKED", "1")}
     print(json.dumps(rec), flush=True)
     results.append(rec)
     del g, rows
