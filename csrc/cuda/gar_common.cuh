@@ -171,6 +171,48 @@ __device__ __forceinline__ void sort_pairs(float (&key)[NP], float (&val)[NP]) {
     sort_pairs_seq<NP>(key, val, std::make_integer_sequence<int, OddEvenNetwork<NP>::table.count>{});
 }
 
+// Bitonic merger: sorts a register array that is already BITONIC (here: |sorted values − their median|, which falls to zero at
+// the median and rises after it; +inf padding beyond the count keeps that shape) with ⌈log2 NP⌉ half-cleaner stages — 52
+// compare-exchanges at NP = 24 where the full network needs 132. Comparators reaching beyond NP are pruned like above.
+template <int NP>
+struct BitonicMerger {
+    static constexpr int kFull = next_pow2(NP);
+    static constexpr int kMax = NP * 6;
+    struct Table {
+        int a[kMax];
+        int b[kMax];
+        int count;
+    };
+    static constexpr Table build() {
+        Table t{};
+        t.count = 0;
+        for (int k = kFull / 2; k >= 1; k >>= 1)
+            for (int i = 0; i + k < NP; ++i)
+                if ((i & k) == 0) {
+                    t.a[t.count] = i;
+                    t.b[t.count] = i + k;
+                    ++t.count;
+                }
+        return t;
+    }
+    static constexpr Table table = build();
+};
+template <int NP, int C>
+__device__ __forceinline__ void merge_exchange(float (&v)[NP]) {
+    constexpr int a = BitonicMerger<NP>::table.a[C], b = BitonicMerger<NP>::table.b[C];
+    float const lo = fminf(v[a], v[b]), hi = fmaxf(v[a], v[b]);
+    v[a] = lo;
+    v[b] = hi;
+}
+template <int NP, int... Cs>
+__device__ __forceinline__ void merge_bitonic_seq(float (&v)[NP], std::integer_sequence<int, Cs...>) {
+    (merge_exchange<NP, Cs>(v), ...);
+}
+template <int NP>
+__device__ __forceinline__ void merge_bitonic(float (&v)[NP]) {
+    merge_bitonic_seq<NP>(v, std::make_integer_sequence<int, BitonicMerger<NP>::table.count>{});
+}
+
 // v[k] for a runtime (warp-uniform) k without dynamic register indexing.
 template <int NP>
 __device__ __forceinline__ float pick_reg(float const (&v)[NP], int k) {

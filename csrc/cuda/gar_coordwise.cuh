@@ -85,7 +85,7 @@ __device__ __forceinline__ void apply_update(FusedUpdate const& u, long long x, 
 // FLT_MAX (finite padding that sorts last). A cheap all-finite test (Σ 0·v on the FMA pipe)
 // selects the common path, which is the bare sorting network; columns containing NaN/±inf take
 // the careful path (NaN propagation or non-finite filtering, depending on the rule).
-template <int NP, int RULE>
+template <int NP, int RULE, bool MERGER = true>
 __device__ __forceinline__ float reduce_column(float (&v)[NP], int cnt, int rank, int upper, float p, unsigned long long seed,
                                                long long x, float first_row_value) {
     if constexpr (RULE == kRuleLinear) {
@@ -131,13 +131,38 @@ __device__ __forceinline__ float reduce_column(float (&v)[NP], int cnt, int rank
             result = has_nan ? NAN : sum / static_cast<float>(hi - lo);
         } else if constexpr (RULE == kRuleAveragedMedian) {
             float const med = pick_reg<NP>(v, upper ? (cnt >> 1) : ((cnt - 1) >> 1));
-            float key[NP];
+            // The β values closest to the median: v is sorted, so their distances to it form a bitonic sequence — a merger finds
+            // the β-th smallest distance r and the sum takes what lies closer than r plus as many at distance r as are still
+            // missing (this replaced a key-value sort of all NP pairs: 5 instructions per compare-exchange of the full network).
+            if constexpr (!MERGER) {   // 8 mixed values (Bulyan at n = 8): measured 0.362 ms with the key-value sort, 0.376 with the merger
+                float key[NP];
 #pragma unroll
-            for (int i = 0; i < NP; ++i) key[i] = (i < cnt) ? fabsf(v[i] - med) : INFINITY;
-            sort_pairs<NP>(key, v);
+                for (int i = 0; i < NP; ++i) key[i] = (i < cnt) ? fabsf(v[i] - med) : INFINITY;
+                sort_pairs<NP>(key, v);
+                float sum = 0.0f;
+#pragma unroll
+                for (int i = 0; i < NP; ++i) sum += (i < rank) ? v[i] : 0.0f;
+                return has_nan ? NAN : sum / static_cast<float>(rank);
+            }
+            float key[NP], ordered[NP];
+#pragma unroll
+            for (int i = 0; i < NP; ++i) ordered[i] = key[i] = (i < cnt) ? fabsf(v[i] - med) : INFINITY;
+            merge_bitonic<NP>(ordered);
+            float const radius = pick_reg<NP>(ordered, rank - 1);
             float sum = 0.0f;
+            int missing = rank;
 #pragma unroll
-            for (int i = 0; i < NP; ++i) sum += (i < rank) ? v[i] : 0.0f;
+            for (int i = 0; i < NP; ++i) {
+                bool const inside = key[i] < radius;
+                sum += inside ? v[i] : 0.0f;
+                missing -= inside ? 1 : 0;
+            }
+#pragma unroll
+            for (int i = 0; i < NP; ++i) {
+                bool const edge = key[i] == radius && missing > 0;
+                sum += edge ? v[i] : 0.0f;
+                missing -= edge ? 1 : 0;
+            }
             result = has_nan ? NAN : sum / static_cast<float>(rank);
         }
         return result;
@@ -226,7 +251,7 @@ __device__ __forceinline__ void columns(CoordArgs const& a, float const* Ws, uns
         float col[NP];
 #pragma unroll
         for (int i = 0; i < NP; ++i) col[i] = v[i][e];
-        result[e] = reduce_column<NP, RULE>(col, cnt, a.rank, a.upper, a.p, a.seed, x + e, first[e]);
+        result[e] = reduce_column<NP, RULE, (NP >= 12 || !MIX)>(col, cnt, a.rank, a.upper, a.p, a.seed, x + e, first[e]);
     }
 }
 
