@@ -84,6 +84,68 @@ def test_pairwise_distances(n, d):
     assert torch.equal(got, again), "distances must be run-to-run deterministic"
 
 
+@pytest.mark.parametrize("n", [9, 12, 13, 16, 17, 20, 21, 24, 25, 28, 29, 32])
+def test_pairwise_distances_many_tiles_per_cta(n):
+    """The 13-32-row kernel (register-resident sums, packed FP32, padded stages) and the packed general kernel over enough
+    coordinates for several tiles per CTA plus a remainder; phantom rows of the padded stages must not leak into the sums."""
+    gar = cuda_lib()
+    d = 148 * 1024 * 3 + 77
+    g = make(n, d, seed=n, spread=0.05)
+    got = gar.pairwise_sqdist(g).cpu().double()
+    want = torch.zeros(n, n, dtype=torch.float64)
+    mat = torch.stack(g).double()
+    for lo in range(0, d, 1 << 18):
+        x = mat[:, lo:lo + (1 << 18)]
+        want += ((x[:, None, :] - x[None, :, :]) ** 2).sum(-1).cpu()
+    want.fill_diagonal_(float("inf"))
+    torch.testing.assert_close(got, want, rtol=5e-6, atol=0)
+    assert torch.equal(got, gar.pairwise_sqdist(g).cpu().double()), "distances must be run-to-run deterministic"
+
+
+@pytest.mark.parametrize("n", [13, 23, 32])
+def test_pairwise_multi_kernel_unaligned_and_nonfinite_rows(n):
+    gar = cuda_lib()
+    d = 70001
+    backing = [torch.randn(d + 3, device="cuda") for _ in range(n)]
+    g = [b[1:d + 1] for b in backing]                    # 4-byte aligned only: every coordinate takes the direct-load path
+    mat = torch.stack(g).cpu().double()
+    want = torch.cdist(mat, mat).pow(2)
+    want.fill_diagonal_(float("inf"))
+    torch.testing.assert_close(gar.pairwise_sqdist(g).cpu().double(), want, rtol=2e-5, atol=1e-5)
+    bad = make(n, d, seed=3)
+    bad[n - 1][d // 2] = float("nan")
+    bad[1][5] = float("inf")
+    got = gar.pairwise_sqdist(bad).cpu()
+    assert torch.isinf(got[n - 1]).all() and torch.isinf(got[:, n - 1]).all() and torch.isinf(got[1]).all()
+    clean = [i for i in range(n) if i not in (1, n - 1)]
+    sub = torch.stack([bad[i] for i in clean]).cpu().double()
+    ref = torch.cdist(sub, sub).pow(2)
+    ref.fill_diagonal_(float("inf"))
+    torch.testing.assert_close(got[clean][:, clean].double(), ref, rtol=2e-5, atol=1e-5)
+
+
+@pytest.mark.parametrize("n,beta", [(8, 4), (13, 9), (23, 18), (24, 3), (32, 20)])
+def test_averaged_median_with_repeated_values(n, beta):
+    """Columns full of repeated values (ties at the selection radius): the result must be the mean of β values that are all at
+    least as close to the median as every value left out."""
+    gar = cuda_lib()
+    d = 5000
+    gen = torch.Generator().manual_seed(n)
+    mat = torch.randint(-3, 4, (n, d), generator=gen).float()
+    g = [mat[i].cuda() for i in range(n)]
+    got = gar.coordwise(g, "averaged_median", beta=beta).cpu().double()
+    med = mat.sort(0).values[(n - 1) // 2]
+    dist = (mat - med).abs()
+    order = dist.sort(0).values
+    radius = order[beta - 1]
+    inside = (mat * (dist < radius)).double().sum(0)
+    missing = beta - (dist < radius).sum(0)
+    edge_vals = torch.where(dist == radius, mat, torch.full_like(mat, float("nan")))
+    lo = inside + missing * torch.nan_to_num(edge_vals, nan=float("inf")).min(0).values.double()
+    hi = inside + missing * torch.nan_to_num(edge_vals, nan=-float("inf")).max(0).values.double()
+    assert ((got * beta >= lo - 1e-4) & (got * beta <= hi + 1e-4)).all()
+
+
 RULE_CASES = [(7, 1, 3000), (8, 1, 40000), (11, 2, 12345), (15, 3, 5000), (23, 5, 2048), (33, 7, 1500)]
 
 
@@ -312,7 +374,8 @@ def test_decentralized_worker_fusion_matches_per_node_path():
     assert diff.max().item() < 2e-3 and (diff > 2e-4).float().mean().item() < 1e-3, diff.max().item()
 
 
-@pytest.mark.parametrize("m,n,k", [(128, 128, 64), (25, 10, 84), (200, 120, 400), (77, 300, 1000), (512, 1024, 4096), (1000, 4096, 25088 // 8)])
+@pytest.mark.parametrize("m,n,k", [(128, 128, 64), (25, 10, 84), (200, 120, 400), (77, 300, 1000), (512, 1024, 4096), (1000, 4096, 25088 // 8),
+                                   (4096, 4096, 512), (2048 + 7, 4096 + 20, 1000), (300, 40000, 136)])   # the last three: CTA-pair kernel
 @pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
 def test_tcgen05_gemm_nt(m, n, k, dtype):
     from garfield_b200.ops import nn as gnn
