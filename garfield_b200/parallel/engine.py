@@ -244,7 +244,7 @@ class SSMWEngine:
         # layer of the model is covered; otherwise each worker keeps its own chain and stream
         self.fused = None
         if fuse_workers and self.workers:
-            self._fuse_workers(module, loss_fn, 1 if self.scatter else max(1, min(int(fusion_chains), len(self.workers))))
+            self._fuse_workers(module, loss_fn, max(1, min(int(fusion_chains), len(self.workers))))
 
         # distances during the backward pass (one GPU, distance-based rule, honest local workers): squared distances are sums
         # over coordinates and the LAST layers' gradients are complete early in the backward pass, so the pairwise kernel
@@ -362,12 +362,12 @@ class SSMWEngine:
         for lo, hi in zip(bounds[:-1], bounds[1:]):
             replica = FlatModel(copy.deepcopy(module), self.device, flat=self.flat, channels_last=self.channels_last)
             sink = None
-            if self.scatter:
+            if self.scatter:     # each chain scatters its own workers' rows (arena rows rank·max_local + lo ...)
                 arenas = [self.grad_arena.peer(r) for r in range(self.world)]
-                bounds = [self._bounds(r) for r in range(self.world)]
-                first, per = self.rank * self.max_local, self.per
-                rank = self.rank
-                sink = lambda params, slices, view_of: ScatterSink(params, slices, view_of, G, arenas, first, per, bounds, rank)
+                owned = [self._bounds(r) for r in range(self.world)]
+                first_row, per, rank, count = self.rank * self.max_local + lo, self.per, self.rank, hi - lo
+                sink = (lambda params, slices, view_of, first_row=first_row, count=count:
+                        ScatterSink(params, slices, view_of, count, arenas, first_row, per, owned, rank))
             group = GroupedWorkers(replica, [w.row for w in self.workers[lo:hi]], loss_fn, sink=sink)
             stream = torch.cuda.Stream(device=self.device) if chains > 1 else None
             self._chains.append((group, data[lo * b:hi * b], target[lo * t:hi * t], self._group_losses[lo:hi], stream))
