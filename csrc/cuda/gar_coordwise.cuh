@@ -37,6 +37,20 @@ __device__ __forceinline__ void vec_load(float (&dst)[V], const float* p) {
     }
 }
 
+// V floats from a 32-bit shared-memory address. The tile loads used to go through generic pointers (`src + i * tile + c`): the
+// compiler then rebuilt the shared window base for EVERY row (S2UR + ULEA + UMOV + ... ≈ 15 instructions per LDS; FMNMX was 26 %
+// of the median kernel's instructions at n = 23). With an explicit address a row costs one IMAD and one LDS.
+template <int V>
+__device__ __forceinline__ void lds_vec(float (&dst)[V], uint32_t addr) {
+    if constexpr (V == 4) {
+        asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(dst[0]), "=f"(dst[1]), "=f"(dst[2]), "=f"(dst[3]) : "r"(addr));
+    } else if constexpr (V == 2) {
+        asm volatile("ld.shared.v2.f32 {%0, %1}, [%2];" : "=f"(dst[0]), "=f"(dst[1]) : "r"(addr));
+    } else {
+        asm volatile("ld.shared.f32 %0, [%1];" : "=f"(dst[0]) : "r"(addr));
+    }
+}
+
 template <int V>
 __device__ __forceinline__ void vec_store(float* p, float const (&src)[V]) {
     if constexpr (V == 4) *reinterpret_cast<float4*>(p) = make_float4(src[0], src[1], src[2], src[3]);
@@ -182,10 +196,11 @@ __device__ __forceinline__ void columns(CoordArgs const& a, float const* Ws, uns
         for (int k = 0; k < NP; ++k)
 #pragma unroll
             for (int e = 0; e < V; ++e) v[k][e] = 0.0f;
+        uint32_t const ws_at = ptx::smem_u32(Ws);   // explicit shared addresses (see lds_vec)
         if constexpr (NP == 1) {   // weighted sum: the weights of 4 inputs per broadcast LDS.128; zero weight = input not read
             for (int i0 = 0; i0 < a.n; i0 += 4) {
-                float4 const w4 = *reinterpret_cast<float4 const*>(Ws + i0);
-                float const w[4] = {w4.x, w4.y, w4.z, w4.w};
+                float w[4];
+                lds_vec<4>(w, ws_at + static_cast<uint32_t>(i0) * 4u);
 #pragma unroll
                 for (int j = 0; j < 4; ++j)
                     if (w[j] != 0.0f) {  // warp-uniform; entries beyond n are zero
@@ -206,13 +221,14 @@ __device__ __forceinline__ void columns(CoordArgs const& a, float const* Ws, uns
             if constexpr (NP >= 4) {
 #pragma unroll
                 for (int k4 = 0; k4 < NP / 4; ++k4) {
-                    float4 const w = *reinterpret_cast<float4 const*>(Ws + i * NPW + k4 * 4);
+                    float w[4];
+                    lds_vec<4>(w, ws_at + static_cast<uint32_t>(i * NPW + k4 * 4) * 4u);
 #pragma unroll
                     for (int e = 0; e < V; ++e) {
-                        v[k4 * 4 + 0][e] = fmaf(w.x, xi[e], v[k4 * 4 + 0][e]);
-                        v[k4 * 4 + 1][e] = fmaf(w.y, xi[e], v[k4 * 4 + 1][e]);
-                        v[k4 * 4 + 2][e] = fmaf(w.z, xi[e], v[k4 * 4 + 2][e]);
-                        v[k4 * 4 + 3][e] = fmaf(w.w, xi[e], v[k4 * 4 + 3][e]);
+                        v[k4 * 4 + 0][e] = fmaf(w[0], xi[e], v[k4 * 4 + 0][e]);
+                        v[k4 * 4 + 1][e] = fmaf(w[1], xi[e], v[k4 * 4 + 1][e]);
+                        v[k4 * 4 + 2][e] = fmaf(w[2], xi[e], v[k4 * 4 + 2][e]);
+                        v[k4 * 4 + 3][e] = fmaf(w[3], xi[e], v[k4 * 4 + 3][e]);
                     }
                 }
             } else {
@@ -299,11 +315,13 @@ __global__ void __launch_bounds__(kThreads) coordwise_kernel(const __grid_consta
             int const s = static_cast<int>(it % kStages);
             uint32_t const phase = static_cast<uint32_t>((it / kStages) & 1);
             ptx::mbar_wait(&ring.full[s], phase);
-            float const* src = stages + s * stage_floats;
+            uint32_t const src = ptx::smem_u32(stages + s * stage_floats);
+            uint32_t const row_bytes = static_cast<uint32_t>(tile) * 4u;
             for (int c = ctid * V; c < tile; c += kConsumers * V) {
                 long long const x = t * tile + c;
                 float r[V];
-                columns<NP, RULE, MIX, V>(a, Ws, used_mask, x, [&](int i, float (&dst)[V]) { vec_load<V>(dst, src + i * tile + c); }, r);
+                uint32_t const at = src + static_cast<uint32_t>(c) * 4u;
+                columns<NP, RULE, MIX, V>(a, Ws, used_mask, x, [&](int i, float (&dst)[V]) { lds_vec<V>(dst, at + static_cast<uint32_t>(i) * row_bytes); }, r);
                 apply_update<V>(a.upd, x, r, a.out);
             }
             __syncwarp();

@@ -96,11 +96,13 @@ __global__ void __launch_bounds__(kThreads) gossip_kernel(const __grid_constant_
             for (long long t = blockIdx.x; t < full_tiles; t += G, ++it) {
                 int const s = static_cast<int>(it % kStages);
                 ptx::mbar_wait(&ring.full[s], static_cast<uint32_t>((it / kStages) & 1));
-                float const* src = stages + s * stage_floats;
+                uint32_t const src = ptx::smem_u32(stages + s * stage_floats);
+                uint32_t const row_bytes = static_cast<uint32_t>(tile) * 4u;
                 for (int c = ctid * V; c < tile; c += kConsumers * V) {
                     long long const x = t * tile + c;
                     float res[V];
-                    columns<NP, RULE, false, V>(a, nullptr, ~0ull, x, [&](int i, float (&dst)[V]) { vec_load<V>(dst, src + i * tile + c); }, res);
+                    uint32_t const at = src + static_cast<uint32_t>(c) * 4u;
+                    columns<NP, RULE, false, V>(a, nullptr, ~0ull, x, [&](int i, float (&dst)[V]) { lds_vec<V>(dst, at + static_cast<uint32_t>(i) * row_bytes); }, res);
                     for (int k = 0; k < g.n_out; ++k) vec_store<V>(g.out[parity][k] + x, res);
                 }
                 __syncwarp();
