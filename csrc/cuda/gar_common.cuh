@@ -89,6 +89,7 @@ struct PairwiseArgs {
     float* W;               // out: theta × n averaging weights (theta = 1 unless Bulyan)
     int* info;              // out: [0] = number of selection rounds, [1..] selected ids of round 0
     SelectArgs sel;
+    unsigned char owner[36];   // pairwise_multi_kernel: consumer warp that owns block pair p (host plan, gb_pairwise_plan)
 };
 
 // ------------------------------------------------------------------- sorting networks ---

@@ -394,7 +394,7 @@ __global__ void __launch_bounds__(kThreads) pairwise_kernel(const __grid_constan
 // against the 16 LDS.128 + 256 FP32 instructions of a 256-coordinate tile, and one lane issuing n one-kilobyte copies per
 // stage. This variant (4-row blocks, B <= 8 → at most 36 block pairs) instead
 //   * gives every warp up to QO off-diagonal and QD diagonal block pairs for the whole kernel (longest-processing-time
-//     assignment: 16 against 6 row pairs) and keeps all their sums in registers — one flush per kernel. The slots are typed
+//     assignment made on the host, plan_multi: 16 against 6 row pairs) and keeps all their sums in registers — one flush per kernel. The slots are typed
 //     so that the unrolled loop holds QO + QD copies of the block code, not 2·(QO + QD): measured at n = 23, ten copies ran
 //     at 0.75 ms and twelve at 0.89 ms — the loop has to stay inside the instruction cache;
 //   * pads each stage to 4·B rows whose phantom rows are zeroed once, so every block takes the predicate-free path;
@@ -409,7 +409,6 @@ __global__ void __launch_bounds__(kThreads, 1) pairwise_multi_kernel(const __gri
     extern __shared__ __align__(128) unsigned char smem_raw[];
     __shared__ TileRing ring;
     __shared__ unsigned int is_last;
-    __shared__ unsigned char owner[kMultiPairs];
     int const n = a.n;
     int const nn = n * n;
     float* slots = reinterpret_cast<float*>(smem_raw);
@@ -426,26 +425,6 @@ __global__ void __launch_bounds__(kThreads, 1) pairwise_multi_kernel(const __gri
     for (int i = threadIdx.x; i < kConsumerWarps * nn; i += blockDim.x) slots[i] = 0.0f;
     for (int s = 0; s < kStages; ++s)
         for (int i = threadIdx.x; i < (padded - n) * tile; i += blockDim.x) stages[s * stage_floats + static_cast<size_t>(n) * tile + i] = 0.0f;
-    if (threadIdx.x == 32) {
-        float load[kConsumerWarps];
-        int held_off[kConsumerWarps], held_diag[kConsumerWarps];
-        for (int w = 0; w < kConsumerWarps; ++w) { load[w] = 0.0f; held_off[w] = held_diag[w] = 0; }
-        for (int pass = 0; pass < 2; ++pass)          // the expensive (off-diagonal) pairs first
-            for (int p = 0; p < BP; ++p) {
-                int bi, bj;
-                block_pair_of(p, B, bi, bj);
-                bool const diag = bi == bj;
-                if (diag != (pass == 1)) continue;
-                int best = -1;
-                for (int w = 0; w < kConsumerWarps; ++w) {
-                    bool const room = diag ? held_diag[w] < QD : held_off[w] < QO;
-                    if (room && (best < 0 || load[w] < load[best])) best = w;
-                }
-                owner[p] = static_cast<unsigned char>(best);     // the host picks (QO, QD) so that a warp with room exists
-                load[best] += diag ? 0.5f * kG * (kG - 1) : 1.0f * kG * kG;
-                ++(diag ? held_diag[best] : held_off[best]);
-            }
-    }
     ring_init(ring);
 
     if (warp == 0) {
@@ -484,7 +463,7 @@ __global__ void __launch_bounds__(kThreads, 1) pairwise_multi_kernel(const __gri
         }
         int n_off = 0, n_diag = 0;
         for (int p = 0; p < BP; ++p)
-            if (owner[p] == cw) {
+            if (a.owner[p] == cw) {
                 int x, y;
                 block_pair_of(p, B, x, y);
                 if (x == y) {
@@ -560,6 +539,37 @@ int multi_tile(int n) {
 
 // Slot counts per block count B = ⌈n/4⌉ (B(B−1)/2 off-diagonal and B diagonal pairs on 8 warps):
 //   B = 4: 6 + 4 → (1, 2);  B = 5: 10 + 5 → (2, 1);  B = 6: 15 + 6 → (2, 1);  B = 7: 21 + 7 → (3, 1);  B = 8: 28 + 8 → (4, 1)
+// Longest-processing-time assignment of the block pairs to the 8 consumer warps under the slot limits (qo off-diagonal, qd
+// diagonal pairs per warp); off-diagonal pairs (16 row pairs) first, then the diagonal ones (6). false = some pair finds no warp.
+bool plan_multi(int n, int qo, int qd, unsigned char* owner) {
+    int const B = (n + 3) / 4;
+    float load[kConsumerWarps] = {};
+    int held_off[kConsumerWarps] = {}, held_diag[kConsumerWarps] = {};
+    for (int pass = 0; pass < 2; ++pass) {
+        int p = 0;
+        for (int bi = 0; bi < B; ++bi)
+            for (int bj = bi; bj < B; ++bj, ++p) {      // same enumeration as block_pair_of
+                bool const diag = bi == bj;
+                if (diag != (pass == 1)) continue;
+                int best = -1;
+                for (int w = 0; w < kConsumerWarps; ++w) {
+                    bool const room = diag ? held_diag[w] < qd : held_off[w] < qo;
+                    if (room && (best < 0 || load[w] < load[best])) best = w;
+                }
+                if (best < 0) return false;
+                owner[p] = static_cast<unsigned char>(best);
+                load[best] += diag ? 6.0f : 16.0f;
+                ++(diag ? held_diag[best] : held_off[best]);
+            }
+    }
+    return true;
+}
+void multi_slots(int n, int& qo, int& qd) {
+    int const B = (n + 3) / 4;
+    qo = B <= 4 ? 1 : B <= 6 ? 2 : B == 7 ? 3 : 4;
+    qd = B <= 4 ? 2 : 1;
+}
+
 using MultiKernel = void (*)(PairwiseArgs);
 // (two CTAs per SM with 256-coordinate tiles were measured too: no faster, 0.74 against 0.72 ms at n = 23)
 // GARFIELD_PW_PACKED=0: scalar FADD / FFMA everywhere (A/B measurements).
@@ -609,7 +619,12 @@ extern "C" GB_API int gb_pairwise_select(float const* const* rows, int n, int64_
     a.use_tma = rows_aligned(a.rows, n) ? 1 : 0;
     // 13..32 rows: register-resident sums. Measured at d = 23.5 M (general kernel -> this one): n = 13 0.61 -> 0.26 ms, 16 0.33 -> 0.26,
     // 20 1.09 -> 0.42, 23 1.58 -> 0.58, 24 0.86 -> 0.59, 28 2.61 -> 0.92, 32 5.79 -> 1.22.
-    bool const multi = n > 12 && n <= kMultiRows && multi_enabled();
+    bool multi = n > 12 && n <= kMultiRows && multi_enabled();
+    if (multi) {
+        int qo, qd;
+        multi_slots(n, qo, qd);
+        multi = plan_multi(n, qo, qd, a.owner);      // no feasible plan (cannot happen for 13..32 rows): general kernel
+    }
     // packed FP32 in the general kernel pays from 9 rows on (n = 10 0.256 -> 0.214 ms, 12 0.223 -> 0.207; n = 8 0.136 -> 0.142)
     bool const packed = n > 8 && packed_enabled();
     a.tile = multi ? multi_tile(n) : pick_tile(n);
@@ -636,6 +651,29 @@ extern "C" GB_API int gb_pairwise_select(float const* const* rows, int n, int64_
     return cuda_check(cudaGetLastError(), "pairwise launch");
 }
 
+
+// What gb_pairwise_select would launch for n rows (host-only; no device work): kind 0 = general kernel (4-row blocks, scalar),
+// 1 = general kernel with packed FP32, 2 = register-resident kernel. For kind 2, `slots` receives (off-diagonal, diagonal) pairs
+// per warp and `owner` the warp of each of the B(B+1)/2 block pairs (B = ⌈n/4⌉, pairs enumerated row-major over bi <= bj).
+extern "C" GB_API int gb_pairwise_plan(int n, int* kind, int* tile, int* slots, unsigned char* owner) {
+    using namespace gb;
+    if (n < 1 || n > kMaxRows || kind == nullptr || tile == nullptr) return cuda_fail("pairwise_plan: bad arguments");
+    bool multi = n > 12 && n <= kMultiRows && multi_enabled();
+    int qo = 0, qd = 0;
+    unsigned char local[kMultiPairs] = {};
+    if (multi) {
+        multi_slots(n, qo, qd);
+        multi = plan_multi(n, qo, qd, local);
+    }
+    *kind = multi ? 2 : (n > 8 && packed_enabled() ? 1 : 0);
+    *tile = multi ? multi_tile(n) : pick_tile(n);
+    if (slots != nullptr) { slots[0] = qo; slots[1] = qd; }
+    if (owner != nullptr && multi) {
+        int const B = (n + 3) / 4;
+        for (int p = 0; p < B * (B + 1) / 2; ++p) owner[p] = local[p];
+    }
+    return 0;
+}
 
 extern "C" GB_API int gb_pairwise_cta_limit(int max_ctas) {
     int const previous = gb::g_pairwise_cta_limit;

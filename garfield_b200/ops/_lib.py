@@ -40,6 +40,7 @@ def _declare(h):
     h.gb_gram_scratch_bytes.argtypes = [i32]
     h.gb_gram_select_tc.argtypes = [pp, i32, i64, i32, i32, i32, i32, i32, vp, i64, vp, vp, vp, vp]
     h.gb_pairwise_cta_limit.argtypes = [i32]
+    h.gb_pairwise_plan.argtypes = [i32, ctypes.POINTER(ctypes.c_int), ctypes.POINTER(ctypes.c_int), ctypes.POINTER(ctypes.c_int), ctypes.c_char_p]
     h.gb_select_only.argtypes = [vp, i32, i32, i32, i32, i32, i32, vp, vp, vp]
     h.gb_gemm_nt.argtypes = [vp, vp, vp, vp, i32, i32, i32, i64, i64, i64, i32, i32, vp]
     h.gb_conv_fprop_tc.argtypes = [vp, vp, vp, vp] + [i32] * 14 + [vp]

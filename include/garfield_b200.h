@@ -138,6 +138,8 @@ GB_API int gb_select_only(float* dist, int n, int mode, int f, int m, int neighb
 /* Cap the grid of this thread's next gb_pairwise_select launches at `max_ctas` CTAs (0 = fill the GPU); returns the previous cap.
  * For a distance pass that runs in the background of other kernels (distances of finished layers during the backward pass). */
 GB_API int gb_pairwise_cta_limit(int max_ctas);
+/* Host-only: which kernel, tile and block-pair assignment gb_pairwise_select uses for n rows (see gar_pairwise.cu). */
+GB_API int gb_pairwise_plan(int n, int* kind, int* tile, int* slots, unsigned char* owner);
 /* Tensor-core variant of gb_pairwise_select for 2 <= n <= 32 sixteen-byte-aligned rows: the Gram
  * matrix X·Xᵀ is accumulated with tcgen05.mma (kind::tf32) in TMEM from TMA-bulk-copied tiles, then
  * D_ij = G_ii + G_jj − 2·G_ij and the same in-kernel selection. TF32 operand precision (see
