@@ -425,7 +425,11 @@ extern "C" GB_API int gb_gemm_nt(void const* A, void const* B, float* C, float c
             return cuda_fail("gemm: cuTensorMapEncodeTiled failed (driver entry point unavailable or bad shape)");
         cudaError_t const e = dtype == 0 ? launch_gemm_pair<true>(ma, mb, C, bias, M, N, K, ldc, relu, st0)
                                          : launch_gemm_pair<false>(ma, mb, C, bias, M, N, K, ldc, relu, st0);
-        return cuda_check(e, "gemm pair launch");
+        if (e == cudaSuccess) return 0;
+        // a device that cannot co-schedule CTA pairs (partitioned GPU, cluster launch refused): the single-CTA kernel below
+        if (e != cudaErrorInvalidClusterSize && e != cudaErrorLaunchOutOfResources && e != cudaErrorInvalidConfiguration && e != cudaErrorNotSupported)
+            return cuda_check(e, "gemm pair launch");
+        (void)cudaGetLastError();
     }
     int const bn = N > 128 ? 256 : 128;
     if (!make_map(&ma, A, M, K, lda, eb, kBM) || !make_map(&mb, B, N, K, ldb, eb, bn))
