@@ -18,6 +18,7 @@
 
 #include "garfield_b200.h"
 #include "launch.cuh"
+#include "pdl.cuh"
 
 namespace gb {
 namespace {
@@ -36,6 +37,7 @@ inline unsigned grid_for(long long total, int block = 256) {
 constexpr int kIm2colPixels = 32;
 __global__ void __launch_bounds__(256) im2col_pad_kernel(const float* __restrict__ x, float* __restrict__ cols, int H, int W, int C, int pitch, int KH,
                                                           int KW, int sh, int sw, int ph, int pw, int Ho, int Wo, int kpad, long long pixels) {
+    pdl_enter();
     __shared__ long long base[kIm2colPixels];     // offset of pixel (n, 0, 0) ... in floats: n·H·W·pitch
     __shared__ int hb[kIm2colPixels], wb[kIm2colPixels];
     long long const pix0 = static_cast<long long>(blockIdx.x) * kIm2colPixels;
@@ -67,6 +69,7 @@ __global__ void __launch_bounds__(256) im2col_pad_kernel(const float* __restrict
 
 __global__ void __launch_bounds__(256) pad_rows_kernel(const float* __restrict__ src, float* __restrict__ dst, int k, long long ld, int kpad,
                                                         long long total) {
+    pdl_enter();
     for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < total; i += static_cast<long long>(gridDim.x) * blockDim.x) {
         int const c = static_cast<int>(i % kpad);
         long long const r = i / kpad;
@@ -77,6 +80,7 @@ __global__ void __launch_bounds__(256) pad_rows_kernel(const float* __restrict__
 // dx[n, h, w, c] = Σ_{(kh, kw): (h + ph − kh) % sh == 0, …} dcols[(n, ho, wo)][(kh, kw, c)]
 __global__ void __launch_bounds__(256) col2im_kernel(const float* __restrict__ dcols, float* __restrict__ dx, int H, int W, int C, int pitch, int KH,
                                                       int KW, int sh, int sw, int ph, int pw, int Ho, int Wo, int kpad, long long total) {
+    pdl_enter();
     for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < total; i += static_cast<long long>(gridDim.x) * blockDim.x) {
         int const c = static_cast<int>(i % C);
         long long r = i / C;
@@ -103,6 +107,7 @@ __global__ void __launch_bounds__(256) col2im_kernel(const float* __restrict__ d
 
 __global__ void __launch_bounds__(256) upsample_zero_kernel(const float4* __restrict__ in, float4* __restrict__ out, int Ho, int Wo, int C4, int sh,
                                                              int sw, int H, int W, long long total) {
+    pdl_enter();
     for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < total; i += static_cast<long long>(gridDim.x) * blockDim.x) {
         int const c = static_cast<int>(i % C4);
         long long r = i / C4;
@@ -117,6 +122,7 @@ __global__ void __launch_bounds__(256) upsample_zero_kernel(const float4* __rest
 
 __global__ void __launch_bounds__(256) maxpool_fwd_kernel(const float4* __restrict__ x, float4* __restrict__ y, uchar4* __restrict__ arg, int H, int W,
                                                            int C4, int K, int s, int p, int Ho, int Wo, long long total) {
+    pdl_enter();
     for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < total; i += static_cast<long long>(gridDim.x) * blockDim.x) {
         int const c = static_cast<int>(i % C4);
         long long r = i / C4;
@@ -147,6 +153,7 @@ __global__ void __launch_bounds__(256) maxpool_fwd_kernel(const float4* __restri
 
 __global__ void __launch_bounds__(256) maxpool_bwd_kernel(const float4* __restrict__ dy, const uchar4* __restrict__ arg, float4* __restrict__ dx, int H,
                                                            int W, int C4, int K, int s, int p, int Ho, int Wo, long long total) {
+    pdl_enter();
     for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < total; i += static_cast<long long>(gridDim.x) * blockDim.x) {
         int const c = static_cast<int>(i % C4);
         long long r = i / C4;
@@ -183,6 +190,7 @@ __global__ void __launch_bounds__(256) maxpool_bwd_kernel(const float4* __restri
 __global__ void __launch_bounds__(256) softmax_ce_grouped_kernel(const float* __restrict__ logits, int ld, const long long* __restrict__ target,
                                                                   float* __restrict__ row_loss, float* __restrict__ dlogits, int ldd, int rows,
                                                                   int classes, int rows_per_group) {
+    pdl_enter();
     int const warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
     if (warp >= rows) return;
     const float* in = logits + static_cast<long long>(warp) * ld;
@@ -202,6 +210,7 @@ __global__ void __launch_bounds__(256) softmax_ce_grouped_kernel(const float* __
 // out[g][c] = scale · Σ_{rows of group g} in[row][c]; one block per (group, 32-column slab), fixed-order reduction.
 __global__ void __launch_bounds__(256) colsum_grouped_kernel(const float* __restrict__ in, long long ld, float* __restrict__ out, int rows_per_group,
                                                               int cols, float scale) {
+    pdl_enter();
     __shared__ float part[8][33];
     int const g = blockIdx.y, c = blockIdx.x * 32 + (threadIdx.x & 31), sub = threadIdx.x >> 5;
     float acc = 0.f;
@@ -217,7 +226,22 @@ __global__ void __launch_bounds__(256) colsum_grouped_kernel(const float* __rest
 }
 
 // ReLU on a flat tensor (forward) and its gradient mask from the OUTPUT (backward): y > 0 ⇔ x > 0.
+// out = a + b over `total` floats (float4 body, scalar tail): the sum of the two gradients that meet where a residual block's
+// input forks — autograd's own accumulation is a library kernel that takes no part in the programmatic launch chain.
+__global__ void __launch_bounds__(256) add_kernel(const float* __restrict__ a, const float* __restrict__ b, float* __restrict__ out, long long total,
+                                                  int vec) {
+    pdl_enter();
+    long long const step = static_cast<long long>(gridDim.x) * blockDim.x;
+    long long const quads = vec ? total / 4 : 0;
+    for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < quads; i += step) {
+        float4 const x = reinterpret_cast<const float4*>(a)[i], y = reinterpret_cast<const float4*>(b)[i];
+        reinterpret_cast<float4*>(out)[i] = make_float4(x.x + y.x, x.y + y.y, x.z + y.z, x.w + y.w);
+    }
+    for (long long i = quads * 4 + static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < total; i += step) out[i] = a[i] + b[i];
+}
+
 __global__ void __launch_bounds__(256) relu_fwd_kernel(const float* __restrict__ x, float* __restrict__ y, long long total) {
+    pdl_enter();
     long long const n4 = total / 4;
     for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < n4; i += static_cast<long long>(gridDim.x) * blockDim.x) {
         float4 v = reinterpret_cast<const float4*>(x)[i];
@@ -228,6 +252,7 @@ __global__ void __launch_bounds__(256) relu_fwd_kernel(const float* __restrict__
         y[i] = fmaxf(x[i], 0.f);
 }
 __global__ void __launch_bounds__(256) relu_bwd_kernel(const float* __restrict__ dy, const float* __restrict__ y, float* __restrict__ dx, long long total) {
+    pdl_enter();
     for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < total; i += static_cast<long long>(gridDim.x) * blockDim.x)
         dx[i] = y[i] > 0.f ? dy[i] : 0.f;
 }
@@ -235,6 +260,7 @@ __global__ void __launch_bounds__(256) relu_bwd_kernel(const float* __restrict__
 // Max pooling for any channel count (scalar lanes): the float4 kernels above need C % 4 == 0.
 __global__ void __launch_bounds__(256) maxpool_fwd_scalar_kernel(const float* __restrict__ x, float* __restrict__ y, unsigned char* __restrict__ arg, int H,
                                                                   int W, int C, int K, int s, int p, int Ho, int Wo, long long total) {
+    pdl_enter();
     for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < total; i += static_cast<long long>(gridDim.x) * blockDim.x) {
         int const c = static_cast<int>(i % C);
         long long r = i / C;
@@ -259,6 +285,7 @@ __global__ void __launch_bounds__(256) maxpool_fwd_scalar_kernel(const float* __
 }
 __global__ void __launch_bounds__(256) maxpool_bwd_scalar_kernel(const float* __restrict__ dy, const unsigned char* __restrict__ arg, float* __restrict__ dx,
                                                                   int H, int W, int C, int K, int s, int p, int Ho, int Wo, long long total) {
+    pdl_enter();
     for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < total; i += static_cast<long long>(gridDim.x) * blockDim.x) {
         int const c = static_cast<int>(i % C);
         long long r = i / C;
@@ -285,6 +312,7 @@ __global__ void __launch_bounds__(256) maxpool_bwd_scalar_kernel(const float* __
 }
 
 __global__ void __launch_bounds__(256) avgpool_fwd_kernel(const float* __restrict__ x, float* __restrict__ y, int hw, int C, long long total) {
+    pdl_enter();
     for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < total; i += static_cast<long long>(gridDim.x) * blockDim.x) {
         int const c = static_cast<int>(i % C);
         long long const n = i / C;
@@ -294,6 +322,7 @@ __global__ void __launch_bounds__(256) avgpool_fwd_kernel(const float* __restric
     }
 }
 __global__ void __launch_bounds__(256) avgpool_bwd_kernel(const float* __restrict__ dy, float* __restrict__ dx, int hw, int C, long long total) {
+    pdl_enter();
     for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < total; i += static_cast<long long>(gridDim.x) * blockDim.x) {
         int const c = static_cast<int>(i % C);
         long long const n = i / C / hw;
@@ -315,7 +344,7 @@ extern "C" GB_API int gb_im2col_pad_nhwc(float const* x, float* cols, int N, int
     long long const pixels = static_cast<long long>(N) * Ho * Wo;
     long long const blocks = (pixels + kIm2colPixels - 1) / kIm2colPixels;
     if (blocks > 2147483647LL) return cuda_fail("im2col_pad_nhwc: too many output pixels");
-    im2col_pad_kernel<<<static_cast<unsigned>(blocks), 256, 0, static_cast<cudaStream_t>(stream)>>>(x, cols, H, W, C, pitch, KH, KW, stride_h, stride_w,
+    launch_pdl(im2col_pad_kernel, dim3(static_cast<unsigned>(blocks)), dim3(256), static_cast<cudaStream_t>(stream), x, cols, H, W, C, pitch, KH, KW, stride_h, stride_w,
                                                                                                    pad_h, pad_w, Ho, Wo, kpad, pixels);
     return cuda_check(cudaGetLastError(), "im2col_pad_nhwc");
 }
@@ -323,7 +352,7 @@ extern "C" GB_API int gb_im2col_pad_nhwc(float const* x, float* cols, int N, int
 extern "C" GB_API int gb_pad_rows(float const* src, float* dst, int64_t rows, int k, int64_t ld, int kpad, void* stream) {
     if (rows < 1 || k < 1 || kpad < k || ld < k) return cuda_fail("pad_rows: bad shape");
     long long const total = rows * kpad;
-    pad_rows_kernel<<<grid_for(total), 256, 0, static_cast<cudaStream_t>(stream)>>>(src, dst, k, ld, kpad, total);
+    launch_pdl(pad_rows_kernel, dim3(grid_for(total)), dim3(256), static_cast<cudaStream_t>(stream), src, dst, k, ld, kpad, total);
     return cuda_check(cudaGetLastError(), "pad_rows");
 }
 
@@ -333,7 +362,7 @@ extern "C" GB_API int gb_col2im_nhwc(float const* dcols, float* dx, int N, int H
         return cuda_fail("col2im_nhwc: bad geometry");
     int const Ho = (H + 2 * pad_h - KH) / stride_h + 1, Wo = (W + 2 * pad_w - KW) / stride_w + 1;
     long long const total = static_cast<long long>(N) * H * W * C;
-    col2im_kernel<<<grid_for(total), 256, 0, static_cast<cudaStream_t>(stream)>>>(dcols, dx, H, W, C, pitch, KH, KW, stride_h, stride_w, pad_h, pad_w, Ho,
+    launch_pdl(col2im_kernel, dim3(grid_for(total)), dim3(256), static_cast<cudaStream_t>(stream), dcols, dx, H, W, C, pitch, KH, KW, stride_h, stride_w, pad_h, pad_w, Ho,
                                                                                   Wo, kpad, total);
     return cuda_check(cudaGetLastError(), "col2im_nhwc");
 }
@@ -342,7 +371,7 @@ extern "C" GB_API int gb_upsample_zero_nhwc(float const* in, float* out, int N, 
                                             void* stream) {
     if (N < 1 || Ho < 1 || Wo < 1 || C < 4 || C % 4 || stride_h < 1 || stride_w < 1 || H < 1 || W < 1) return cuda_fail("upsample_zero_nhwc: bad geometry");
     long long const total = static_cast<long long>(N) * H * W * (C / 4);
-    upsample_zero_kernel<<<grid_for(total), 256, 0, static_cast<cudaStream_t>(stream)>>>(reinterpret_cast<const float4*>(in), reinterpret_cast<float4*>(out),
+    launch_pdl(upsample_zero_kernel, dim3(grid_for(total)), dim3(256), static_cast<cudaStream_t>(stream), reinterpret_cast<const float4*>(in), reinterpret_cast<float4*>(out),
                                                                                          Ho, Wo, C / 4, stride_h, stride_w, H, W, total);
     return cuda_check(cudaGetLastError(), "upsample_zero_nhwc");
 }
@@ -353,11 +382,11 @@ extern "C" GB_API int gb_maxpool_nhwc_forward(float const* x, float* y, unsigned
     int const Ho = (H + 2 * pad - k) / stride + 1, Wo = (W + 2 * pad - k) / stride + 1;
     if (C % 4) {
         long long const all = static_cast<long long>(N) * Ho * Wo * C;
-        maxpool_fwd_scalar_kernel<<<grid_for(all), 256, 0, static_cast<cudaStream_t>(stream)>>>(x, y, arg, H, W, C, k, stride, pad, Ho, Wo, all);
+        launch_pdl(maxpool_fwd_scalar_kernel, dim3(grid_for(all)), dim3(256), static_cast<cudaStream_t>(stream), x, y, arg, H, W, C, k, stride, pad, Ho, Wo, all);
         return cuda_check(cudaGetLastError(), "maxpool_nhwc_forward");
     }
     long long const total = static_cast<long long>(N) * Ho * Wo * (C / 4);
-    maxpool_fwd_kernel<<<grid_for(total), 256, 0, static_cast<cudaStream_t>(stream)>>>(reinterpret_cast<const float4*>(x), reinterpret_cast<float4*>(y),
+    launch_pdl(maxpool_fwd_kernel, dim3(grid_for(total)), dim3(256), static_cast<cudaStream_t>(stream), reinterpret_cast<const float4*>(x), reinterpret_cast<float4*>(y),
                                                                                        reinterpret_cast<uchar4*>(arg), H, W, C / 4, k, stride, pad, Ho, Wo,
                                                                                        total);
     return cuda_check(cudaGetLastError(), "maxpool_nhwc_forward");
@@ -369,11 +398,11 @@ extern "C" GB_API int gb_maxpool_nhwc_backward(float const* dy, unsigned char co
     int const Ho = (H + 2 * pad - k) / stride + 1, Wo = (W + 2 * pad - k) / stride + 1;
     if (C % 4) {
         long long const all = static_cast<long long>(N) * H * W * C;
-        maxpool_bwd_scalar_kernel<<<grid_for(all), 256, 0, static_cast<cudaStream_t>(stream)>>>(dy, arg, dx, H, W, C, k, stride, pad, Ho, Wo, all);
+        launch_pdl(maxpool_bwd_scalar_kernel, dim3(grid_for(all)), dim3(256), static_cast<cudaStream_t>(stream), dy, arg, dx, H, W, C, k, stride, pad, Ho, Wo, all);
         return cuda_check(cudaGetLastError(), "maxpool_nhwc_backward");
     }
     long long const total = static_cast<long long>(N) * H * W * (C / 4);
-    maxpool_bwd_kernel<<<grid_for(total), 256, 0, static_cast<cudaStream_t>(stream)>>>(reinterpret_cast<const float4*>(dy),
+    launch_pdl(maxpool_bwd_kernel, dim3(grid_for(total)), dim3(256), static_cast<cudaStream_t>(stream), reinterpret_cast<const float4*>(dy),
                                                                                        reinterpret_cast<const uchar4*>(arg), reinterpret_cast<float4*>(dx),
                                                                                        H, W, C / 4, k, stride, pad, Ho, Wo, total);
     return cuda_check(cudaGetLastError(), "maxpool_nhwc_backward");
@@ -383,7 +412,7 @@ extern "C" GB_API int gb_softmax_ce_grouped(float const* logits, int ld, int64_t
                                             int classes, int rows_per_group, void* stream) {
     if (rows < 1 || classes < 1 || ld < classes || ldd < classes || rows_per_group < 1) return cuda_fail("softmax_ce_grouped: bad shape");
     int const blocks = (rows * 32 + 255) / 256;
-    softmax_ce_grouped_kernel<<<blocks, 256, 0, static_cast<cudaStream_t>(stream)>>>(logits, ld, reinterpret_cast<const long long*>(target), row_loss,
+    launch_pdl(softmax_ce_grouped_kernel, dim3(blocks), dim3(256), static_cast<cudaStream_t>(stream), logits, ld, reinterpret_cast<const long long*>(target), row_loss,
                                                                                      dlogits, ldd, rows, classes, rows_per_group);
     return cuda_check(cudaGetLastError(), "softmax_ce_grouped");
 }
@@ -391,31 +420,39 @@ extern "C" GB_API int gb_softmax_ce_grouped(float const* logits, int ld, int64_t
 extern "C" GB_API int gb_colsum_grouped(float const* in, int64_t ld, float* out, int groups, int rows_per_group, int cols, float scale, void* stream) {
     if (groups < 1 || rows_per_group < 1 || cols < 1 || ld < cols) return cuda_fail("colsum_grouped: bad shape");
     dim3 const grid(static_cast<unsigned>((cols + 31) / 32), static_cast<unsigned>(groups));
-    colsum_grouped_kernel<<<grid, 256, 0, static_cast<cudaStream_t>(stream)>>>(in, ld, out, rows_per_group, cols, scale);
+    launch_pdl(colsum_grouped_kernel, dim3(grid), dim3(256), static_cast<cudaStream_t>(stream), in, ld, out, rows_per_group, cols, scale);
     return cuda_check(cudaGetLastError(), "colsum_grouped");
+}
+
+extern "C" GB_API int gb_add(float const* a, float const* b, float* out, int64_t total, void* stream) {
+    using namespace gb;
+    if (total < 1) return 0;
+    int const vec = ((reinterpret_cast<uintptr_t>(a) | reinterpret_cast<uintptr_t>(b) | reinterpret_cast<uintptr_t>(out)) & 15u) == 0 ? 1 : 0;
+    launch_pdl(add_kernel, dim3(grid_for(total / 4 + 1)), dim3(256), static_cast<cudaStream_t>(stream), a, b, out, static_cast<long long>(total), vec);
+    return cuda_check(cudaGetLastError(), "add");
 }
 
 extern "C" GB_API int gb_relu_forward(float const* x, float* y, int64_t total, void* stream) {
     if (total < 1) return cuda_fail("relu: empty tensor");
     if ((reinterpret_cast<uintptr_t>(x) | reinterpret_cast<uintptr_t>(y)) & 15u) return cuda_fail("relu: tensors must be 16-byte aligned");
-    relu_fwd_kernel<<<grid_for(total / 4 + 1), 256, 0, static_cast<cudaStream_t>(stream)>>>(x, y, total);
+    launch_pdl(relu_fwd_kernel, dim3(grid_for(total / 4 + 1)), dim3(256), static_cast<cudaStream_t>(stream), x, y, total);
     return cuda_check(cudaGetLastError(), "relu_forward");
 }
 extern "C" GB_API int gb_relu_backward(float const* dy, float const* y, float* dx, int64_t total, void* stream) {
     if (total < 1) return cuda_fail("relu: empty tensor");
-    relu_bwd_kernel<<<grid_for(total), 256, 0, static_cast<cudaStream_t>(stream)>>>(dy, y, dx, total);
+    launch_pdl(relu_bwd_kernel, dim3(grid_for(total)), dim3(256), static_cast<cudaStream_t>(stream), dy, y, dx, total);
     return cuda_check(cudaGetLastError(), "relu_backward");
 }
 
 extern "C" GB_API int gb_avgpool_nhwc_forward(float const* x, float* y, int64_t n, int hw, int C, void* stream) {
     if (n < 1 || hw < 1 || C < 1) return cuda_fail("avgpool_nhwc: bad shape");
     long long const total = n * C;
-    avgpool_fwd_kernel<<<grid_for(total), 256, 0, static_cast<cudaStream_t>(stream)>>>(x, y, hw, C, total);
+    launch_pdl(avgpool_fwd_kernel, dim3(grid_for(total)), dim3(256), static_cast<cudaStream_t>(stream), x, y, hw, C, total);
     return cuda_check(cudaGetLastError(), "avgpool_nhwc_forward");
 }
 extern "C" GB_API int gb_avgpool_nhwc_backward(float const* dy, float* dx, int64_t n, int hw, int C, void* stream) {
     if (n < 1 || hw < 1 || C < 1) return cuda_fail("avgpool_nhwc: bad shape");
     long long const total = n * hw * C;
-    avgpool_bwd_kernel<<<grid_for(total), 256, 0, static_cast<cudaStream_t>(stream)>>>(dy, dx, hw, C, total);
+    launch_pdl(avgpool_bwd_kernel, dim3(grid_for(total)), dim3(256), static_cast<cudaStream_t>(stream), dy, dx, hw, C, total);
     return cuda_check(cudaGetLastError(), "avgpool_nhwc_backward");
 }

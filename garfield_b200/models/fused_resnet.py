@@ -27,6 +27,10 @@ def _first_conv(block, x):
     fork = getattr(block.conv1, "_gb_fork", None)
     if block.downsample is None and fork is not None and FORK_SKIP[0]:
         return fork(x)
+    split = getattr(block.conv1, "_gb_split", None)      # worker-fusion layer on its own kernels: the two gradients are summed by them
+    if split is not None and x.requires_grad:
+        a, b = split(x)
+        return block.conv1(a), b
     return block.conv1(x), x
 
 
@@ -35,7 +39,7 @@ def _bottleneck_forward(self, x):
     out = fused_batch_norm(y1, self.bn1, relu=True)
     out = fused_batch_norm(self.conv2(out), self.bn2, relu=True)
     if self.downsample is not None:
-        identity = fused_batch_norm(self.downsample[0](x), self.downsample[1], relu=False)
+        identity = fused_batch_norm(self.downsample[0](identity), self.downsample[1], relu=False)   # `identity` is x (or its fork view)
     return fused_batch_norm(self.conv3(out), self.bn3, residual=identity, relu=True)
 
 
@@ -43,7 +47,7 @@ def _basic_forward(self, x):
     y1, identity = _first_conv(self, x)
     out = fused_batch_norm(y1, self.bn1, relu=True)
     if self.downsample is not None:
-        identity = fused_batch_norm(self.downsample[0](x), self.downsample[1], relu=False)
+        identity = fused_batch_norm(self.downsample[0](identity), self.downsample[1], relu=False)   # `identity` is x (or its fork view)
     return fused_batch_norm(self.conv2(out), self.bn2, residual=identity, relu=True)
 
 

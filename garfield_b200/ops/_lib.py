@@ -56,6 +56,7 @@ def _declare(h):
     h.gb_colsum_grouped.argtypes = [vp, i64, vp, i32, i32, i32, f32, vp]
     h.gb_relu_forward.argtypes = [vp, vp, i64, vp]
     h.gb_relu_backward.argtypes = [vp, vp, vp, i64, vp]
+    h.gb_add.argtypes = [vp, vp, vp, i64, vp]
     h.gb_avgpool_nhwc_forward.argtypes = [vp, vp, i64, i32, i32, vp]
     h.gb_avgpool_nhwc_backward.argtypes = [vp, vp, i64, i32, i32, vp]
     h.gb_conv2d_forward.argtypes = [vp, vp, vp, vp] + [i32] * 10 + [vp]

@@ -446,6 +446,23 @@ class _TcConv(torch.autograd.Function):
         return gx, None, None, None, None, None, None, None
 
 
+class _TcSplit(torch.autograd.Function):
+    """The point where a residual block's input forks (first convolution / identity): two views forward; backward sums the two
+    gradients with our own kernel, which takes part in the programmatic launch chain (autograd's accumulation does not)."""
+
+    @staticmethod
+    def forward(ctx, x):
+        return x.view_as(x), x.view_as(x)
+
+    @staticmethod
+    def backward(ctx, ga, gb):
+        if ga is None or gb is None:
+            return ga if gb is None else gb
+        same = ga.shape == gb.shape and ga.stride() == gb.stride() and ga.dtype == gb.dtype == torch.float32 and ga.is_cuda
+        dense = same and (ga.is_contiguous() or (ga.dim() == 4 and ga.is_contiguous(memory_format=torch.channels_last)))
+        return convops.add(ga, gb) if dense else ga + gb
+
+
 class _TcLinear(torch.autograd.Function):
     """Linear layer of the fused pass as a 1×1-geometry GEMM on the same kernels."""
 
@@ -584,6 +601,8 @@ class GroupedWorkers:
                 fwd = self._conv_forward(index[id(m.weight)], None if m.bias is None else index[id(m.bias)], m)
                 m.forward = types.MethodType(fwd, m)
                 m._gb_fork = fwd.fork
+                if OWN_KERNELS[0] and device.type == "cuda" and os.environ.get("GARFIELD_OWN_ADD", "0") == "1":   # opt-in: no gain measured
+                    m._gb_split = _TcSplit.apply
             elif isinstance(m, torch.nn.Linear):
                 m.forward = types.MethodType(self._linear_forward(index[id(m.weight)], None if m.bias is None else index[id(m.bias)]), m)
             elif isinstance(m, self._BATCHNORM):

@@ -208,6 +208,8 @@ GB_API int gb_softmax_ce_grouped(float const* logits, int ld, int64_t const* tar
 GB_API int gb_colsum_grouped(float const* in, int64_t ld, float* out, int groups, int rows_per_group, int cols, float scale, void* stream);
 GB_API int gb_relu_forward(float const* x, float* y, int64_t total, void* stream);
 GB_API int gb_relu_backward(float const* dy, float const* y, float* dx, int64_t total, void* stream);
+/* out = a + b (dense float arrays of `total` elements; out may alias a or b). */
+GB_API int gb_add(float const* a, float const* b, float* out, int64_t total, void* stream);
 GB_API int gb_avgpool_nhwc_forward(float const* x, float* y, int64_t n, int hw, int C, void* stream);
 GB_API int gb_avgpool_nhwc_backward(float const* dy, float* dx, int64_t n, int hw, int C, void* stream);
 
