@@ -156,28 +156,29 @@ __device__ __forceinline__ float reduce_column(float (&v)[NP], int cnt, int rank
                 float sum = 0.0f;
 #pragma unroll
                 for (int i = 0; i < NP; ++i) sum += (i < rank) ? v[i] : 0.0f;
-                return has_nan ? NAN : sum / static_cast<float>(rank);
-            }
-            float key[NP], ordered[NP];
+                result = has_nan ? NAN : sum / static_cast<float>(rank);
+            } else {
+                float key[NP], ordered[NP];
 #pragma unroll
-            for (int i = 0; i < NP; ++i) ordered[i] = key[i] = (i < cnt) ? fabsf(v[i] - med) : INFINITY;
-            merge_bitonic<NP>(ordered);
-            float const radius = pick_reg<NP>(ordered, rank - 1);
-            float sum = 0.0f;
-            int missing = rank;
+                for (int i = 0; i < NP; ++i) ordered[i] = key[i] = (i < cnt) ? fabsf(v[i] - med) : INFINITY;
+                merge_bitonic<NP>(ordered);
+                float const radius = pick_reg<NP>(ordered, rank - 1);
+                float sum = 0.0f;
+                int missing = rank;
 #pragma unroll
-            for (int i = 0; i < NP; ++i) {
-                bool const inside = key[i] < radius;
-                sum += inside ? v[i] : 0.0f;
-                missing -= inside ? 1 : 0;
-            }
+                for (int i = 0; i < NP; ++i) {
+                    bool const inside = key[i] < radius;
+                    sum += inside ? v[i] : 0.0f;
+                    missing -= inside ? 1 : 0;
+                }
 #pragma unroll
-            for (int i = 0; i < NP; ++i) {
-                bool const edge = key[i] == radius && missing > 0;
-                sum += edge ? v[i] : 0.0f;
-                missing -= edge ? 1 : 0;
+                for (int i = 0; i < NP; ++i) {
+                    bool const edge = key[i] == radius && missing > 0;
+                    sum += edge ? v[i] : 0.0f;
+                    missing -= edge ? 1 : 0;
+                }
+                result = has_nan ? NAN : sum / static_cast<float>(rank);
             }
-            result = has_nan ? NAN : sum / static_cast<float>(rank);
         }
         return result;
     }
