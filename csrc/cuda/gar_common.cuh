@@ -55,7 +55,6 @@ struct CoordArgs {
     int theta;        // > 0: values fed to the rule are y = W·x  (W is theta × n, row-major)
     int tile;         // coordinates per ring stage
     int use_tma;      // 0: rows are not 16-byte aligned → direct global loads only
-    int warp_producer;  // 1: lane i of the producer warp issues the copies of rows i, i + 32 (0: one elected lane issues all)
     float p;          // condense probability
     unsigned long long seed;
     long long d;
@@ -305,31 +304,6 @@ __device__ __forceinline__ void ring_produce(TileRing& ring, float* stage_base, 
         float* dst = stage_base + s * stage_floats;
         for (int i = 0; i < n; ++i)
             if (want(i)) ptx::bulk_g2s(dst + static_cast<size_t>(i) * tile, rows.p[i] + t * tile, row_bytes, &ring.full[s]);
-    }
-}
-
-// Same, called by ALL lanes of the producer warp: lane i issues the copies of rows i and i + 32, so a stage of n rows costs one
-// copy's issue time instead of n.
-template <class Want>
-__device__ __forceinline__ void ring_produce_warp(TileRing& ring, float* stage_base, RowTable const& rows, int n, int tile, long long full_tiles,
-                                                  Want want) {
-    int const lane = threadIdx.x & 31;
-    size_t const stage_floats = static_cast<size_t>(n) * tile;
-    uint32_t const row_bytes = static_cast<uint32_t>(tile) * 4u;
-    int needed = 0;
-    for (int i = 0; i < n; ++i) needed += want(i) ? 1 : 0;
-    float const* const row0 = (lane < n && want(lane)) ? rows.p[lane] : nullptr;
-    float const* const row1 = (lane + 32 < n && want(lane + 32)) ? rows.p[lane + 32] : nullptr;
-    long long it = 0;
-    for (long long t = blockIdx.x; t < full_tiles; t += gridDim.x, ++it) {
-        int const s = static_cast<int>(it % kStages);
-        uint32_t const phase = static_cast<uint32_t>((it / kStages) & 1);
-        ptx::mbar_wait(&ring.empty[s], phase ^ 1u);
-        if (lane == 0) ptx::mbar_arrive_expect_tx(&ring.full[s], row_bytes * static_cast<uint32_t>(needed));
-        __syncwarp();
-        float* dst = stage_base + s * stage_floats;
-        if (row0 != nullptr) ptx::bulk_g2s(dst + static_cast<size_t>(lane) * tile, row0 + t * tile, row_bytes, &ring.full[s]);
-        if (row1 != nullptr) ptx::bulk_g2s(dst + static_cast<size_t>(lane + 32) * tile, row1 + t * tile, row_bytes, &ring.full[s]);
     }
 }
 

@@ -302,11 +302,9 @@ __global__ void __launch_bounds__(kThreads) coordwise_kernel(const __grid_consta
     }
 
     if (warp == 0) {
-        auto const want = [&](int i) { return ((used_mask >> i) & 1ull) != 0ull; };
-        if (full_tiles > 0) {
-            if (a.warp_producer) ring_produce_warp(ring, stages, a.rows, a.n, tile, full_tiles, want);
-            else if (ptx::elect_one()) ring_produce(ring, stages, a.rows, a.n, tile, full_tiles, want);
-        }
+        // (one copy per lane of the producer warp instead of one elected lane issuing all n was measured: no difference)
+        if (full_tiles > 0 && ptx::elect_one())
+            ring_produce(ring, stages, a.rows, a.n, tile, full_tiles, [&](int i) { return ((used_mask >> i) & 1ull) != 0ull; });
     } else {
         int const ctid = threadIdx.x - 32;
         constexpr int kConsumers = 32 * kConsumerWarps;
