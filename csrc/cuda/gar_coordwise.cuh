@@ -58,13 +58,21 @@ __device__ __forceinline__ void vec_store(float* p, float const (&src)[V]) {
     else *p = src[0];
 }
 
-// SGD step (torch.optim.SGD semantics) + publication, on V consecutive coordinates.
+// Parameter and momentum of V consecutive coordinates — what apply_update reads. Split off so that the streaming loop can issue
+// these global loads one tile AHEAD: issued inside apply_update they start only after the tile's rows have been reduced, and every
+// warp then sits out a full DRAM latency per tile (the rows come through the TMA ring; these two streams did not).
 template <int V>
-__device__ __forceinline__ void apply_update(FusedUpdate const& u, long long x, float (&g)[V], float* out) {
+__device__ __forceinline__ void load_state(FusedUpdate const& u, long long x, float (&p)[V], float (&m)[V]) {
+    if (u.mode == 0) return;
+    vec_load<V>(p, u.param + x);
+    if (u.momentum != 0.0f && !u.first_step) vec_load<V>(m, u.mom + x);
+}
+
+// SGD step (torch.optim.SGD semantics) + publication, on V consecutive coordinates; p / m = load_state of the same coordinates.
+template <int V>
+__device__ __forceinline__ void apply_update(FusedUpdate const& u, long long x, float (&g)[V], float* out, float (&p)[V], float const (&m)[V]) {
     if (out != nullptr) vec_store<V>(out + x, g);
     if (u.mode == 0) return;
-    float p[V];
-    vec_load<V>(p, u.param + x);
 #pragma unroll
     for (int e = 0; e < V; ++e) g[e] = fmaf(u.weight_decay, p[e], g[e]);
     if (u.momentum != 0.0f) {
@@ -73,9 +81,8 @@ __device__ __forceinline__ void apply_update(FusedUpdate const& u, long long x, 
 #pragma unroll
             for (int e = 0; e < V; ++e) buf[e] = g[e];
         } else {
-            vec_load<V>(buf, u.mom + x);
 #pragma unroll
-            for (int e = 0; e < V; ++e) buf[e] = fmaf(u.momentum, buf[e], (1.0f - u.dampening) * g[e]);
+            for (int e = 0; e < V; ++e) buf[e] = fmaf(u.momentum, m[e], (1.0f - u.dampening) * g[e]);
         }
         vec_store<V>(u.mom + x, buf);
 #pragma unroll
@@ -93,6 +100,14 @@ __device__ __forceinline__ void apply_update(FusedUpdate const& u, long long x, 
 #pragma unroll
     for (int k = 0; k < kMaxMirrors; ++k)
         if (k < u.n_mirrors) vec_store<V>(u.mirror[k] + x, p);
+}
+template <int V>
+__device__ __forceinline__ void apply_update(FusedUpdate const& u, long long x, float (&g)[V], float* out) {
+    float p[V], m[V];
+#pragma unroll
+    for (int e = 0; e < V; ++e) p[e] = m[e] = 0.0f;
+    load_state<V>(u, x, p, m);
+    apply_update<V>(u, x, g, out, p, m);
 }
 
 // Reduce the `cnt` values of one coordinate held in v[0..NP). Entries at index >= cnt must hold
@@ -310,12 +325,37 @@ __global__ void __launch_bounds__(kThreads) coordwise_kernel(const __grid_consta
         constexpr int kConsumers = 32 * kConsumerWarps;
         size_t const stage_floats = static_cast<size_t>(a.n) * tile;
         long long it = 0;
+        // every thread visits at most one column group per tile (the usual case: 1024-coordinate tiles, 4 coordinates per thread):
+        // its parameter / momentum values are fetched one tile ahead
+        bool const ahead = tile <= kConsumers * V && a.upd.mode != 0;
+        bool const mine = ctid * V < tile;
+        float p_next[V], m_next[V];
+#pragma unroll
+        for (int e = 0; e < V; ++e) p_next[e] = m_next[e] = 0.0f;
+        if (ahead && mine && static_cast<long long>(blockIdx.x) < full_tiles)
+            load_state<V>(a.upd, static_cast<long long>(blockIdx.x) * tile + ctid * V, p_next, m_next);
         for (long long t = blockIdx.x; t < full_tiles; t += gridDim.x, ++it) {
             int const s = static_cast<int>(it % kStages);
             uint32_t const phase = static_cast<uint32_t>((it / kStages) & 1);
+            float p_now[V], m_now[V];
+            if (ahead) {
+#pragma unroll
+                for (int e = 0; e < V; ++e) { p_now[e] = p_next[e]; m_now[e] = m_next[e]; }
+                if (mine && t + gridDim.x < full_tiles) load_state<V>(a.upd, (t + gridDim.x) * tile + ctid * V, p_next, m_next);
+            }
             ptx::mbar_wait(&ring.full[s], phase);
             uint32_t const src = ptx::smem_u32(stages + s * stage_floats);
             uint32_t const row_bytes = static_cast<uint32_t>(tile) * 4u;
+            if (ahead) {
+                if (mine) {
+                    int const c = ctid * V;
+                    long long const x = t * tile + c;
+                    float r[V];
+                    uint32_t const at = src + static_cast<uint32_t>(c) * 4u;
+                    columns<NP, RULE, MIX, V>(a, Ws, used_mask, x, [&](int i, float (&dst)[V]) { lds_vec<V>(dst, at + static_cast<uint32_t>(i) * row_bytes); }, r);
+                    apply_update<V>(a.upd, x, r, a.out, p_now, m_now);
+                }
+            } else
             for (int c = ctid * V; c < tile; c += kConsumers * V) {
                 long long const x = t * tile + c;
                 float r[V];
