@@ -263,13 +263,38 @@ __device__ __forceinline__ void finish_cta(PairwiseArgs const& a, float* slots, 
     __syncthreads();
     if (!is_last) return;
     __threadfence();
+    // Σ over the CTAs' partials, in a fixed order (double): the whole GPU waits for this one CTA, so the sum of each of the
+    // n(n−1)/2 pairs is cut into S segments (b ≡ seg mod S) taken by different threads, each with 4 independent accumulators —
+    // at n = 8 that is 37 loads behind one another per thread where one thread per matrix entry had 296.
+    int const pairs = n * (n - 1) / 2;
+    int const S = pairs == 0 ? 1 : max(1, min(8, static_cast<int>(blockDim.x) / pairs));
+    double* const red = reinterpret_cast<double*>(smem_raw);       // pairs × S segment sums (slots and stages are idle by now)
+    unsigned const G = gridDim.x;
+    for (int w = threadIdx.x; w < pairs * S; w += blockDim.x) {
+        int const pr = w / S, seg = w - pr * S;
+        int i = 0, rest = pr;                                      // pair index → (i < j), row-major over the upper triangle
+        while (rest >= n - 1 - i) { rest -= n - 1 - i; ++i; }
+        int const src = i * n + (i + 1 + rest);
+        double acc0 = 0.0, acc1 = 0.0, acc2 = 0.0, acc3 = 0.0;
+        unsigned b = static_cast<unsigned>(seg);
+        for (; b + 3u * S < G; b += 4u * S) {
+            acc0 += static_cast<double>(__ldcg(a.partials + static_cast<size_t>(b) * nn + src));
+            acc1 += static_cast<double>(__ldcg(a.partials + static_cast<size_t>(b + S) * nn + src));
+            acc2 += static_cast<double>(__ldcg(a.partials + static_cast<size_t>(b + 2u * S) * nn + src));
+            acc3 += static_cast<double>(__ldcg(a.partials + static_cast<size_t>(b + 3u * S) * nn + src));
+        }
+        for (; b < G; b += S) acc0 += static_cast<double>(__ldcg(a.partials + static_cast<size_t>(b) * nn + src));
+        red[w] = (acc0 + acc1) + (acc2 + acc3);
+    }
+    __syncthreads();
     for (int e = threadIdx.x; e < nn; e += blockDim.x) {
         int const i = e / n, j = e % n;
         float out = INFINITY;
         if (i != j) {
-            int const src = i < j ? i * n + j : j * n + i;
+            int const lo = min(i, j), hi = max(i, j);
+            int const pr = lo * n - lo * (lo + 1) / 2 + (hi - lo - 1);
             double total = 0.0;
-            for (unsigned b = 0; b < gridDim.x; ++b) total += static_cast<double>(__ldcg(a.partials + static_cast<size_t>(b) * nn + src));
+            for (int seg = 0; seg < S; ++seg) total += red[pr * S + seg];
             float const f = static_cast<float>(total);
             out = (fabsf(f) <= FLT_MAX) ? f : INFINITY;
         }
