@@ -64,3 +64,50 @@ def test_rpc_ssmw_config1_plumbing():
             "--fw", "1", "--gar", "krum", "--num_iter", "3", "--device", "cpu", "--acc_freq", "1000", "--log", "true"]
     outs = launch("applications/Aggregathor/trainer.py", args, lambda r: ["--rank", str(r)], 7)
     assert "Iteration 2 loss" in outs[0]
+
+
+def _train_dist_rank(rank, world, port, queue, extra):
+    import importlib.util
+    import os
+
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world))
+    path = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "applications", "playgrounds", "train_dist.py")
+    spec = importlib.util.spec_from_file_location("train_dist_playground", path)
+    module = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(module)
+    flat, losses = module.main(["--dataset", "synthetic-mnist", "--model", "convnet", "--num_iter", "8", "--batch", "8", "--device", "cpu"] + extra,
+                               spawned=True)
+    queue.put((rank, flat.numpy().copy(), losses))
+
+
+@pytest.mark.parametrize("broadcast", [True, False])
+def test_playground_train_dist_parameter_server(broadcast):
+    """The vanilla data-parallel playground over gloo (1 server + 2 workers): with the broadcast every rank ends on the server's
+    model and the loss falls; without it (the reference's behaviour) the workers drift away from the server."""
+    import socket
+
+    import numpy as np
+    import torch.multiprocessing as mp
+
+    ctx = mp.get_context("spawn")
+    queue = ctx.Queue()
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        port = s.getsockname()[1]
+    procs = [ctx.Process(target=_train_dist_rank, args=(r, 3, port, queue, [] if broadcast else ["--no-broadcast"])) for r in range(3)]
+    for p in procs:
+        p.start()
+    results = {}
+    for _ in procs:
+        rank, flat, losses = queue.get(timeout=240)
+        results[rank] = (flat, losses)
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    server = results[0][0]
+    assert np.isfinite(server).all() and results[0][1] == []
+    assert len(results[1][1]) == 8 and len(results[2][1]) == 8
+    if broadcast:
+        assert np.array_equal(results[1][0], server) and np.array_equal(results[2][0], server)
+    else:
+        assert not np.array_equal(results[1][0], server)
